@@ -1,0 +1,15 @@
+"""hfops-b200: B200-native (sm_100a) implementation of HeteroFusionRCNN's point-cloud operator path.
+
+Drop-in modules (same function names, argument order and shapes as the reference's
+tf_sampling / tf_grouping / tf_interpolate / tf_cropping / bev_iou), eager on torch CUDA
+tensors, calling hand-written CUDA through the C-ABI of include/hfops.h:
+
+    from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample, gather_point
+    from heterofusionrcnn_b200.grouping.tf_grouping import query_ball_point, group_point
+    from heterofusionrcnn_b200.interpolate.tf_interpolate import three_nn, three_interpolate
+    from heterofusionrcnn_b200.cropping.tf_cropping import pc_crop_and_sample
+    from heterofusionrcnn_b200.bev_iou.bev_iou import compute_bev_iou, oriented_nms
+"""
+from ._lib import HfOpsError, InvalidArgumentError, launch_count, load  # noqa: F401
+
+__version__ = "0.1.0"

@@ -1,0 +1,131 @@
+"""The operator chain the benchmark times: the calls hf/core makes into the five op modules.
+
+Per batch of scans (BASELINE.json configs 2-4):
+  SA level l = 1..4   farthest_point_sample -> gather_point -> query_ball_point ->
+                      group_point(xyz) -> group_point(features)
+                      (hf/core/feature_extractors/pointnet_util.py:42-56)
+  FP level l = 4..1   three_nn -> inverse-distance weights -> three_interpolate
+                      (pointnet_util.py:303-308)
+  RoI crop            pc_crop_and_sample on 512 proposals per scan (rcnn_model.py:478-489)
+  NMS                 oriented_nms on 9000 score-sorted BEV boxes per scan, first 512 kept
+                      (compute_iou.py:67-80, model_util.py:101-142)
+The MLPs between the ops are dense NN layers outside this path; their outputs are
+stood in for by resident synthetic feature tensors of the right shapes.
+"""
+from dataclasses import dataclass, field
+from typing import List
+
+import numpy as np
+import torch
+
+from . import synthetic
+from .bev_iou.bev_iou import oriented_nms_batch
+from .cropping.tf_cropping import pc_crop_and_sample
+from .grouping.tf_grouping import group_point, query_ball_point
+from .interpolate.tf_interpolate import three_interpolate, three_nn
+from .sampling.tf_sampling import farthest_point_sample, gather_point
+
+
+@dataclass
+class ChainConfig:
+    points: int = 16384
+    npoint: List[int] = field(default_factory=lambda: [4096, 1024, 256, 64])
+    radius: List[float] = field(default_factory=lambda: [0.1, 0.2, 0.4, 0.8])
+    nsample: int = 32
+    sa_channels: List[int] = field(default_factory=lambda: [1, 96, 256, 512])  # features grouped at SA l
+    fp_channels: List[int] = field(default_factory=lambda: [1024, 512, 512, 128])  # interpolated at FP 4..1
+    crop_boxes: int = 512
+    crop_resize: int = 512
+    crop_channels: int = 288
+    nms_boxes: int = 9000
+    nms_thresh: float = 0.85
+    post_nms: int = 512
+    with_crop: bool = True
+    with_nms: bool = True
+
+    def scaled(self, points):
+        """Same chain on a different cloud size (npoint = n/4 per level)."""
+        c = ChainConfig(**{**self.__dict__})
+        c.points = points
+        c.npoint = [points // 4, points // 16, points // 64, points // 256]
+        return c
+
+
+def make_host_inputs(cfg, batch, seed=2):
+    """Host-side (numpy) inputs of one batch; `seed` follows SURVEY.md 8d (1000*config+scene)."""
+    xyz, inten = synthetic.make_scans(seed, batch, cfg.points)
+    rng = np.random.default_rng(seed * 7919 + 1)
+    host = {"xyz": xyz, "intensity": inten}
+    n_levels = [cfg.points] + list(cfg.npoint)
+    host["sa_feats"] = [None] + [rng.standard_normal((batch, n_levels[l], cfg.sa_channels[l]), dtype=np.float32)
+                                 for l in range(1, 4)]
+    # FP level j (0 = coarsest): known points = level 4-j, channels fp_channels[j]
+    host["fp_feats"] = [rng.standard_normal((batch, n_levels[4 - j], cfg.fp_channels[j]), dtype=np.float32)
+                        for j in range(4)]
+    if cfg.with_crop:
+        host["crop_fts"] = rng.standard_normal((batch, cfg.points, cfg.crop_channels), dtype=np.float32)
+        host["fg_mask"] = rng.random((batch, cfg.points)) < 0.3
+        boxes = [synthetic.boxes3d_to_corners(synthetic.make_boxes3d(seed * 31 + i, xyz[i], cfg.crop_boxes))
+                 for i in range(batch)]
+        host["crop_boxes"] = np.concatenate(boxes, axis=0)
+        host["box_ind"] = np.repeat(np.arange(batch, dtype=np.int32), cfg.crop_boxes)
+    if cfg.with_nms:
+        host["nms_boxes"] = np.stack([synthetic.make_nms_boxes(seed * 17 + i, cfg.nms_boxes) for i in range(batch)])
+    return host
+
+
+def _to_dev(a, device, pin):
+    if a is None:
+        return None
+    t = torch.from_numpy(np.ascontiguousarray(a))
+    if pin:
+        t = t.pin_memory()
+    return t.to(device, non_blocking=pin)
+
+
+def to_device(host, device, pin=False):
+    out = {}
+    for k, v in host.items():
+        out[k] = [_to_dev(x, device, pin) for x in v] if isinstance(v, list) else _to_dev(v, device, pin)
+    return out
+
+
+def run_chain(dev, cfg):
+    """Run the chain on device-resident inputs `dev` (see make_host_inputs).  Returns a dict of results."""
+    res = {}
+    xyz = [dev["xyz"]]
+    fps_idx = []
+    feats = [dev["intensity"]] + list(dev["sa_feats"][1:])
+    # ---- set abstraction ----
+    for l in range(4):
+        idx = farthest_point_sample(cfg.npoint[l], xyz[l])
+        new_xyz = gather_point(xyz[l], idx)
+        gidx, cnt = query_ball_point(cfg.radius[l], cfg.nsample, xyz[l], new_xyz)
+        gxyz = group_point(xyz[l], gidx)
+        gfeat = group_point(feats[l], gidx)
+        fps_idx.append(idx)
+        xyz.append(new_xyz)
+        res["sa%d" % (l + 1)] = (gidx, cnt, gxyz, gfeat)
+    res["fps_idx"] = fps_idx
+    res["xyz_levels"] = xyz
+    # ---- feature propagation, coarse to fine ----
+    for j in range(4):
+        unknown, known = xyz[3 - j], xyz[4 - j]
+        dist, idx = three_nn(unknown, known)
+        dist = torch.clamp_min(dist, 1e-10)  # pointnet_util.py:304-307
+        inv = 1.0 / dist
+        w = inv / inv.sum(dim=2, keepdim=True)
+        res["fp%d" % (4 - j)] = (dist, idx, three_interpolate(dev["fp_feats"][j], idx, w))
+    if cfg.with_crop:
+        res["crop"] = pc_crop_and_sample(dev["xyz"], dev["crop_fts"], dev["intensity"], dev["fg_mask"],
+                                         dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
+    if cfg.with_nms:
+        keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
+        res["nms_keep"] = keep[:, : cfg.post_nms]
+        res["nms_num"] = num
+    return res
+
+
+def chain_launches(cfg):
+    """Kernels of libhfops launched by one run_chain call."""
+    return 4 * 5 + 4 * 2 + (1 if cfg.with_crop else 0) + (2 if cfg.with_nms else 0)

@@ -1,0 +1,208 @@
+// cropping.cu — RoI point crop with feature pooling (pc_crop_and_sample) for sm_100a.
+//
+// Replaces cropping/tf_cropping_g.cu:7-132 + the output memsets of
+// cropping/tf_cropping.cpp:171-176 (see include/hfops.h).
+//
+// One CTA per box, three phases, everything the box needs staying in shared memory:
+//   1. select: each warp scans a contiguous slice of the scene's points in ascending
+//      order and compacts the inside-the-box indices with ballot/popc (ordered, no
+//      atomics — the reference's atomicInc slot assignment, :85, is a race); a prefix over
+//      the 8 warp counts concatenates the slices, first `resize` kept;
+//   2. pad: slot s >= count repeats slot (s - count) mod count (:108-126) — done on the
+//      index list, so padded rows are copied from the source exactly like selected rows;
+//   3. copy: HBM-bound.  One warp per output row, 128-bit loads of the gathered feature
+//      row and streaming 128-bit stores, four rows in flight per warp.  Every output
+//      element is written exactly once (empty boxes are zero-filled here), so no memset
+//      pass over the 4.8 GB output is needed.
+#include "common.cuh"
+
+namespace hf {
+namespace {
+
+constexpr int kCropThreads = 256;
+constexpr int kCropWarps = kCropThreads / 32;
+
+// dot() of tf_cropping_g.cu:3-5 in the order nvcc contracts it on sm_100a.
+__device__ __forceinline__ float dot3(float x1, float y1, float z1, float x2, float y2, float z2) {
+    return __fmaf_rn(z1, z2, __fmaf_rn(y1, y2, __fmul_rn(x1, x2)));
+}
+
+template <bool VEC4>
+__global__ void __launch_bounds__(kCropThreads)
+    crop_kernel(const float *__restrict__ pts_data, const float *__restrict__ fts_data,
+                const float *__restrict__ int_data, const uint8_t *__restrict__ mask_data,
+                const float *__restrict__ boxes, const int *__restrict__ box_ind, int npts, int resize,
+                int channel, int ichannel, float *__restrict__ crop_pts, float *__restrict__ crop_fts,
+                float *__restrict__ crop_int, uint8_t *__restrict__ crop_mask, int *__restrict__ crop_ind,
+                uint8_t *__restrict__ non_empty) {
+    extern __shared__ int smem_i[];
+    int *sel = smem_i;                // [resize] final source index per slot
+    int *wlist = smem_i + resize;     // [kCropWarps][resize] per-warp ordered hits
+    __shared__ int wcount[kCropWarps];
+
+    const int b = blockIdx.x;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const float *bx = boxes + (size_t)b * 24;
+    const float p1x = bx[0], p1y = bx[8], p1z = bx[16];
+    const float p2x = bx[1], p2y = bx[9], p2z = bx[17];
+    const float p4x = bx[3], p4y = bx[11], p4z = bx[19];
+    const float p5x = bx[4], p5y = bx[12], p5z = bx[20];
+    // is_point_inside (:7-41); everything that does not depend on the point is hoisted
+    const float ux = p2x - p1x, uy = p2y - p1y, uz = p2z - p1z;
+    const float vx = p4x - p1x, vy = p4y - p1y, vz = p4z - p1z;
+    const float wx = p5x - p1x, wy = p5y - p1y, wz = p5z - p1z;
+    const float u_p1 = dot3(ux, uy, uz, p1x, p1y, p1z), u_p2 = dot3(ux, uy, uz, p2x, p2y, p2z);
+    const float v_p1 = dot3(vx, vy, vz, p1x, p1y, p1z), v_p4 = dot3(vx, vy, vz, p4x, p4y, p4z);
+    const float w_p1 = dot3(wx, wy, wz, p1x, p1y, p1z), w_p5 = dot3(wx, wy, wz, p5x, p5y, p5z);
+
+    const int bch = box_ind[b];
+    const float *pts = pts_data + (size_t)bch * npts * 3;
+
+    // ---- 1. select ----
+    const int per_warp = (npts + kCropWarps - 1) / kCropWarps;
+    const int lo = warp * per_warp;
+    const int hi = min(npts, lo + per_warp);
+    int *mine = wlist + warp * resize;
+    int cnt = 0;
+    for (int p0 = lo; p0 < hi && cnt < resize; p0 += 32) {
+        int p = p0 + lane;
+        bool in = false;
+        if (p < hi) {
+            float px = pts[(size_t)p * 3], py = pts[(size_t)p * 3 + 1], pz = pts[(size_t)p * 3 + 2];
+            float ud = dot3(ux, uy, uz, px, py, pz);
+            float vd = dot3(vx, vy, vz, px, py, pz);
+            float wd = dot3(wx, wy, wz, px, py, pz);
+            in = u_p1 < ud && ud < u_p2 && v_p1 < vd && vd < v_p4 && w_p1 < wd && wd < w_p5;
+        }
+        unsigned bal = __ballot_sync(0xffffffffu, in);
+        int pos = cnt + __popc(bal & ((1u << lane) - 1u));
+        if (in && pos < resize) mine[pos] = p;
+        cnt += __popc(bal);
+    }
+    if (cnt > resize) cnt = resize;
+    if (lane == 0) wcount[warp] = cnt;
+    __syncthreads();
+    int offset = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kCropWarps; ++w) {
+        int c = wcount[w];
+        if (w < warp) offset += c;
+        total += c;
+    }
+    const int count = min(total, resize);
+    for (int i = lane; i < cnt; i += 32) {
+        int pos = offset + i;
+        if (pos < resize) sel[pos] = mine[i];
+    }
+    __syncthreads();
+    // ---- 2. pad ----
+    if (count > 0) {
+        for (int s = count + t; s < resize; s += kCropThreads) sel[s] = sel[(s - count) % count];
+    }
+    __syncthreads();
+    if (t == 0) non_empty[b] = count > 0 ? 1 : 0;
+
+    // ---- 3. copy ----
+    float *o_pts = crop_pts + (size_t)b * resize * 3;
+    float *o_int = crop_int + (size_t)b * resize * ichannel;
+    uint8_t *o_mask = crop_mask + (size_t)b * resize;
+    int *o_ind = crop_ind + (size_t)b * resize;
+    const float *intens = int_data + (size_t)bch * npts * ichannel;
+    const uint8_t *mask = mask_data + (size_t)bch * npts;
+    for (int s = t; s < resize; s += kCropThreads) {
+        if (count > 0) {
+            int p = sel[s];
+            o_pts[s * 3] = pts[(size_t)p * 3];
+            o_pts[s * 3 + 1] = pts[(size_t)p * 3 + 1];
+            o_pts[s * 3 + 2] = pts[(size_t)p * 3 + 2];
+            for (int c = 0; c < ichannel; ++c) o_int[s * ichannel + c] = intens[(size_t)p * ichannel + c];
+            o_mask[s] = mask[p];
+            o_ind[s] = p;
+        } else {
+            o_pts[s * 3] = 0.f; o_pts[s * 3 + 1] = 0.f; o_pts[s * 3 + 2] = 0.f;
+            for (int c = 0; c < ichannel; ++c) o_int[s * ichannel + c] = 0.f;
+            o_mask[s] = 0;
+            o_ind[s] = 0;
+        }
+    }
+    if (VEC4) {
+        const int c4 = channel >> 2;
+        const float4 *fts = reinterpret_cast<const float4 *>(fts_data) + (size_t)bch * npts * c4;
+        float4 *o = reinterpret_cast<float4 *>(crop_fts) + (size_t)b * resize * c4;
+        if (count > 0) {
+            for (int s0 = warp * 4; s0 < resize; s0 += kCropWarps * 4) {
+                int src[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) src[u] = (s0 + u < resize) ? sel[s0 + u] : -1;
+                for (int v = lane; v < c4; v += 32) {
+                    float4 val[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (src[u] >= 0) val[u] = __ldg(&fts[(size_t)src[u] * c4 + v]);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (src[u] >= 0) stg_cs_f4(&o[(size_t)(s0 + u) * c4 + v], val[u]);
+                }
+            }
+        } else {
+            const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+            const size_t tot = (size_t)resize * c4;
+            for (size_t e = t; e < tot; e += kCropThreads) stg_cs_f4(&o[e], zero);
+        }
+    } else {
+        const float *fts = fts_data + (size_t)bch * npts * channel;
+        float *o = crop_fts + (size_t)b * resize * channel;
+        for (int s = warp; s < resize; s += kCropWarps) {
+            if (count > 0) {
+                const float *src = fts + (size_t)sel[s] * channel;
+                for (int c = lane; c < channel; c += 32) o[(size_t)s * channel + c] = __ldg(&src[c]);
+            } else {
+                for (int c = lane; c < channel; c += 32) o[(size_t)s * channel + c] = 0.f;
+            }
+        }
+    }
+}
+
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_pc_crop_and_sample(const float *pts, const float *fts, const float *intensities,
+                                     const uint8_t *mask, const float *boxes, const int *box_ind, int num_boxes,
+                                     int batch, int npts, int resize, int channel, int intensity_channel,
+                                     float *crop_pts, float *crop_fts, float *crop_intensities,
+                                     uint8_t *crop_mask, int *crop_ind, uint8_t *non_empty_box,
+                                     hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(resize > 0, "PcCropAndSample expects positive resize");
+    HF_REQUIRE(batch >= 1 && npts > 0, "PcCropAndSample expects (B, P, 3) pts shape");
+    HF_REQUIRE(channel > 0, "PcCropAndSample expects (B, P, C) fts shape");
+    HF_REQUIRE(intensity_channel >= 1, "PcCropAndSample expects (B, P, 1) intensities shape");
+    HF_REQUIRE(num_boxes >= 0, "PcCropAndSample expects (N, 3, 8) boxes shape");
+    HF_REQUIRE(pts && fts && intensities && mask && boxes && box_ind && crop_pts && crop_fts &&
+                   crop_intensities && crop_mask && crop_ind && non_empty_box,
+               "PcCropAndSample: null pointer");
+    if (num_boxes == 0) return HF_OK;
+    size_t smem = (size_t)(1 + kCropWarps) * resize * sizeof(int);
+    if (smem > 200 * 1024) {
+        set_error("PcCropAndSample: resize=%d needs %zu bytes of shared memory (max 204800)", resize, smem);
+        return HF_ERR_UNSUPPORTED;
+    }
+    bool vec = (channel % 4 == 0) && ((reinterpret_cast<uintptr_t>(fts) & 15) == 0) &&
+               ((reinterpret_cast<uintptr_t>(crop_fts) & 15) == 0);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (vec) {
+        auto kern = crop_kernel<true>;
+        if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
+                                                   intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask,
+                                                   crop_ind, non_empty_box);
+    } else {
+        auto kern = crop_kernel<false>;
+        if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
+                                                   intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask,
+                                                   crop_ind, non_empty_box);
+    }
+    HF_LAUNCH_OK("crop_kernel");
+    return HF_OK;
+}

@@ -1,0 +1,241 @@
+// grouping.cu — query_ball_point and group_point for sm_100a.
+//
+// Replaces grouping/tf_grouping_g.cu:3-57 of the reference (see include/hfops.h).
+//
+// query_ball_point: one thread per query scans the dataset points in ascending index
+// (which is what "first nsample in the ball" means, tf_grouping_g.cu:15-33); the dataset
+// is streamed through shared memory in TMA-staged tiles and read as broadcasts, four
+// candidates per three 128-bit loads.  The reference's test
+//     max(sqrtf(d2), 1e-20f) < radius
+// is evaluated as d2 < thr2 with thr2 computed on the host as the smallest float whose
+// correctly-rounded sqrtf is >= radius — sqrtf is monotonic and correctly rounded on
+// both sides, so the two predicates accept exactly the same d2 and the inner loop has no
+// square root.  Hit lists are assembled per CTA in shared memory and written coalesced.
+//
+// group_point: pure row gather, HBM bound.  One warp per output row walks the channels
+// with 128-bit loads/stores (channel-last, as the reference API already is), four rows in
+// flight per warp; c not divisible by 4 (xyz: 3, intensity: 1) takes a scalar path.
+#include <math.h>
+
+#include "common.cuh"
+#include "xyz_tiles.cuh"
+
+namespace hf {
+namespace {
+
+constexpr int kBqThreads = 128;
+constexpr int kBqTile = 1024;
+
+// ROWBUF: hit rows are staged in dynamic shared memory [threads][nsample+1] and written
+// coalesced at the end; otherwise (very large nsample) they go straight to global.
+template <bool ROWBUF>
+__global__ void __launch_bounds__(kBqThreads)
+    query_ball_kernel(int n, int m, float thr2, int nsample, const float *__restrict__ xyz1,
+                      const float *__restrict__ xyz2, int *__restrict__ idx, int *__restrict__ pts_cnt) {
+    __shared__ __align__(16) float stage0[kBqTile * 3];
+    __shared__ __align__(16) float stage1[kBqTile * 3];
+    __shared__ __align__(8) uint64_t bars[2];
+    extern __shared__ int rowbuf[];  // ROWBUF: kBqThreads * (nsample + 1)
+
+    const int t = threadIdx.x;
+    const int scene = blockIdx.y;
+    const int j = blockIdx.x * kBqThreads + t;
+    const bool active = j < m;
+    const float *q = xyz2 + ((size_t)scene * m + (active ? j : 0)) * 3;
+    const float x2 = q[0], y2 = q[1], z2 = q[2];
+    int *grow = idx + ((size_t)scene * m + (active ? j : 0)) * nsample;
+    int *srow = rowbuf + t * (nsample + 1);
+    int cnt = active ? 0 : nsample;
+
+    XyzTilePipe<kBqTile> pipe;
+    pipe.init(stage0, stage1, bars, xyz1 + (size_t)scene * n * 3, n);
+    pipe.prefetch(0);
+    for (int i = 0; i < pipe.ntiles; ++i) {
+        pipe.prefetch(i + 1);
+        const float *s = pipe.acquire(i);
+        const int c = pipe.count(i);
+        const int kbase = i * kBqTile;
+        if (cnt < nsample) {
+            const float4 *s4 = reinterpret_cast<const float4 *>(s);
+            const int groups = c >> 2;
+            int g = 0;
+#pragma unroll 2
+            for (; g < groups; ++g) {
+                float4 a = s4[3 * g], bb = s4[3 * g + 1], cc = s4[3 * g + 2];
+                float d0 = sqdist(x2 - a.x, y2 - a.y, z2 - a.z);
+                float d1 = sqdist(x2 - a.w, y2 - bb.x, z2 - bb.y);
+                float d2 = sqdist(x2 - bb.z, y2 - bb.w, z2 - cc.x);
+                float d3 = sqdist(x2 - cc.y, y2 - cc.z, z2 - cc.w);
+                if (fminf(fminf(d0, d1), fminf(d2, d3)) < thr2) {
+                    float dd[4] = {d0, d1, d2, d3};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (dd[u] < thr2 && cnt < nsample) {
+                            if (ROWBUF) srow[cnt] = kbase + 4 * g + u;
+                            else grow[cnt] = kbase + 4 * g + u;
+                            ++cnt;
+                        }
+                    }
+                    if (cnt >= nsample) break;
+                }
+            }
+            if (cnt < nsample) {
+                for (int k = groups << 2; k < c; ++k) {
+                    float d = sqdist(x2 - s[3 * k], y2 - s[3 * k + 1], z2 - s[3 * k + 2]);
+                    if (d < thr2 && cnt < nsample) {
+                        if (ROWBUF) srow[cnt] = kbase + k;
+                        else grow[cnt] = kbase + k;
+                        ++cnt;
+                    }
+                }
+            }
+        }
+        // all queries of the CTA full -> nothing left to find (also frees the stage)
+        if (__syncthreads_and(cnt >= nsample)) break;
+    }
+    pipe.drain();
+
+    if (active) pts_cnt[(size_t)scene * m + j] = cnt;
+    if (ROWBUF) {
+        srow[nsample] = active ? cnt : 0;
+        __syncthreads();
+        const int rows = min(kBqThreads, m - blockIdx.x * kBqThreads);
+        int *gbase = idx + ((size_t)scene * m + (size_t)blockIdx.x * kBqThreads) * nsample;
+        const int total = rows * nsample;
+        for (int e = t; e < total; e += kBqThreads) {
+            int r = e / nsample, l = e - r * nsample;
+            const int *row = rowbuf + r * (nsample + 1);
+            int rc = row[nsample];
+            // unused slots repeat the first hit (:26-29); a row with no hit is written as 0
+            gbase[e] = l < rc ? row[l] : (rc > 0 ? row[0] : 0);
+        }
+    } else if (active) {
+        int first = cnt > 0 ? grow[0] : 0;
+        for (int l = cnt; l < nsample; ++l) grow[l] = first;
+    }
+}
+
+// ---- group_point ------------------------------------------------------------------
+constexpr int kGpThreads = 256;
+constexpr int kGpRowsPerWarp = 4;
+
+// c % 4 == 0, 16-byte aligned rows.  grid = (blocks, b).
+__global__ void __launch_bounds__(kGpThreads)
+    group_point_vec4_kernel(int n, int c4, int rows, const float4 *__restrict__ points,
+                            const int *__restrict__ idx, float4 *__restrict__ out) {
+    const int scene = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * kGpThreads + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * kGpThreads) >> 5;
+    const float4 *pts = points + (size_t)scene * n * c4;
+    const int *ind = idx + (size_t)scene * rows;
+    float4 *o = out + (size_t)scene * rows * c4;
+    for (int r0 = warp * kGpRowsPerWarp; r0 < rows; r0 += nwarps * kGpRowsPerWarp) {
+        int src[kGpRowsPerWarp];
+#pragma unroll
+        for (int u = 0; u < kGpRowsPerWarp; ++u) src[u] = (r0 + u < rows) ? ind[r0 + u] : -1;
+        for (int v = lane; v < c4; v += 32) {
+            float4 val[kGpRowsPerWarp];
+#pragma unroll
+            for (int u = 0; u < kGpRowsPerWarp; ++u)
+                if (src[u] >= 0) val[u] = __ldg(&pts[(size_t)src[u] * c4 + v]);
+#pragma unroll
+            for (int u = 0; u < kGpRowsPerWarp; ++u)
+                if (src[u] >= 0) stg_cs_f4(&o[(size_t)(r0 + u) * c4 + v], val[u]);
+        }
+    }
+}
+
+// any c: flat (row, channel) mapping so stores are coalesced; gathers are 4-byte.
+__global__ void __launch_bounds__(kGpThreads)
+    group_point_scalar_kernel(int n, int c, int rows, const float *__restrict__ points,
+                              const int *__restrict__ idx, float *__restrict__ out) {
+    const int scene = blockIdx.y;
+    const float *pts = points + (size_t)scene * n * c;
+    const int *ind = idx + (size_t)scene * rows;
+    float *o = out + (size_t)scene * rows * c;
+    const long long total = (long long)rows * c;
+    for (long long e = (long long)blockIdx.x * kGpThreads + threadIdx.x; e < total;
+         e += (long long)gridDim.x * kGpThreads) {
+        int r = (int)(e / c);
+        int l = (int)(e - (long long)r * c);
+        o[e] = __ldg(&pts[(size_t)ind[r] * c + l]);
+    }
+}
+
+}  // namespace
+
+// Smallest float t with sqrtf(t) >= radius; d2 < t  <=>  sqrtf(d2) < radius for d2 >= 0.
+// The reference additionally clamps sqrtf(d2) up to 1e-20f, which only matters for
+// radius <= 1e-20f, where nothing can be accepted (returns 0).
+float ball_threshold(float radius) {
+    if (!(radius > 1e-20f)) return 0.f;
+    double r2 = (double)radius * (double)radius;
+    float t = (float)r2;
+    if (isinf(t)) return t;
+    while (t > 0.f && sqrtf(nextafterf(t, 0.f)) >= radius) t = nextafterf(t, 0.f);
+    while (sqrtf(t) < radius) t = nextafterf(t, INFINITY);
+    return t;
+}
+
+}  // namespace hf
+
+extern "C" int hf_query_ball_point(int b, int n, int m, float radius, int nsample, const float *xyz1,
+                                   const float *xyz2, int *idx, int *pts_cnt, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(radius > 0, "QueryBallPoint expects positive radius");
+    HF_REQUIRE(nsample > 0, "QueryBallPoint expects positive nsample");
+    HF_REQUIRE(b >= 0 && n >= 1 && m >= 0, "QueryBallPoint expects (batch_size, ndataset, 3) xyz1 shape.");
+    HF_REQUIRE(xyz1 && xyz2 && idx && pts_cnt, "QueryBallPoint: null pointer");
+    HF_REQUIRE(b <= 65535, "QueryBallPoint: batch_size > 65535 not supported");
+    if (b == 0 || m == 0) return HF_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    float thr2 = ball_threshold(radius);
+    dim3 grid((m + kBqThreads - 1) / kBqThreads, b);
+    size_t rowbytes = (size_t)kBqThreads * (nsample + 1) * sizeof(int);
+    if (rowbytes <= 160 * 1024) {
+        auto kern = query_ball_kernel<true>;
+        if (rowbytes + 25 * 1024 > 48 * 1024)
+            HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rowbytes));
+        kern<<<grid, kBqThreads, rowbytes, s>>>(n, m, thr2, nsample, xyz1, xyz2, idx, pts_cnt);
+    } else {
+        query_ball_kernel<false><<<grid, kBqThreads, 0, s>>>(n, m, thr2, nsample, xyz1, xyz2, idx, pts_cnt);
+    }
+    HF_LAUNCH_OK("query_ball_kernel");
+    return HF_OK;
+}
+
+extern "C" int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,
+                              float *out, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(b >= 0 && n >= 1 && c >= 1 && m >= 0 && nsample >= 0,
+               "GroupPoint expects (batch_size, num_points, channel) points shape");
+    HF_REQUIRE(points && idx && out, "GroupPoint: null pointer");
+    HF_REQUIRE(b <= 65535, "GroupPoint: batch_size > 65535 not supported");
+    HF_REQUIRE((long long)m * nsample < (1ll << 31), "GroupPoint: npoint*nsample must fit int32");
+    const int rows = m * nsample;
+    if (b == 0 || rows == 0) return HF_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int sms = num_sms();
+    bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(points) & 15) == 0) &&
+               ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    if (vec) {
+        int warps_needed = (rows + kGpRowsPerWarp - 1) / kGpRowsPerWarp;
+        int blocks = (warps_needed + (kGpThreads / 32) - 1) / (kGpThreads / 32);
+        int cap = (sms * 8 + b - 1) / b;  // ~8 resident CTAs per SM over the whole grid
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        group_point_vec4_kernel<<<dim3(blocks, b), kGpThreads, 0, s>>>(
+            n, c / 4, rows, reinterpret_cast<const float4 *>(points), idx, reinterpret_cast<float4 *>(out));
+        HF_LAUNCH_OK("group_point_vec4_kernel");
+    } else {
+        long long total = (long long)rows * c;
+        long long blocks = (total + kGpThreads - 1) / kGpThreads;
+        long long cap = ((long long)sms * 8 + b - 1) / b;
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        group_point_scalar_kernel<<<dim3((unsigned)blocks, b), kGpThreads, 0, s>>>(n, c, rows, points, idx, out);
+        HF_LAUNCH_OK("group_point_scalar_kernel");
+    }
+    return HF_OK;
+}

@@ -1,0 +1,64 @@
+"""Ball query / group_point — mirror of the reference's grouping/tf_grouping.py.
+
+Native code: csrc/grouping.cu via include/hfops.h.
+"""
+import torch
+
+from .. import _lib
+from .._tensors import dev_tensor, require, stream_ptr
+
+
+def query_ball_point(radius, nsample, xyz1, xyz2):
+    """
+    Input:
+        radius: float32, ball search radius
+        nsample: int32, number of points selected in each ball region
+        xyz1: (batch_size, ndataset, 3) float32 array, input points
+        xyz2: (batch_size, npoint, 3) float32 array, query points
+    Output:
+        idx: (batch_size, npoint, nsample) int32 array, indices to input points
+        pts_cnt: (batch_size, npoint) int32 array, number of unique points in each local region
+
+    Reference: grouping/tf_grouping.py:11-23, op checks grouping/tf_grouping.cpp:67-106.
+    Rows with no point in the ball are returned as 0 (uninitialised in the reference).
+    """
+    require(float(radius) > 0, "QueryBallPoint expects positive radius")
+    require(int(nsample) > 0, "QueryBallPoint expects positive nsample")
+    xyz1 = dev_tensor(xyz1, torch.float32, "xyz1")
+    xyz2 = dev_tensor(xyz2, torch.float32, "xyz2")
+    require(xyz1.dim() == 3 and xyz1.shape[2] == 3, "QueryBallPoint expects (batch_size, ndataset, 3) xyz1 shape.")
+    require(xyz2.dim() == 3 and xyz2.shape[2] == 3, "QueryBallPoint expects (batch_size, npoint, 3) xyz2 shape.")
+    require(xyz2.shape[0] == xyz1.shape[0], "QueryBallPoint expects xyz1 and xyz2 to share batch_size")
+    b, n, m = xyz1.shape[0], xyz1.shape[1], xyz2.shape[1]
+    idx = torch.empty((b, m, int(nsample)), dtype=torch.int32, device=xyz1.device)
+    pts_cnt = torch.empty((b, m), dtype=torch.int32, device=xyz1.device)
+    with torch.cuda.device(xyz1.device):
+        rc = _lib.load().hf_query_ball_point(
+            b, n, m, float(radius), int(nsample), xyz1.data_ptr(), xyz2.data_ptr(), idx.data_ptr(),
+            pts_cnt.data_ptr(), stream_ptr(xyz1.device))
+    _lib.check(rc, "query_ball_point")
+    return idx, pts_cnt
+
+
+def group_point(points, idx):
+    """
+    Input:
+        points: (batch_size, ndataset, channel) float32 array, points to sample from
+        idx: (batch_size, npoint, nsample) int32 array, indices to points
+    Output:
+        out: (batch_size, npoint, nsample, channel) float32 array, values sampled from points
+
+    Reference: grouping/tf_grouping.py:44-52, op checks grouping/tf_grouping.cpp:143-171.
+    """
+    points = dev_tensor(points, torch.float32, "points")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    require(points.dim() == 3, "GroupPoint expects (batch_size, num_points, channel) points shape")
+    b, n, c = points.shape
+    require(idx.dim() == 3 and idx.shape[0] == b, "GroupPoint expects (batch_size, npoints, nsample) idx shape")
+    m, nsample = idx.shape[1], idx.shape[2]
+    out = torch.empty((b, m, nsample, c), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        rc = _lib.load().hf_group_point(b, n, c, m, nsample, points.data_ptr(), idx.data_ptr(), out.data_ptr(),
+                                        stream_ptr(points.device))
+    _lib.check(rc, "group_point")
+    return out

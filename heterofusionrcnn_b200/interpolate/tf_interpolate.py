@@ -1,0 +1,83 @@
+"""three_nn / three_interpolate — mirror of the reference's interpolate/tf_interpolate.py.
+
+Native code: csrc/interpolate.cu via include/hfops.h.
+"""
+import torch
+
+from .. import _lib
+from .._tensors import dev_tensor, require, stream_ptr
+
+
+def three_nn(xyz1, xyz2):
+    """
+    Input:
+        xyz1: (b,n,3) float32 array, unknown points
+        xyz2: (b,m,3) float32 array, known points
+    Output:
+        dist: (b,n,3) float32 array, distances to known points
+        idx: (b,n,3) int32 array, indices to known points
+
+    Reference: interpolate/tf_interpolate.py:11-20, op checks interpolate/tf_interpolate.cpp:63-96.
+    As in the reference kernel the "distances" are SQUARED distances, ascending.
+    """
+    xyz1 = dev_tensor(xyz1, torch.float32, "xyz1")
+    xyz2 = dev_tensor(xyz2, torch.float32, "xyz2")
+    require(xyz1.dim() == 3 and xyz1.shape[2] == 3, "ThreeNN expects (b,n,3) xyz1 shape.")
+    require(xyz2.dim() == 3 and xyz2.shape[2] == 3, "ThreeNN expects (b,m,3) xyz2 shape.")
+    require(xyz2.shape[0] == xyz1.shape[0], "ThreeNN expects xyz1 and xyz2 to share b")
+    b, n, m = xyz1.shape[0], xyz1.shape[1], xyz2.shape[1]
+    dist = torch.empty((b, n, 3), dtype=torch.float32, device=xyz1.device)
+    idx = torch.empty((b, n, 3), dtype=torch.int32, device=xyz1.device)
+    with torch.cuda.device(xyz1.device):
+        rc = _lib.load().hf_three_nn(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
+                                     stream_ptr(xyz1.device))
+    _lib.check(rc, "three_nn")
+    return dist, idx
+
+
+def three_interpolate(points, idx, weight):
+    """
+    Input:
+        points: (b,m,c) float32 array, known points
+        idx: (b,n,3) int32 array, indices to known points
+        weight: (b,n,3) float32 array, weights on known points
+    Output:
+        out: (b,n,c) float32 array, interpolated point values
+
+    Reference: interpolate/tf_interpolate.py:26-37 (transpose -> channel-first op -> transpose);
+    here the kernel works channel-last directly, so no transposes are materialised.
+    """
+    points = dev_tensor(points, torch.float32, "points")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    weight = dev_tensor(weight, torch.float32, "weight")
+    require(points.dim() == 3, "ThreeInterpolate expects (b,m,c) points shape")
+    b, m, c = points.shape
+    require(idx.dim() == 3 and idx.shape[0] == b and idx.shape[2] == 3, "ThreeInterpolate expects (b,n,3) idx shape")
+    n = idx.shape[1]
+    require(weight.dim() == 3 and weight.shape[0] == b and weight.shape[1] == n and weight.shape[2] == 3,
+            "ThreeInterpolate expects (b,n,3) weight shape")
+    out = torch.empty((b, n, c), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        rc = _lib.load().hf_three_interpolate_nlc(b, m, c, n, points.data_ptr(), idx.data_ptr(), weight.data_ptr(),
+                                                  out.data_ptr(), stream_ptr(points.device))
+    _lib.check(rc, "three_interpolate")
+    return out
+
+
+def three_interpolate_channel_first(points, idx, weight):
+    """The native op's own layout (interpolate/tf_interpolate.cpp:102-139): points (b,c,m) -> (b,c,n)."""
+    points = dev_tensor(points, torch.float32, "points")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    weight = dev_tensor(weight, torch.float32, "weight")
+    require(points.dim() == 3, "ThreeInterpolate expects (b,c,m) points shape")
+    b, c, m = points.shape
+    require(idx.dim() == 3 and idx.shape[0] == b and idx.shape[2] == 3, "ThreeInterpolate expects (b,n,3) idx shape")
+    n = idx.shape[1]
+    require(weight.dim() == 3 and weight.shape[0] == b and weight.shape[1] == n and weight.shape[2] == 3,
+            "ThreeInterpolate expects (b,n,3) weight shape")
+    out = torch.empty((b, c, n), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        rc = _lib.load().hf_three_interpolate(b, c, m, n, points.data_ptr(), idx.data_ptr(), weight.data_ptr(),
+                                              out.data_ptr(), stream_ptr(points.device))
+    _lib.check(rc, "three_interpolate")
+    return out

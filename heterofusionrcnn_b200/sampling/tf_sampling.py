@@ -1,0 +1,64 @@
+"""Farthest point sampling / gather_point — mirror of the reference's sampling/tf_sampling.py.
+
+Same names, argument order and shapes; tensors are torch CUDA tensors (used as device
+buffers) instead of lazy TF graph nodes.  Native code: csrc/sampling.cu via include/hfops.h.
+"""
+import torch
+
+from .. import _lib
+from .._tensors import dev_tensor, require, stream_ptr
+
+# FPS keeps clouds of up to this many points entirely on chip; beyond it the kernel needs
+# the reference's (32, n) float scratch (sampling/tf_sampling.cpp:115).
+_ON_CHIP_POINTS = 65536
+
+
+def gather_point(inp, idx):
+    """
+input:
+    batch_size * ndataset * 3   float32
+    batch_size * npoints        int32
+returns:
+    batch_size * npoints * 3    float32
+
+    Reference: sampling/tf_sampling.py:38-46, op checks sampling/tf_sampling.cpp:126-148.
+    """
+    inp = dev_tensor(inp, torch.float32, "inp")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    require(inp.dim() == 3 and inp.shape[2] == 3, "GatherPoint expects (batch_size,num_points,3) inp shape")
+    b, n = inp.shape[0], inp.shape[1]
+    require(idx.dim() == 2 and idx.shape[0] == b, "GatherPoint expects (batch_size,num_result) idx shape")
+    m = idx.shape[1]
+    out = torch.empty((b, m, 3), dtype=torch.float32, device=inp.device)
+    with torch.cuda.device(inp.device):
+        rc = _lib.load().hf_gather_point(b, n, m, inp.data_ptr(), idx.data_ptr(), out.data_ptr(), stream_ptr(inp.device))
+    _lib.check(rc, "gather_point")
+    return out
+
+
+def farthest_point_sample(npoint, inp):
+    """
+input:
+    int32
+    batch_size * ndataset * 3   float32
+returns:
+    batch_size * npoint         int32
+
+    Reference: sampling/tf_sampling.py:61-69, op checks sampling/tf_sampling.cpp:95-123.
+    Starts at index 0; ties resolve exactly as the reference kernel does
+    (sampling/tf_sampling_g.cu:146-163).
+    """
+    require(isinstance(npoint, int) and npoint > 0, "FarthestPointSample expects positive npoint")
+    inp = dev_tensor(inp, torch.float32, "inp")
+    require(inp.dim() == 3 and inp.shape[2] == 3, "FarthestPointSample expects (batch_size,num_points,3) inp shape")
+    b, n = inp.shape[0], inp.shape[1]
+    out = torch.empty((b, npoint), dtype=torch.int32, device=inp.device)
+    temp = None
+    if n > _ON_CHIP_POINTS:
+        temp = torch.empty((32, n), dtype=torch.float32, device=inp.device)
+    with torch.cuda.device(inp.device):
+        rc = _lib.load().hf_farthest_point_sample(
+            b, n, npoint, inp.data_ptr(), temp.data_ptr() if temp is not None else None, out.data_ptr(),
+            stream_ptr(inp.device))
+    _lib.check(rc, "farthest_point_sample")
+    return out

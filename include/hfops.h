@@ -1,0 +1,144 @@
+/* hfops.h — C-ABI of libhfops.so: the B200 (sm_100a) implementation of the
+ * HeteroFusionRCNN point-cloud operator path.
+ *
+ * Every entry point replaces one native launcher of the reference (the functions
+ * its TF OpKernels forward-declare and its *_g.cu files define); the reference
+ * interface each one stands in for is cited as file:line against the reference
+ * tree.  Differences from the reference launchers, uniform across the API:
+ *   - extern "C", plain pointers and ints only (no torch / TF types);
+ *   - a trailing `hf_stream_t stream` (a cudaStream_t; NULL = legacy default
+ *     stream, which is what the reference always used);
+ *   - an int status is returned (HF_OK or a negative HF_ERR_*); nothing ever
+ *     calls exit() (reference: tf_interpolate_g.cu:82-86, bev_iou.cpp:14-22);
+ *   - no hidden allocation: scratch is passed in by the caller and sized by a
+ *     *_workspace_bytes() query;
+ *   - all pointers are DEVICE pointers unless the name ends in _host;
+ *   - re-entrant: no global state besides a launch counter and a per-thread
+ *     last-error string.
+ * Layouts are the reference's: row-major contiguous (batch, points, channels),
+ * fp32 / int32, bool = 1 byte.
+ */
+#ifndef HFOPS_H_
+#define HFOPS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void *hf_stream_t; /* cudaStream_t */
+
+#define HF_OK 0
+#define HF_ERR_INVALID_ARG (-1) /* the reference's OP_REQUIRES -> InvalidArgument cases */
+#define HF_ERR_CUDA (-2)        /* a CUDA runtime call / launch failed */
+#define HF_ERR_WORKSPACE (-3)   /* workspace NULL or too small */
+#define HF_ERR_UNSUPPORTED (-4) /* size outside what the kernels cover */
+
+/* ---- library info ------------------------------------------------------ */
+const char *hf_version(void);
+/* Message for the last non-HF_OK status returned on the calling thread. */
+const char *hf_last_error(void);
+/* Number of kernels this library has launched in this process (all threads). */
+unsigned long long hf_launch_count(void);
+
+/* ---- sampling ----------------------------------------------------------- */
+/* Replaces farthestpointsamplingLauncher(b,n,m,inp,temp,out), sampling/tf_sampling_g.cu:203
+ * (op: sampling/tf_sampling.cpp:95-123).  inp (b,n,3) -> out (b,m) int32, out[:,0]=0.
+ * Tie-break is the reference's: max min-distance, then lowest (index mod 512), then
+ * lowest index (tf_sampling_g.cu:146-163).  `temp` is the reference's 32*n float
+ * scratch; it is not needed here (the running distances live in registers) and may
+ * be NULL — the parameter is kept so the call shape matches the reference launcher.
+ * Requires m >= 1 (tf_sampling.cpp:99). */
+int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
+                             hf_stream_t stream);
+/* Tuning override for the FPS launch shape (cluster size 1/2/4/8, 0 = heuristic). */
+void hf_fps_set_cluster(int cluster);
+
+/* Replaces gatherpointLauncher(b,n,m,inp,idx,out), sampling/tf_sampling_g.cu:206.
+ * inp (b,n,3), idx (b,m) -> out (b,m,3). */
+int hf_gather_point(int b, int n, int m, const float *inp, const int *idx, float *out,
+                    hf_stream_t stream);
+
+/* ---- grouping ----------------------------------------------------------- */
+/* Replaces queryBallPointLauncher(b,n,m,radius,nsample,xyz1,xyz2,idx,pts_cnt),
+ * grouping/tf_grouping_g.cu:125.  xyz1 (b,n,3) dataset, xyz2 (b,m,3) queries ->
+ * idx (b,m,nsample), pts_cnt (b,m).  First `nsample` dataset points in index order
+ * with max(sqrtf(d2),1e-20f) < radius; remaining slots repeat the first hit.
+ * Rows with no hit are written as 0 (the reference leaves them uninitialised,
+ * tf_grouping.cpp:87-100).  Requires radius > 0, nsample > 0 (tf_grouping.cpp:71,74). */
+int hf_query_ball_point(int b, int n, int m, float radius, int nsample, const float *xyz1,
+                        const float *xyz2, int *idx, int *pts_cnt, hf_stream_t stream);
+
+/* Replaces groupPointLauncher(b,n,c,m,nsample,points,idx,out), grouping/tf_grouping_g.cu:133.
+ * points (b,n,c), idx (b,m,nsample) -> out (b,m,nsample,c). */
+int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,
+                   float *out, hf_stream_t stream);
+
+/* ---- interpolate -------------------------------------------------------- */
+/* Replaces three_nn_gpu(b,n,m,unknown,known,dist2,idx), interpolate/tf_interpolate_g.cu:68.
+ * unknown (b,n,3), known (b,m,3) -> dist2 (b,n,3) squared distances ascending,
+ * idx (b,n,3); equal distances keep the lower index.  With m < 3 the unused
+ * distances are +inf and their indices 0, as in the reference. */
+int hf_three_nn(int b, int n, int m, const float *unknown, const float *known, float *dist2,
+                int *idx, hf_stream_t stream);
+
+/* Replaces three_interpolate_gpu(b,c,m,n,points,idx,weight,out),
+ * interpolate/tf_interpolate_g.cu:112 — CHANNEL-FIRST like that launcher:
+ * points (b,c,m), idx/weight (b,n,3) -> out (b,c,n). */
+int hf_three_interpolate(int b, int c, int m, int n, const float *points, const int *idx,
+                         const float *weight, float *out, hf_stream_t stream);
+/* Channel-last form = the Python contract of interpolate/tf_interpolate.py:26-37
+ * (which wraps the launcher in two transposes; this entry makes them unnecessary):
+ * points (b,m,c), idx/weight (b,n,3) -> out (b,n,c). */
+int hf_three_interpolate_nlc(int b, int m, int c, int n, const float *points, const int *idx,
+                             const float *weight, float *out, hf_stream_t stream);
+
+/* ---- cropping ----------------------------------------------------------- */
+/* Replaces pccropandsample_gpu(...), cropping/tf_cropping_g.cu:152 together with the
+ * output memsets of its wrapper (cropping/tf_cropping.cpp:171-176): every output
+ * element is written by this call, no pre-initialisation is needed.
+ * pts (B,P,3), fts (B,P,C), intensities (B,P,IC), mask (B,P) bool, boxes (N,3,8)
+ * corners [axis][corner], box_ind (N) -> crop_pts (N,R,3), crop_fts (N,R,C),
+ * crop_intensities (N,R,IC), crop_mask (N,R) bool, crop_ind (N,R), non_empty_box (N) bool.
+ * Slot order is canonical (ascending point index, first R kept); the reference's
+ * order is an atomicInc race (tf_cropping_g.cu:85).  Requires resize > 0 and
+ * 0 <= box_ind < batch (out-of-range box_ind is the caller's error, unchecked, as in
+ * the reference). */
+int hf_pc_crop_and_sample(const float *pts, const float *fts, const float *intensities,
+                          const uint8_t *mask, const float *boxes, const int *box_ind,
+                          int num_boxes, int batch, int npts, int resize, int channel,
+                          int intensity_channel, float *crop_pts, float *crop_fts,
+                          float *crop_intensities, uint8_t *crop_mask, int *crop_ind,
+                          uint8_t *non_empty_box, hf_stream_t stream);
+
+/* ---- bev_iou ------------------------------------------------------------ */
+/* Replaces compute_bev_iou_gpu(num_a,boxes_a,num_b,boxes_b,ans_overlap,ans_iou),
+ * bev_iou/bev_iou_g.cu:308 (+ the two memsets of bev_iou.cpp:175-176).
+ * boxes (N,5) [x1,y1,x2,y2,ry] -> overlap (N,M), iou (N,M). */
+int hf_compute_bev_iou(int num_a, const float *boxes_a, int num_b, const float *boxes_b,
+                       float *ans_overlap, float *ans_iou, hf_stream_t stream);
+
+/* Replaces oriented_nms_gpu(boxes,mask,boxes_num,thresh), bev_iou/bev_iou_g.cu:317.
+ * mask is (N, ceil(N/64)) uint64, bit j of mask[i][cb] set iff iou(i, 64*cb+j) > thresh,
+ * diagonal tiles only j > i.  upper_only != 0 skips the tiles below the diagonal
+ * (written as 0) — the reference sweep never reads them (bev_iou.cpp:101-103). */
+int hf_oriented_nms_mask(const float *boxes, unsigned long long *mask, int boxes_num,
+                         float nms_overlap_thresh, int upper_only, hf_stream_t stream);
+
+/* Whole of OrientedNMSOp::Compute (bev_iou/bev_iou.cpp:54-118) on the device: mask,
+ * greedy sweep and keep[0]-padding, with no host round trip.  Boxes must be
+ * score-sorted by the caller, as in the reference (compute_iou.py:77-80).
+ * Batched over `scenes` independent box sets (the reference maps scenes with
+ * tf.map_fn, rpn_model.py:683): boxes (S,N,5) -> keep (S,N) int32, num_kept (S)
+ * (may be NULL).  Workspace: hf_oriented_nms_workspace_bytes(S,N). */
+size_t hf_oriented_nms_workspace_bytes(int scenes, int boxes_num);
+int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh,
+                    int *keep, int *num_kept, void *workspace, size_t workspace_bytes,
+                    hf_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HFOPS_H_ */

@@ -1,0 +1,249 @@
+"""numpy/ctypes bindings of the CPU oracle (oracle/hf_oracle.cpp) and of oracle/_ref.
+
+TEST INFRASTRUCTURE ONLY — see oracle/__init__.py.  Every function takes and returns
+host numpy arrays; shapes and dtypes follow the reference's Python API.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_DIR = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(_DIR, "libhf_oracle.so")
+REF_DIR = os.path.join(_DIR, "_ref")
+
+_i, _f, _p = ctypes.c_int, ctypes.c_float, ctypes.c_void_p
+
+
+def build(force=False):
+    """Compile the oracle (and oracle/_ref when /root/reference is present) via oracle/Makefile."""
+    if force or not os.path.exists(ORACLE_SO) or os.path.getmtime(ORACLE_SO) < os.path.getmtime(
+            os.path.join(_DIR, "hf_oracle.cpp")):
+        subprocess.run(["make", "-C", _DIR, "libhf_oracle.so"], check=True, stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT)
+    if os.path.isdir("/root/reference"):
+        subprocess.run(["make", "-C", _DIR, "ref"], check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    return ORACLE_SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(ORACLE_SO):
+            build()
+        _lib = ctypes.CDLL(ORACLE_SO)
+        _lib.hf_oracle_oriented_nms.restype = _i
+        _lib.hf_oracle_nms_sweep.restype = _i
+        _lib.hf_oracle_get_threads.restype = _i
+    return _lib
+
+
+def _c(a, dtype):
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(_p)
+
+
+def set_threads(n):
+    lib().hf_oracle_set_threads(_i(int(n)))
+
+
+# ---- oracle ops ------------------------------------------------------------------
+def farthest_point_sample(npoint, inp):
+    inp = _c(inp, np.float32)
+    b, n, _ = inp.shape
+    out = np.zeros((b, npoint), np.int32)
+    lib().hf_oracle_farthest_point_sample(_i(b), _i(n), _i(npoint), _ptr(inp), _ptr(out))
+    return out
+
+
+def gather_point(inp, idx):
+    inp, idx = _c(inp, np.float32), _c(idx, np.int32)
+    b, n, _ = inp.shape
+    m = idx.shape[1]
+    out = np.zeros((b, m, 3), np.float32)
+    lib().hf_oracle_gather_point(_i(b), _i(n), _i(m), _ptr(inp), _ptr(idx), _ptr(out))
+    return out
+
+
+def query_ball_point(radius, nsample, xyz1, xyz2):
+    xyz1, xyz2 = _c(xyz1, np.float32), _c(xyz2, np.float32)
+    b, n, _ = xyz1.shape
+    m = xyz2.shape[1]
+    idx = np.zeros((b, m, nsample), np.int32)
+    cnt = np.zeros((b, m), np.int32)
+    lib().hf_oracle_query_ball_point(_i(b), _i(n), _i(m), _f(radius), _i(nsample), _ptr(xyz1), _ptr(xyz2), _ptr(idx),
+                                     _ptr(cnt))
+    return idx, cnt
+
+
+def group_point(points, idx):
+    points, idx = _c(points, np.float32), _c(idx, np.int32)
+    b, n, c = points.shape
+    m, ns = idx.shape[1], idx.shape[2]
+    out = np.zeros((b, m, ns, c), np.float32)
+    lib().hf_oracle_group_point(_i(b), _i(n), _i(c), _i(m), _i(ns), _ptr(points), _ptr(idx), _ptr(out))
+    return out
+
+
+def three_nn(xyz1, xyz2):
+    xyz1, xyz2 = _c(xyz1, np.float32), _c(xyz2, np.float32)
+    b, n, _ = xyz1.shape
+    m = xyz2.shape[1]
+    dist = np.zeros((b, n, 3), np.float32)
+    idx = np.zeros((b, n, 3), np.int32)
+    lib().hf_oracle_three_nn(_i(b), _i(n), _i(m), _ptr(xyz1), _ptr(xyz2), _ptr(dist), _ptr(idx))
+    return dist, idx
+
+
+def three_interpolate(points, idx, weight):
+    points, idx, weight = _c(points, np.float32), _c(idx, np.int32), _c(weight, np.float32)
+    b, m, c = points.shape
+    n = idx.shape[1]
+    out = np.zeros((b, n, c), np.float32)
+    lib().hf_oracle_three_interpolate(_i(b), _i(m), _i(c), _i(n), _ptr(points), _ptr(idx), _ptr(weight), _ptr(out))
+    return out
+
+
+def three_interpolate_channel_first(points, idx, weight):
+    points, idx, weight = _c(points, np.float32), _c(idx, np.int32), _c(weight, np.float32)
+    b, c, m = points.shape
+    n = idx.shape[1]
+    out = np.zeros((b, c, n), np.float32)
+    lib().hf_oracle_three_interpolate_cf(_i(b), _i(c), _i(m), _i(n), _ptr(points), _ptr(idx), _ptr(weight), _ptr(out))
+    return out
+
+
+def pc_crop_and_sample(pts, fts, intensities, mask, boxes, box_ind, resize):
+    pts, fts, intensities = _c(pts, np.float32), _c(fts, np.float32), _c(intensities, np.float32)
+    mask = _c(mask, np.uint8)
+    boxes, box_ind = _c(boxes, np.float32), _c(box_ind, np.int32)
+    B, P, C = fts.shape
+    IC = intensities.shape[2]
+    N, R = boxes.shape[0], int(resize)
+    crop_pts = np.zeros((N, R, 3), np.float32)
+    crop_fts = np.zeros((N, R, C), np.float32)
+    crop_int = np.zeros((N, R, IC), np.float32)
+    crop_mask = np.zeros((N, R), np.uint8)
+    crop_ind = np.zeros((N, R), np.int32)
+    non_empty = np.zeros((N,), np.uint8)
+    lib().hf_oracle_pc_crop_and_sample(_ptr(pts), _ptr(fts), _ptr(intensities), _ptr(mask), _ptr(boxes), _ptr(box_ind),
+                                       _i(N), _i(B), _i(P), _i(R), _i(C), _i(IC), _ptr(crop_pts), _ptr(crop_fts),
+                                       _ptr(crop_int), _ptr(crop_mask), _ptr(crop_ind), _ptr(non_empty))
+    return crop_pts, crop_fts, crop_int, crop_mask.astype(bool), crop_ind, non_empty.astype(bool)
+
+
+def compute_bev_iou(proposals, gt_bboxes):
+    a, g = _c(proposals, np.float32), _c(gt_bboxes, np.float32)
+    n, m = a.shape[0], g.shape[0]
+    overlap = np.zeros((n, m), np.float32)
+    iou = np.zeros((n, m), np.float32)
+    lib().hf_oracle_compute_bev_iou(_i(n), _ptr(a), _i(m), _ptr(g), _ptr(overlap), _ptr(iou))
+    return overlap, iou
+
+
+def oriented_nms_mask(boxes, thresh):
+    boxes = _c(boxes, np.float32)
+    n = boxes.shape[0]
+    mask = np.zeros((n, (n + 63) // 64), np.uint64)
+    lib().hf_oracle_oriented_nms_mask(_ptr(boxes), _ptr(mask), _i(n), _f(thresh))
+    return mask
+
+
+def nms_sweep(mask):
+    mask = _c(mask, np.uint64)
+    n = mask.shape[0]
+    keep = np.zeros((n,), np.int32)
+    kept = lib().hf_oracle_nms_sweep(_ptr(mask), _i(n), _ptr(keep))
+    return keep, kept
+
+
+def oriented_nms(boxes, thresh, return_info=False):
+    """-> keep (N,) int32 [, (num_kept, min |iou - thresh| over evaluated pairs)]."""
+    boxes = _c(boxes, np.float32)
+    n = boxes.shape[0]
+    keep = np.zeros((n,), np.int32)
+    margin = ctypes.c_float(0)
+    kept = lib().hf_oracle_oriented_nms(_ptr(boxes), _i(n), _f(thresh), _ptr(keep), ctypes.byref(margin))
+    return (keep, (kept, float(margin.value))) if return_info else keep
+
+
+# ---- oracle/_ref: the reference's own sources, compiled where they lie --------------
+def _mangled(so, name):
+    out = subprocess.run(["nm", "-D", "--defined-only", so], check=True, stdout=subprocess.PIPE, text=True).stdout
+    for line in out.splitlines():
+        sym = line.split()[-1]
+        if sym.startswith("_Z%d%s" % (len(name), name)):
+            return sym
+    raise KeyError("%s not exported by %s" % (name, so))
+
+
+def ref_available(which):
+    return os.path.exists(os.path.join(REF_DIR, which))
+
+
+_ref_cache = {}
+
+
+def _ref(which):
+    if which not in _ref_cache:
+        _ref_cache[which] = ctypes.CDLL(os.path.join(REF_DIR, which))
+    return _ref_cache[which]
+
+
+def ref_interpolate_cpu(points, idx, weight):
+    """interpolate/interpolate.cpp:84-104 interpolate_cpu, the reference's own CPU code."""
+    so = os.path.join(REF_DIR, "libref_interpolate_cpu.so")
+    fn = getattr(_ref("libref_interpolate_cpu.so"), _mangled(so, "interpolate_cpu"))
+    points, idx, weight = _c(points, np.float32), _c(idx, np.int32), _c(weight, np.float32)
+    b, m, c = points.shape
+    n = idx.shape[1]
+    out = np.zeros((b, n, c), np.float32)
+    fn(_i(b), _i(m), _i(c), _i(n), _ptr(points), _ptr(idx), _ptr(weight), _ptr(out))
+    return out
+
+
+def ref_query_ball_point_cpu(radius, nsample, xyz1, xyz2):
+    """grouping/test/query_ball_point.cpp:19-47 (no pts_cnt output)."""
+    so = os.path.join(REF_DIR, "libref_grouping_cpu.so")
+    fn = getattr(_ref("libref_grouping_cpu.so"), _mangled(so, "query_ball_point_cpu"))
+    xyz1, xyz2 = _c(xyz1, np.float32), _c(xyz2, np.float32)
+    b, n, _ = xyz1.shape
+    m = xyz2.shape[1]
+    idx = np.zeros((b, m, nsample), np.int32)
+    fn(_i(b), _i(n), _i(m), _f(radius), _i(nsample), _ptr(xyz1), _ptr(xyz2), _ptr(idx))
+    return idx
+
+
+def ref_group_point_cpu(points, idx):
+    """grouping/test/query_ball_point.cpp:52-66."""
+    so = os.path.join(REF_DIR, "libref_grouping_cpu.so")
+    fn = getattr(_ref("libref_grouping_cpu.so"), _mangled(so, "group_point_cpu"))
+    points, idx = _c(points, np.float32), _c(idx, np.int32)
+    b, n, c = points.shape
+    m, ns = idx.shape[1], idx.shape[2]
+    out = np.zeros((b, m, ns, c), np.float32)
+    fn(_i(b), _i(n), _i(c), _i(m), _i(ns), _ptr(points), _ptr(idx), _ptr(out))
+    return out
+
+
+def ref_bev_host(boxes_a, boxes_b):
+    """bev_iou/bev_iou_g.cu:102-224 box_overlap / iou_bev compiled for the host (oracle/ref_bev_host.cu)."""
+    L = _ref("libref_bev_host.so")
+    L.ref_host_box_overlap.restype = _f
+    L.ref_host_iou_bev.restype = _f
+    a, g = _c(boxes_a, np.float32), _c(boxes_b, np.float32)
+    overlap = np.zeros((a.shape[0], g.shape[0]), np.float32)
+    iou = np.zeros_like(overlap)
+    for i in range(a.shape[0]):
+        for j in range(g.shape[0]):
+            pa, pb = _ptr(a[i]), _ptr(g[j])
+            overlap[i, j] = L.ref_host_box_overlap(pa, pb)
+            iou[i, j] = L.ref_host_iou_bev(pa, pb)
+    return overlap, iou

@@ -1,0 +1,75 @@
+"""CPU: the C-ABI library loads and exports every symbol include/hfops.h declares; the
+Python mirror validates arguments like the reference's OP_REQUIRES; no CPU fallback exists."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "hfops.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(hf_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_builds_and_exports_every_declared_symbol():
+    from heterofusionrcnn_b200 import build, _lib
+
+    path = build.build()
+    lib = ctypes.CDLL(path)
+    names = declared_symbols()
+    assert len(names) >= 15
+    for name in names:
+        assert hasattr(lib, name), "libhfops.so does not export %s" % name
+    # the ctypes table covers exactly the header
+    assert sorted(_lib.SIGNATURES) == names
+    assert b"sm_100a" in _lib.load().hf_version()
+
+
+def test_status_codes_without_a_gpu():
+    """Argument validation happens before any CUDA call, so it is testable on CPU."""
+    from heterofusionrcnn_b200 import _lib
+
+    lib = _lib.load()
+    assert lib.hf_farthest_point_sample(1, 8, 0, 1, None, 1, None) == _lib.HF_ERR_INVALID_ARG
+    assert b"positive npoint" in lib.hf_last_error()
+    assert lib.hf_query_ball_point(1, 8, 4, -1.0, 4, 1, 1, 1, 1, None) == _lib.HF_ERR_INVALID_ARG
+    assert b"positive radius" in lib.hf_last_error()
+    assert lib.hf_query_ball_point(1, 8, 4, 1.0, 0, 1, 1, 1, 1, None) == _lib.HF_ERR_INVALID_ARG
+    assert lib.hf_pc_crop_and_sample(1, 1, 1, 1, 1, 1, 1, 1, 8, 0, 4, 1, 1, 1, 1, 1, 1, 1, None) == _lib.HF_ERR_INVALID_ARG
+    assert lib.hf_oriented_nms_mask(1, 1, 4, -0.5, 0, None) == _lib.HF_ERR_INVALID_ARG
+    assert lib.hf_oriented_nms(1, 1, 100, 0.5, 1, None, None, 0, None) == _lib.HF_ERR_WORKSPACE
+    assert lib.hf_oriented_nms_workspace_bytes(16, 9000) == 16 * 9000 * 141 * 8
+    assert lib.hf_farthest_point_sample(0, 8, 4, 1, None, 1, None) == _lib.HF_OK  # empty batch: no launch
+
+
+def test_python_mirror_rejects_bad_arguments_and_cpu_tensors():
+    from heterofusionrcnn_b200 import InvalidArgumentError
+    from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample, gather_point
+    from heterofusionrcnn_b200.grouping.tf_grouping import query_ball_point
+    from heterofusionrcnn_b200.bev_iou.bev_iou import oriented_nms
+
+    x = torch.zeros(1, 8, 3)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        farthest_point_sample(4, x)
+    with pytest.raises(InvalidArgumentError, match="positive npoint"):
+        farthest_point_sample(0, x)
+    with pytest.raises(InvalidArgumentError, match="positive radius"):
+        query_ball_point(0.0, 4, x, x)
+    with pytest.raises(InvalidArgumentError, match="nms_threshold"):
+        oriented_nms(torch.zeros(4, 5), -1.0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        gather_point(x, torch.zeros(1, 4, dtype=torch.int32))
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "heterofusionrcnn_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in src.replace("no oracle", ""), "%s mentions the oracle" % f

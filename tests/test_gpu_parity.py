@@ -1,0 +1,322 @@
+"""GPU: the CUDA path (through the Python mirror -> ctypes -> C-ABI) against the CPU oracle
+and, where oracle/_ref/libref_cuda.so travelled with the tree, against the UNMODIFIED
+reference CUDA kernels running on the same B200.
+
+Bar: bit-exact for every integer / index / bool output; floats within 1e-5 relative
+(BASELINE.json north_star), and in practice bit-exact where the arithmetic order is pinned.
+"""
+import numpy as np
+import pytest
+import torch
+
+from heterofusionrcnn_b200 import synthetic
+from heterofusionrcnn_b200.bev_iou.bev_iou import compute_bev_iou, oriented_nms, oriented_nms_batch, oriented_nms_mask
+from heterofusionrcnn_b200.cropping.tf_cropping import pc_crop_and_sample
+from heterofusionrcnn_b200.grouping.tf_grouping import group_point, query_ball_point
+from heterofusionrcnn_b200.interpolate.tf_interpolate import (three_interpolate, three_interpolate_channel_first,
+                                                              three_nn)
+from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample, gather_point
+
+import _refcuda
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5  # north_star float tolerance
+
+
+def T(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def N(t):
+    return t.detach().cpu().numpy()
+
+
+def close(a, b, rtol=RTOL):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    scale = np.maximum(np.abs(a), np.abs(b))
+    return np.all(np.abs(a - b) <= rtol * scale + 1e-12)
+
+
+needs_ref = pytest.mark.skipif(not _refcuda.available(), reason="oracle/_ref/libref_cuda.so not built")
+
+
+# ---------------------------------------------------------------- FPS / gather
+@pytest.mark.parametrize("b,n,m,dup", [(2, 16384, 1024, 0), (3, 4096, 1024, 0), (2, 1024, 256, 0), (4, 256, 64, 0),
+                                       (2, 5000, 300, 0), (2, 700, 700, 0), (1, 3, 7, 0), (2, 16384, 600, 4000),
+                                       (1, 8192, 64, 8000)])
+def test_fps_matches_oracle(cuda, oracle, b, n, m, dup):
+    xyz, _ = synthetic.make_scans(11 + n + m, b, n, duplicate_pad=dup)
+    want = oracle.farthest_point_sample(m, xyz)
+    got = N(farthest_point_sample(m, T(xyz, cuda)))
+    assert got.dtype == np.int32 and got.shape == (b, m)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("cluster", [1, 2, 4, 8])
+def test_fps_every_cluster_shape(cuda, oracle, cluster):
+    from heterofusionrcnn_b200 import _lib
+
+    xyz, _ = synthetic.make_scans(5, 2, 6000, duplicate_pad=1500)
+    want = oracle.farthest_point_sample(512, xyz)
+    _lib.load().hf_fps_set_cluster(cluster)
+    try:
+        got = N(farthest_point_sample(512, T(xyz, cuda)))
+    finally:
+        _lib.load().hf_fps_set_cluster(0)
+    assert np.array_equal(got, want)
+
+
+@needs_ref
+def test_fps_matches_reference_kernel_full_size(cuda):
+    """BASELINE config 2 size, against the reference's own kernel on this GPU (ties included)."""
+    xyz, _ = synthetic.make_scans(2, 4, 16384, duplicate_pad=2000)
+    x = T(xyz, cuda)
+    assert torch.equal(farthest_point_sample(4096, x), _refcuda.fps(4096, x))
+
+
+def test_fps_65536_properties(cuda):
+    """BASELINE config 5 size (too slow for the serial oracle): size-independent properties."""
+    xyz, _ = synthetic.make_scans(9, 2, 65536)
+    x = T(xyz, cuda)
+    idx = farthest_point_sample(2048, x)
+    i = N(idx)
+    assert i[:, 0].tolist() == [0, 0] and i.min() >= 0 and i.max() < 65536
+    for s in range(2):
+        assert len(set(i[s].tolist())) == 2048  # distinct points => no repeats
+    # greedy property: the min-distance to the chosen set is non-increasing along the sequence
+    p = torch.gather(x, 1, idx.long().unsqueeze(-1).expand(-1, -1, 3))
+    for s in range(2):
+        d = torch.cdist(p[s, :512].double(), p[s, :512].double())
+        prev = torch.full((512,), float("inf"), dtype=torch.float64, device=cuda)
+        mins = []
+        for j in range(1, 512):
+            mins.append(d[j, :j].min().item())
+        assert all(mins[k] >= mins[k + 1] - 1e-6 for k in range(len(mins) - 1))
+
+
+def test_gather_point(cuda, oracle):
+    rng = np.random.default_rng(3)
+    xyz = rng.standard_normal((3, 777, 3)).astype(np.float32)
+    idx = rng.integers(0, 777, (3, 129)).astype(np.int32)
+    assert np.array_equal(N(gather_point(T(xyz, cuda), T(idx, cuda))), oracle.gather_point(xyz, idx))
+
+
+# ---------------------------------------------------------------- ball query / group
+@pytest.mark.parametrize("b,n,m,r,ns", [(2, 16384, 512, 0.8, 32), (2, 4096, 1024, 0.2, 32), (2, 1024, 256, 0.4, 32),
+                                        (3, 1001, 130, 2.0, 16), (1, 50, 7, 100.0, 64), (2, 4096, 100, 0.05, 8),
+                                        (1, 2048, 64, 4.0, 400)])
+def test_query_ball_point_matches_oracle(cuda, oracle, b, n, m, r, ns):
+    xyz, _ = synthetic.make_scans(n + m, b, n)
+    q = xyz[:, :m] if m % 2 else oracle.gather_point(xyz, oracle.farthest_point_sample(m, xyz))
+    q = np.ascontiguousarray(q)
+    widx, wcnt = oracle.query_ball_point(r, ns, xyz, q)
+    gidx, gcnt = query_ball_point(r, ns, T(xyz, cuda), T(q, cuda))
+    assert np.array_equal(N(gcnt), wcnt)
+    assert np.array_equal(N(gidx), widx)  # rows without a hit are 0 on both sides
+
+
+def test_query_ball_point_radius_edge_is_bit_exact(cuda, oracle):
+    """Points sitting exactly on / one ulp around the radius: the sqrt-free test must agree."""
+    rng = np.random.default_rng(0)
+    r = np.float32(0.3)
+    n = 4096
+    dirs = rng.standard_normal((n, 3))
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    scale = r * (1 + rng.integers(-4, 5, n) * 2.0 ** -23)
+    xyz = (dirs * scale[:, None]).astype(np.float32)[None]
+    q = np.zeros((1, 1, 3), np.float32)
+    widx, wcnt = oracle.query_ball_point(float(r), n, xyz, q)
+    gidx, gcnt = query_ball_point(float(r), n, T(xyz, cuda), T(q, cuda))
+    assert 0 < wcnt[0, 0] < n
+    assert np.array_equal(N(gcnt), wcnt) and np.array_equal(N(gidx), widx)
+
+
+@needs_ref
+def test_query_ball_point_matches_reference_kernel(cuda):
+    xyz, _ = synthetic.make_scans(21, 2, 16384)
+    x = T(xyz, cuda)
+    q = gather_point(x, farthest_point_sample(1024, x))
+    for r in (0.1, 0.8, 4.0):
+        gidx, gcnt = query_ball_point(r, 32, x, q)
+        ridx, rcnt = _refcuda.query_ball_point(r, 32, x, q)
+        assert torch.equal(gcnt, rcnt)
+        hit = rcnt > 0  # the reference leaves rows without a hit uninitialised
+        assert torch.equal(gidx[hit], ridx[hit])
+
+
+@pytest.mark.parametrize("c", [1, 3, 4, 96, 130, 256])
+def test_group_point(cuda, oracle, c):
+    rng = np.random.default_rng(c)
+    pts = rng.standard_normal((2, 500, c)).astype(np.float32)
+    idx = rng.integers(0, 500, (2, 37, 9)).astype(np.int32)
+    got = group_point(T(pts, cuda), T(idx, cuda))
+    assert got.shape == (2, 37, 9, c)
+    assert np.array_equal(N(got), oracle.group_point(pts, idx))
+
+
+# ---------------------------------------------------------------- three_nn / interpolate
+@pytest.mark.parametrize("b,n,m", [(2, 16384, 4096), (2, 4096, 1024), (3, 1024, 256), (2, 256, 64), (2, 333, 1027),
+                                   (1, 10, 2), (1, 5, 1)])
+def test_three_nn_matches_oracle(cuda, oracle, b, n, m):
+    xyz, _ = synthetic.make_scans(n * 3 + m, b, max(n, m), duplicate_pad=max(n, m) // 8)
+    unknown = np.ascontiguousarray(xyz[:, :n])
+    known = np.ascontiguousarray(xyz[:, ::-1][:, :m])
+    wd, wi = oracle.three_nn(unknown, known)
+    gd, gi = three_nn(T(unknown, cuda), T(known, cuda))
+    assert np.array_equal(N(gi), wi)
+    assert np.array_equal(N(gd), wd)  # includes the +inf of m < 3
+
+
+@needs_ref
+def test_three_nn_and_interpolate_match_reference_kernels(cuda):
+    xyz, _ = synthetic.make_scans(4, 2, 16384, duplicate_pad=1000)
+    x = T(xyz, cuda)
+    known = gather_point(x, farthest_point_sample(4096, x))
+    gd, gi = three_nn(x, known)
+    rd, ri = _refcuda.three_nn(x, known)
+    assert torch.equal(gi, ri) and torch.equal(gd, rd)
+    w = T(synthetic.fp_weights(N(gd)), cuda)
+    feats = torch.randn(2, 4096, 128, device=cuda)
+    got = three_interpolate(feats, gi, w)
+    ref = _refcuda.three_interpolate_channel_first(feats.transpose(1, 2).contiguous(), gi, w).transpose(1, 2)
+    assert torch.equal(got, ref)  # same FMA order => bit-identical, stronger than the 1e-5 bar
+    cf = three_interpolate_channel_first(feats.transpose(1, 2).contiguous(), gi, w)
+    assert torch.equal(cf.transpose(1, 2), ref)
+
+
+@pytest.mark.parametrize("c", [1, 3, 128, 132, 1024])
+def test_three_interpolate(cuda, oracle, c):
+    rng = np.random.default_rng(c)
+    pts = rng.standard_normal((2, 300, c)).astype(np.float32)
+    idx = rng.integers(0, 300, (2, 701, 3)).astype(np.int32)
+    w = rng.random((2, 701, 3)).astype(np.float32)
+    w /= w.sum(-1, keepdims=True)
+    want = oracle.three_interpolate(pts, idx, w)
+    got = N(three_interpolate(T(pts, cuda), T(idx, cuda), T(w, cuda)))
+    assert close(got, want) and np.array_equal(got, want)
+    cf = N(three_interpolate_channel_first(T(pts.transpose(0, 2, 1), cuda), T(idx, cuda), T(w, cuda)))
+    assert np.array_equal(cf.transpose(0, 2, 1), want)
+
+
+# ---------------------------------------------------------------- crop
+def crop_inputs(seed, B, P, C, nbox):
+    xyz, inten = synthetic.make_scans(seed, B, P)
+    rng = np.random.default_rng(seed)
+    fts = rng.standard_normal((B, P, C)).astype(np.float32)
+    mask = rng.random((B, P)) < 0.3
+    b3 = [synthetic.make_boxes3d(seed * 13 + i, xyz[i], nbox) for i in range(B)]
+    b3[0][:3, 3:6] *= 6.0  # a few big boxes: more than `resize` points inside
+    b3[-1][0, 0] += 500.0  # and an empty one
+    boxes = np.concatenate([synthetic.boxes3d_to_corners(x) for x in b3])
+    box_ind = np.repeat(np.arange(B, dtype=np.int32), nbox)
+    return xyz, fts, inten, mask, boxes, box_ind
+
+
+@pytest.mark.parametrize("C,R", [(288, 512), (7, 64), (4, 16)])
+def test_crop_matches_oracle(cuda, oracle, C, R):
+    args = crop_inputs(5 + C, 2, 16384, C, 40)
+    want = oracle.pc_crop_and_sample(*args, R)
+    got = pc_crop_and_sample(*[T(a, cuda) for a in args], R)
+    names = ["crop_pts", "crop_fts", "crop_intensities", "crop_mask", "crop_ind", "non_empty_box"]
+    assert not want[5].all() and want[5].any()
+    for name, g, w in zip(names, got, want):
+        assert N(g).shape == w.shape, name
+        assert np.array_equal(N(g), w), name
+
+
+@needs_ref
+def test_crop_agrees_with_reference_kernel_up_to_its_race(cuda):
+    """The reference assigns slots with a racing atomicInc: compare what is race-free
+    (which boxes are empty, and the SET of cropped points when fewer than R are inside)."""
+    args = [T(a, cuda) for a in crop_inputs(77, 2, 16384, 16, 64)]
+    R = 512
+    got = pc_crop_and_sample(*args, R)
+    ref = _refcuda.pc_crop_and_sample(*args, R)
+    assert torch.equal(got[5], ref[5])
+    gi, ri = N(got[4]), N(ref[4])
+    checked = 0
+    for b in range(gi.shape[0]):
+        u = np.unique(gi[b])
+        if N(got[5])[b] and len(u) < R:
+            assert np.array_equal(u, np.unique(ri[b]))
+            checked += 1
+    assert checked > 20
+
+
+# ---------------------------------------------------------------- BEV IoU / NMS
+def test_bev_iou_known_answers_and_oracle(cuda, oracle):
+    a = np.array([[0, 0, 1, 1, 0], [2, 2, 3, 3, 0]], np.float32)
+    g = np.array([[0, 0, 1, 1, 0], [2, 2, 4, 4, 0], [5, 5, 6, 6, 0]], np.float32)
+    ov, iou = compute_bev_iou(T(a, cuda), T(g, cuda))  # demo of bev_iou/bev_iou.py:47-57
+    assert np.array_equal(N(ov), [[1, 0, 0], [0, 1, 0]]) and np.array_equal(N(iou), [[1, 0, 0], [0, 0.25, 0]])
+    boxes = synthetic.make_nms_boxes(3, 700, clusters=6)
+    wo, wi = oracle.compute_bev_iou(boxes[:300], boxes[300:])
+    go, gi = compute_bev_iou(T(boxes[:300], cuda), T(boxes[300:], cuda))
+    assert (wo > 0).mean() > 0.05
+    # libdevice vs glibc sin/cos/atan2 differ in the last ulps: float tolerance, and exact zeros agree
+    assert np.allclose(N(go), wo, rtol=1e-4, atol=1e-5) and np.allclose(N(gi), wi, rtol=1e-4, atol=1e-5)
+    assert np.array_equal(N(go) == 0, wo == 0)
+
+
+@needs_ref
+def test_bev_iou_matches_reference_kernel(cuda):
+    boxes = T(synthetic.make_nms_boxes(8, 2000, clusters=10), cuda)
+    go, gi = compute_bev_iou(boxes[:1000], boxes[1000:])
+    ro, ri = _refcuda.compute_bev_iou(boxes[:1000], boxes[1000:])
+    assert torch.equal(go == 0, ro == 0)
+    assert torch.allclose(go, ro, rtol=RTOL, atol=1e-6) and torch.allclose(gi, ri, rtol=RTOL, atol=1e-6)
+
+
+@pytest.mark.parametrize("n,thresh,clusters", [(3, 0.5, 1), (64, 0.5, 2), (65, 0.3, 2), (1000, 0.7, 8),
+                                               (2500, 0.01, 12), (2500, 0.85, 12)])
+def test_oriented_nms_matches_oracle(cuda, oracle, n, thresh, clusters):
+    if n == 3:
+        boxes = np.array([[0, 0, 1, 1, 0], [2, 2, 3, 3, 0], [0, 0, 0.75, 0.75, 0]], np.float32)  # bev_iou.py:59-62
+    else:
+        boxes = synthetic.make_nms_boxes(n, n, clusters)
+    want, (kept, margin) = oracle.oriented_nms(boxes, thresh, return_info=True)
+    keep, num = oriented_nms_batch(T(boxes, cuda)[None], thresh, return_num_kept=True)
+    assert margin > 1e-5, "test input has a pair within 1e-5 of the threshold (SURVEY A.7)"
+    assert int(num[0]) == kept
+    assert np.array_equal(N(keep[0]), want)
+    assert np.array_equal(N(oriented_nms(T(boxes, cuda), thresh)), want)
+    if n == 3:
+        assert want.tolist() == [0, 1, 0]
+
+
+def test_oriented_nms_mask_matches_oracle_and_sweep(cuda, oracle):
+    boxes = synthetic.make_nms_boxes(12, 900, 5)
+    wmask = oracle.oriented_nms_mask(boxes, 0.6)
+    full = N(oriented_nms_mask(T(boxes, cuda), 0.6)).view(np.uint64)
+    assert np.array_equal(full, wmask)
+    upper = N(oriented_nms_mask(T(boxes, cuda), 0.6, upper_only=True)).view(np.uint64)
+    cb = (900 + 63) // 64
+    for i in range(900):
+        assert np.array_equal(upper[i, i // 64:], wmask[i, i // 64:]) and not upper[i, : i // 64].any()
+    keep, _ = oracle.nms_sweep(upper)
+    assert np.array_equal(keep, oracle.oriented_nms(boxes, 0.6))
+
+
+@needs_ref
+def test_nms_matches_reference_kernel_full_size(cuda, oracle):
+    """BASELINE config 4: 9000 boxes; reference mask kernel + the reference's host sweep."""
+    boxes = np.stack([synthetic.make_nms_boxes(100 + s, 9000) for s in range(2)])
+    keep, num = oriented_nms_batch(T(boxes, cuda), 0.85, return_num_kept=True)
+    for s in range(2):
+        rmask = N(_refcuda.nms_mask(T(boxes[s], cuda), 0.85)).view(np.uint64)
+        want, kept = oracle.nms_sweep(rmask)
+        assert int(num[s]) == kept and np.array_equal(N(keep[s]), want)
+
+
+def test_nms_full_size_properties(cuda):
+    boxes = T(synthetic.make_nms_boxes(55, 9000), cuda)
+    keep, num = oriented_nms_batch(boxes[None], 0.8, return_num_kept=True)
+    k = int(num[0])
+    kept = keep[0, :k].long()
+    assert k > 0 and torch.all(kept[1:] > kept[:-1]) and torch.all(keep[0, k:] == keep[0, 0])
+    _, iou = compute_bev_iou(boxes[kept], boxes[kept])
+    iou.fill_diagonal_(0)
+    assert float(iou.max()) <= 0.8  # no two survivors overlap more than the threshold
+    # idempotence: NMS of the survivors keeps them all
+    again, num2 = oriented_nms_batch(boxes[kept][None], 0.8, return_num_kept=True)
+    assert int(num2[0]) == k
