@@ -192,13 +192,13 @@ extern "C" int hf_pc_crop_and_sample(const float *pts, const float *fts, const f
     cudaStream_t s = (cudaStream_t)stream;
     if (vec) {
         auto kern = crop_kernel<true>;
-        if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
                                                    intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask,
                                                    crop_ind, non_empty_box);
     } else {
         auto kern = crop_kernel<false>;
-        if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
                                                    intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask,
                                                    crop_ind, non_empty_box);

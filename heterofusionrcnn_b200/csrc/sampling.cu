@@ -257,7 +257,7 @@ template <int CLUSTER, int THREADS, int PTS>
 int launch_fps(int b, int n, int m, const float *inp, int *out, cudaStream_t stream) {
     auto kern = fps_cluster_kernel<CLUSTER, THREADS, PTS>;
     size_t smem = (size_t)3 * THREADS * PTS * sizeof(float);
-    if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)b * CLUSTER);
     cfg.blockDim = dim3(THREADS);

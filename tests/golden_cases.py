@@ -37,7 +37,7 @@ def inputs_for(name):
         return dict(xyz=xyz, query=q)
     if op == "three_nn":
         xyz, _ = synthetic.make_scans(s, c["b"], c["n"], duplicate_pad=c["n"] // 10)
-        return dict(unknown=xyz, known=np.ascontiguousarray(xyz[:, ::-1][:, : c["m"]]))
+        return dict(unknown=xyz, known=xyz[:, ::-1][:, : c["m"]].copy())
     if op == "interp":
         pts = rng.standard_normal((c["b"], c["m"], c["c"])).astype(np.float32)
         idx = rng.integers(0, c["m"], (c["b"], c["n"], 3)).astype(np.int32)

@@ -160,7 +160,7 @@ def test_group_point(cuda, oracle, c):
 def test_three_nn_matches_oracle(cuda, oracle, b, n, m):
     xyz, _ = synthetic.make_scans(n * 3 + m, b, max(n, m), duplicate_pad=max(n, m) // 8)
     unknown = np.ascontiguousarray(xyz[:, :n])
-    known = np.ascontiguousarray(xyz[:, ::-1][:, :m])
+    known = xyz[:, ::-1][:, :m].copy()
     wd, wi = oracle.three_nn(unknown, known)
     gd, gi = three_nn(T(unknown, cuda), T(known, cuda))
     assert np.array_equal(N(gi), wi)
@@ -274,9 +274,13 @@ def test_oriented_nms_matches_oracle(cuda, oracle, n, thresh, clusters):
         boxes = np.array([[0, 0, 1, 1, 0], [2, 2, 3, 3, 0], [0, 0, 0.75, 0.75, 0]], np.float32)  # bev_iou.py:59-62
     else:
         boxes = synthetic.make_nms_boxes(n, n, clusters)
-    want, (kept, margin) = oracle.oriented_nms(boxes, thresh, return_info=True)
+    for _ in range(8):  # keep-list equality is only defined away from the threshold
+        want, (kept, margin) = oracle.oriented_nms(boxes, thresh, return_info=True)
+        if margin > 1e-5:
+            break
+        thresh += 0.00137
+    assert margin > 1e-5, "test input has a pair within 1e-5 of the threshold"
     keep, num = oriented_nms_batch(T(boxes, cuda)[None], thresh, return_num_kept=True)
-    assert margin > 1e-5, "test input has a pair within 1e-5 of the threshold (SURVEY A.7)"
     assert int(num[0]) == kept
     assert np.array_equal(N(keep[0]), want)
     assert np.array_equal(N(oriented_nms(T(boxes, cuda), thresh)), want)
