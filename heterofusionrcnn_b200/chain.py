@@ -90,19 +90,71 @@ def to_device(host, device, pin=False):
     return out
 
 
-def run_chain(dev, cfg):
-    """Run the chain on device-resident inputs `dev` (see make_host_inputs).  Returns a dict of results."""
+def to_pinned(host):
+    """numpy inputs -> pinned host torch tensors (the host buffers a caller of the op API holds)."""
+    def pin(a):
+        return None if a is None else torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    return {k: [pin(x) for x in v] if isinstance(v, list) else pin(v) for k, v in host.items()}
+
+
+def to_device_from_pinned(pinned, device):
+    """One asynchronous host->device copy per input tensor on the current stream."""
+    def up(t):
+        return None if t is None else t.to(device, non_blocking=True)
+    return {k: [up(x) for x in v] if isinstance(v, list) else up(v) for k, v in pinned.items()}
+
+
+def host_results(res, cfg):
+    """The results of one chain pass that leave the device in the reference pipeline: index
+    outputs the host consumes (proposal keep lists, sampled indices, counts, empty-box flags).
+    Grouped / interpolated / cropped feature tensors feed the next network layer on the GPU."""
+    outs = list(res["fps_idx"]) + [res["sa%d" % (l + 1)][1] for l in range(4)]
+    if cfg.with_nms:
+        outs += [res["nms_keep"].contiguous(), res["nms_num"]]
+    if cfg.with_crop:
+        outs.append(res["crop"][5])
+    return outs
+
+
+class _NoProbe:
+    """Default probe: does nothing.  bench.py passes one that brackets each op with CUDA events."""
+
+    def __call__(self, name, **meta):
+        return self
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+
+def run_chain(dev, cfg, probe=None):
+    """Run the chain on device-resident inputs `dev` (see make_host_inputs).  Returns a dict of results.
+
+    `probe(name, **shape)` (optional) must return a context manager; every libhfops launch runs
+    inside one, named after its kernel family, with the shape figures its algorithmic
+    bytes / flops are computed from.
+    """
+    probe = probe or _NoProbe()
     res = {}
     xyz = [dev["xyz"]]
     fps_idx = []
     feats = [dev["intensity"]] + list(dev["sa_feats"][1:])
+    b = dev["xyz"].shape[0]
     # ---- set abstraction ----
     for l in range(4):
-        idx = farthest_point_sample(cfg.npoint[l], xyz[l])
-        new_xyz = gather_point(xyz[l], idx)
-        gidx, cnt = query_ball_point(cfg.radius[l], cfg.nsample, xyz[l], new_xyz)
-        gxyz = group_point(xyz[l], gidx)
-        gfeat = group_point(feats[l], gidx)
+        n, m, ns = xyz[l].shape[1], cfg.npoint[l], cfg.nsample
+        with probe("fps", level=l + 1, b=b, n=n, m=m):
+            idx = farthest_point_sample(m, xyz[l])
+        with probe("gather_point", level=l + 1, b=b, n=n, m=m):
+            new_xyz = gather_point(xyz[l], idx)
+        with probe("query_ball_point", level=l + 1, b=b, n=n, m=m, ns=ns):
+            gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz)
+        with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
+            gxyz = group_point(xyz[l], gidx)
+        with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
+            gfeat = group_point(feats[l], gidx)
         fps_idx.append(idx)
         xyz.append(new_xyz)
         res["sa%d" % (l + 1)] = (gidx, cnt, gxyz, gfeat)
@@ -111,16 +163,24 @@ def run_chain(dev, cfg):
     # ---- feature propagation, coarse to fine ----
     for j in range(4):
         unknown, known = xyz[3 - j], xyz[4 - j]
-        dist, idx = three_nn(unknown, known)
-        dist = torch.clamp_min(dist, 1e-10)  # pointnet_util.py:304-307
-        inv = 1.0 / dist
-        w = inv / inv.sum(dim=2, keepdim=True)
-        res["fp%d" % (4 - j)] = (dist, idx, three_interpolate(dev["fp_feats"][j], idx, w))
+        n, m, c = unknown.shape[1], known.shape[1], dev["fp_feats"][j].shape[2]
+        with probe("three_nn", level=4 - j, b=b, n=n, m=m):
+            dist, idx = three_nn(unknown, known)
+        with probe("fp_weights_torch", level=4 - j, b=b, n=n):
+            dist = torch.clamp_min(dist, 1e-10)  # pointnet_util.py:304-307
+            inv = 1.0 / dist
+            w = inv / inv.sum(dim=2, keepdim=True)
+        with probe("three_interpolate", level=4 - j, b=b, n=n, m=m, c=c):
+            out = three_interpolate(dev["fp_feats"][j], idx, w)
+        res["fp%d" % (4 - j)] = (dist, idx, out)
     if cfg.with_crop:
-        res["crop"] = pc_crop_and_sample(dev["xyz"], dev["crop_fts"], dev["intensity"], dev["fg_mask"],
-                                         dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
+        with probe("pc_crop_and_sample", b=b, p=cfg.points, c=cfg.crop_channels, nb=dev["crop_boxes"].shape[0],
+                   r=cfg.crop_resize):
+            res["crop"] = pc_crop_and_sample(dev["xyz"], dev["crop_fts"], dev["intensity"], dev["fg_mask"],
+                                             dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
     if cfg.with_nms:
-        keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
+        with probe("oriented_nms", b=b, nb=cfg.nms_boxes):
+            keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
         res["nms_keep"] = keep[:, : cfg.post_nms]
         res["nms_num"] = num
     return res

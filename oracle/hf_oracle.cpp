@@ -24,6 +24,7 @@
 // CPU baseline.
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -36,7 +37,8 @@ namespace {
 
 int g_threads = 1;
 
-// parallel_for over [0,count): static contiguous chunks, one std::thread each.
+// parallel_for over [0,count): g_threads std::threads pulling contiguous chunks off an
+// atomic cursor (dynamic, so triangular workloads such as the NMS mask stay balanced).
 void parallel_for(int64_t count, const std::function<void(int64_t, int64_t)> &fn) {
     int nt = g_threads;
     if (nt <= 1 || count <= 1) {
@@ -44,11 +46,18 @@ void parallel_for(int64_t count, const std::function<void(int64_t, int64_t)> &fn
         return;
     }
     if (nt > count) nt = (int)count;
+    const int64_t chunk = std::max<int64_t>(1, count / ((int64_t)nt * 16));
+    std::atomic<int64_t> cursor{0};
     std::vector<std::thread> pool;
     pool.reserve(nt);
     for (int t = 0; t < nt; ++t) {
-        int64_t lo = count * t / nt, hi = count * (t + 1) / nt;
-        pool.emplace_back([=, &fn] { fn(lo, hi); });
+        pool.emplace_back([&fn, &cursor, chunk, count] {
+            for (;;) {
+                int64_t lo = cursor.fetch_add(chunk, std::memory_order_relaxed);
+                if (lo >= count) break;
+                fn(lo, std::min(count, lo + chunk));
+            }
+        });
     }
     for (auto &th : pool) th.join();
 }
