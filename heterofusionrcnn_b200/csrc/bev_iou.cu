@@ -16,7 +16,8 @@
 //     others, bev_iou.cpp:101-103); suppression bits are assembled with shared-memory
 //     atomicOr; the greedy sweep runs on the device, one CTA per scene, 64 boxes per step
 //     (a register-resident serial resolve of the diagonal word + a parallel OR of the kept
-//     rows), so there is no 10 MB mask D2H copy, no host loop and no H2D copy.
+//     rows), so there is no 10 MB mask D2H copy, no host loop and no H2D copy;
+//   * the fused NMS entry (hf_oriented_nms) goes further — see "Fused NMS path" below.
 // The clip itself follows the reference's arithmetic step by step (same candidate order,
 // same strict/non-strict comparisons, same stable angular ordering, same fan), because
 // the NMS keep list is a bit-exact output and depends on every comparison.
@@ -99,7 +100,7 @@ __device__ __forceinline__ bool in_box(const float *B, float px, float py) {
 }
 
 // box_overlap (:102-206) on precomputed boxes.
-__device__ float overlap_pre(const float *A, const float *B) {
+__device__ __forceinline__ float overlap_pre(const float *A, const float *B) {
     float ptx[24], pty[24], ang[24];
     int cnt = 0;
     float sx = 0.f, sy = 0.f;
@@ -244,25 +245,264 @@ __global__ void __launch_bounds__(kBevThreads)
     if (t < row_size) sm[(size_t)(row_start * kTile + t) * cb + col_start] = smask[t];
 }
 
-// ---- greedy sweep -----------------------------------------------------------------
-// One CTA per scene.  bev_iou.cpp:87-112.
-constexpr int kSweepThreads = 256;
-__global__ void __launch_bounds__(kSweepThreads)
-    nms_sweep_kernel(int boxes_num, const unsigned long long *__restrict__ mask, int *__restrict__ keep,
-                     int *__restrict__ num_kept) {
+// ===================================================================================
+// Fused NMS path (hf_oriented_nms): prepare -> filter -> clip -> sweep.
+//
+// The 64x64-tile kernel above spends its time in the polygon clip of every pair whose
+// bounding circles touch (7% of the pairs of a 9000-proposal scene).  For the
+// *thresholded* question "iou > thresh" far fewer pairs need the exact clip:
+//   prepare  one thread per box: the per-box record of precompute_box (sin/cos, rotated
+//            corners, padded radius) + a compact 8-float "lite" record, written once per
+//            scene instead of once per tile;
+//   filter   per (row tile, chunk of column tiles): stage 1 bounding circles (column box in
+//            registers, row boxes broadcast from shared memory, warp-private ballot
+//            compaction, no atomics); stage 2 a separating-axis UPPER BOUND on the overlap
+//            (intersection is contained in A cut by B's extent along A's axes and vice
+//            versa) turned into an upper bound on the IoU — pairs whose bound is safely
+//            below the threshold have bit 0 without clipping.  Survivors are appended to a
+//            global pair list (one atomicAdd per CTA flush);
+//   clip     one thread per surviving pair, full warps, both records in registers; exact
+//            reference arithmetic (overlap_pre); atomicOr of the suppression bit;
+//   sweep    see nms_sweep_kernel2.
+// The bound only ever removes pairs whose exact IoU is below the threshold by a margin
+// (1e-3 relative + float slack), so the mask — and the keep list — are unchanged.
+// ===================================================================================
+constexpr int kRec = 24;    // full record: kPre floats + hx, hy, area, pad (96 B, float4 aligned)
+constexpr int kLite = 8;    // cx, cy, radius, hx, hy, cos, sin, area
+constexpr int kLitePad = 9; // shared-memory row stride (conflict-free for 32 consecutive boxes)
+constexpr int kChunk = 8;   // column tiles per filter CTA
+constexpr int kList2Cap = 8192;
+
+__global__ void __launch_bounds__(256)
+    nms_prepare_kernel(long long total, const float *__restrict__ boxes, float *__restrict__ rec,
+                       float *__restrict__ lite) {
+    long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total) return;
+    float pre[kRec];
+    precompute_box(boxes + g * 5, pre);
+    float hx = (pre[2] - pre[0]) * 0.5f, hy = (pre[3] - pre[1]) * 0.5f;
+    pre[20] = hx;
+    pre[21] = hy;
+    pre[22] = (pre[2] - pre[0]) * (pre[3] - pre[1]);
+    pre[23] = 0.f;
+    float4 *o = reinterpret_cast<float4 *>(rec + g * kRec);
+#pragma unroll
+    for (int k = 0; k < kRec / 4; ++k) o[k] = make_float4(pre[4 * k], pre[4 * k + 1], pre[4 * k + 2], pre[4 * k + 3]);
+    float4 *l = reinterpret_cast<float4 *>(lite + g * kLite);
+    l[0] = make_float4(pre[5], pre[6], pre[19], hx);
+    l[1] = make_float4(hy, pre[7], pre[8], pre[22]);
+}
+
+// Separating-axis upper bound.  A, B: lite records.  true = the exact test iou > thresh is
+// certainly false (overlap bound too small), so the pair needs no clip.
+__device__ __forceinline__ bool sat_rejects(const float *A, const float *B, float tq) {
+    const float acx = A[0], acy = A[1], ahx = A[3], ahy = A[4], aca = A[5], asa = A[6], aar = A[7];
+    const float bcx = B[0], bcy = B[1], bhx = B[3], bhy = B[4], bca = B[5], bsa = B[6], bar = B[7];
+    if (!(ahx > 0.f && ahy > 0.f && bhx > 0.f && bhy > 0.f)) return false;  // degenerate input: always clip
+    const float dx = bcx - acx, dy = bcy - acy;
+    const float cd = fabsf(aca * bca + asa * bsa), sd = fabsf(asa * bca - aca * bsa);
+    // slack: float error of the projections (coordinates ~1e2 m -> ~1e-5) + the 1e-5 inclusion margin
+    const float m = 1e-4f + 4e-6f * (fabsf(acx) + fabsf(acy) + fabsf(bcx) + fabsf(bcy) + A[2] + B[2]);
+    // in A's frame: local x axis = (cos,-sin), local y axis = (sin,cos)  (rotate_around_center, :92-96)
+    float du = dx * aca - dy * asa, dv = dx * asa + dy * aca;
+    float eu = bhx * cd + bhy * sd + m, ev = bhx * sd + bhy * cd + m;
+    float ou = fminf(ahx, du + eu) - fmaxf(-ahx, du - eu);
+    float ov = fminf(ahy, dv + ev) - fmaxf(-ahy, dv - ev);
+    if (ou <= 0.f || ov <= 0.f) return true;  // separated along one of A's axes: overlap is exactly 0
+    // in B's frame
+    float du2 = -(dx * bca - dy * bsa), dv2 = -(dx * bsa + dy * bca);
+    float eu2 = ahx * cd + ahy * sd + m, ev2 = ahx * sd + ahy * cd + m;
+    float ou2 = fminf(bhx, du2 + eu2) - fmaxf(-bhx, du2 - eu2);
+    float ov2 = fminf(bhy, dv2 + ev2) - fmaxf(-bhy, dv2 - ev2);
+    if (ou2 <= 0.f || ov2 <= 0.f) return true;
+    if (!(tq > 0.f)) return false;
+    float ub = fminf(fminf(ou * ov, ou2 * ov2), fminf(aar, bar) * 1.00001f + m);
+    float denom = aar + bar - ub;
+    if (!(denom > 0.f)) return false;
+    return ub < tq * denom;  // iou <= ub/denom < tq <= thresh - margin
+}
+
+// Exact test of one pair on full records held in registers; sets the mask bit.
+__device__ __forceinline__ void clip_pair(const float *__restrict__ rec, unsigned long long *__restrict__ mask,
+                                          int cb, int row, int col, float thresh) {
+    float a[kRec], b[kRec];
+    const float4 *pa = reinterpret_cast<const float4 *>(rec + (size_t)row * kRec);
+    const float4 *pb = reinterpret_cast<const float4 *>(rec + (size_t)col * kRec);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {  // floats 0..19 are all the clip reads
+        float4 va = __ldg(pa + k), vb = __ldg(pb + k);
+        a[4 * k] = va.x; a[4 * k + 1] = va.y; a[4 * k + 2] = va.z; a[4 * k + 3] = va.w;
+        b[4 * k] = vb.x; b[4 * k + 1] = vb.y; b[4 * k + 2] = vb.z; b[4 * k + 3] = vb.w;
+    }
+    float s = overlap_pre(a, b);
+    if (iou_from_overlap(a, b, s) > thresh) atomicOr(&mask[(size_t)row * cb + (col >> 6)], 1ull << (col & 63));
+}
+
+__device__ __noinline__ void clip_pair_overflow(const float *rec, unsigned long long *mask, int cb, int row, int col,
+                                                float thresh) {
+    clip_pair(rec, mask, cb, row, col, thresh);
+}
+
+struct NmsLists {
+    unsigned long long *pairs;  // [cap] (scene << 48) | (row << 24) | col
+    unsigned long long *count;  // pairs appended so far (may exceed cap: the excess was clipped inline)
+    unsigned long long cap;
+};
+
+// grid = (ceil(cb/kChunk), cb, scenes); CTA (chunk, rb) handles row tile rb against column tiles
+// ct in [max(rb, chunk*kChunk), (chunk+1)*kChunk).
+__global__ void __launch_bounds__(256, 4)
+    nms_filter_kernel(int boxes_num, float thresh, const float *__restrict__ rec_all, const float *__restrict__ lite_all,
+                      unsigned long long *__restrict__ mask_all, NmsLists lists) {
+    __shared__ float rowl[kTile * kLitePad];
+    __shared__ float coll[kTile * kLitePad];
+    __shared__ unsigned short list1[8][512];
+    __shared__ unsigned int list2[kList2Cap];
+    __shared__ int n2s;
+    __shared__ unsigned long long flush_base;
+
+    const int cb = (boxes_num + kTile - 1) / kTile;
+    const int rb = blockIdx.y, scene = blockIdx.z;
+    const int ct_lo = max(rb, (int)blockIdx.x * kChunk), ct_hi = min(cb, ((int)blockIdx.x + 1) * kChunk);
+    if (ct_lo >= ct_hi) return;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const float *lite = lite_all + (size_t)scene * boxes_num * kLite;
+    const float *rec = rec_all + (size_t)scene * boxes_num * kRec;
+    unsigned long long *mask = mask_all + (size_t)scene * boxes_num * cb;
+    const int row_size = min(boxes_num - rb * kTile, kTile);
+    const float tq = thresh * (1.f - 1e-3f) - 1e-6f;
+
+    if (t == 0) n2s = 0;
+    for (int w = t; w < kTile * kLite; w += 256) {
+        int bx = w >> 3, f = w & 7;
+        rowl[bx * kLitePad + f] = bx < row_size ? lite[(size_t)(rb * kTile) * kLite + w] : 0.f;
+    }
+
+    auto flush = [&]() {  // all threads; list2[0..n2s) -> global pair list (or clipped here when it is full)
+        __syncthreads();
+        const int n2 = n2s;
+        if (n2 > 0) {
+            if (t == 0) flush_base = atomicAdd(lists.count, (unsigned long long)n2);
+            __syncthreads();
+            const unsigned long long base = flush_base;
+            for (int q = t; q < n2; q += 256) {
+                unsigned int e = list2[q];
+                int row = rb * kTile + (int)(e & 63u), col = (int)(e >> 6);
+                if (base + q < lists.cap)
+                    lists.pairs[base + q] = ((unsigned long long)scene << 48) | ((unsigned long long)row << 24) | (unsigned)col;
+                else
+                    clip_pair_overflow(rec, mask, cb, row, col, thresh);
+            }
+        }
+        __syncthreads();
+        if (t == 0) n2s = 0;
+        __syncthreads();
+    };
+
+    for (int ct = ct_lo; ct < ct_hi; ++ct) {
+        const int col_size = min(boxes_num - ct * kTile, kTile);
+        __syncthreads();  // previous tile's readers of coll are done
+        for (int w = t; w < kTile * kLite; w += 256) {
+            int bx = w >> 3, f = w & 7;
+            coll[bx * kLitePad + f] = bx < col_size ? lite[(size_t)(ct * kTile) * kLite + w] : 0.f;
+        }
+        __syncthreads();
+        // ---- stage 1: bounding circles.  warp w: columns 32*(w&1)+lane, rows 16*(w>>1) .. +16
+        const int j = 32 * (warp & 1) + lane;
+        const float jcx = coll[j * kLitePad], jcy = coll[j * kLitePad + 1], jr = coll[j * kLitePad + 2];
+        const bool jvalid = j < col_size;
+        const bool diag = ct == rb;
+        int cnt1 = 0;
+        unsigned short *mine = list1[warp];
+#pragma unroll 4
+        for (int k = 0; k < 16; ++k) {
+            const int i = 16 * (warp >> 1) + k;
+            const float dx = rowl[i * kLitePad] - jcx, dy = rowl[i * kLitePad + 1] - jcy, rr = rowl[i * kLitePad + 2] + jr;
+            bool live = jvalid && i < row_size && (!diag || j > i) && !(dx * dx + dy * dy > rr * rr);
+            unsigned bal = __ballot_sync(0xffffffffu, live);
+            if (live) mine[cnt1 + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)((i << 6) | j);
+            cnt1 += __popc(bal);
+        }
+        __syncwarp();
+        // ---- stage 2: separating-axis bound on this warp's survivors
+        for (int q0 = 0; q0 < cnt1; q0 += 32) {
+            const int q = q0 + lane;
+            bool pass = false;
+            unsigned int entry = 0;
+            if (q < cnt1) {
+                const int e = mine[q], i = e >> 6, jj = e & 63;
+                pass = !sat_rejects(rowl + i * kLitePad, coll + jj * kLitePad, tq);
+                entry = (unsigned)i | ((unsigned)(ct * kTile + jj) << 6);
+            }
+            unsigned bal = __ballot_sync(0xffffffffu, pass);
+            if (bal) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&n2s, __popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (pass) list2[base + __popc(bal & ((1u << lane) - 1u))] = entry;
+            }
+        }
+        // a tile adds at most 4096 entries: flush when the next one might not fit
+        __syncthreads();
+        if (n2s > kList2Cap - kTile * kTile) flush();
+    }
+    flush();
+}
+
+// One thread per listed pair (grid-stride over the list).
+__global__ void __launch_bounds__(256)
+    nms_clip_kernel(int boxes_num, float thresh, const float *__restrict__ rec_all,
+                    unsigned long long *__restrict__ mask_all, NmsLists lists) {
+    const int cb = (boxes_num + kTile - 1) / kTile;
+    unsigned long long n = *lists.count;
+    if (n > lists.cap) n = lists.cap;
+    for (unsigned long long q = (unsigned long long)blockIdx.x * 256 + threadIdx.x; q < n;
+         q += (unsigned long long)gridDim.x * 256) {
+        unsigned long long e = lists.pairs[q];
+        int scene = (int)(e >> 48), row = (int)((e >> 24) & 0xFFFFFFull), col = (int)(e & 0xFFFFFFull);
+        clip_pair(rec_all + (size_t)scene * boxes_num * kRec, mask_all + (size_t)scene * boxes_num * cb, cb, row, col, thresh);
+    }
+}
+
+// Greedy sweep, one 1024-thread CTA per scene (bev_iou.cpp:87-112).  Per block of 64 boxes:
+// thread 0 resolves the diagonal word serially in registers; the rows of the block (all
+// column words to the right) were loaded by all threads BEFORE the resolve (64 rows x 16
+// column lanes, 8 words in flight per thread), so once the kept bits are known the kept
+// rows are OR-reduced (redux.or per warp, then one shared atomicOr) into the removal
+// words without waiting for memory again.
+constexpr int kSweep2Threads = 1024;
+constexpr int kSweepInflight = 8;
+__global__ void __launch_bounds__(kSweep2Threads)
+    nms_sweep_kernel2(int boxes_num, const unsigned long long *__restrict__ mask, int *__restrict__ keep,
+                      int *__restrict__ num_kept) {
     extern __shared__ unsigned long long remv[];  // [cb]
     __shared__ unsigned long long sdiag[kTile];
     __shared__ unsigned long long skeep;
     const int cb = (boxes_num + kTile - 1) / kTile;
-    const int scene = blockIdx.x, t = threadIdx.x;
+    const int scene = blockIdx.x, t = threadIdx.x, lane = t & 31;
+    const int r = t & 63, g = t >> 6;  // row of the block, column lane (16 of them)
     const unsigned long long *sm = mask + (size_t)scene * boxes_num * cb;
     int *kp = keep + (size_t)scene * boxes_num;
-    for (int c = t; c < cb; c += kSweepThreads) remv[c] = 0ull;
+    for (int c = t; c < cb; c += kSweep2Threads) remv[c] = 0ull;
     int kept = 0;
+    unsigned long long dnext = (t < kTile && t < boxes_num) ? sm[(size_t)t * cb] : 0ull;
     __syncthreads();
     for (int nb = 0; nb < cb; ++nb) {
         const int size = min(boxes_num - nb * kTile, kTile);
-        if (t < kTile) sdiag[t] = t < size ? sm[(size_t)(nb * kTile + t) * cb + nb] : 0ull;
+        const bool rvalid = r < size;
+        const unsigned long long *rowp = sm + (size_t)(nb * kTile + r) * cb;
+        if (t < kTile) sdiag[t] = dnext;
+        // first wave of this block's row words, issued before the resolve
+        unsigned long long w[kSweepInflight];
+#pragma unroll
+        for (int k = 0; k < kSweepInflight; ++k) {
+            int c = nb + 1 + g + 16 * k;
+            w[k] = (rvalid && c < cb) ? rowp[c] : 0ull;
+        }
+        if (t < kTile && nb + 1 < cb) {
+            int row = (nb + 1) * kTile + t;
+            dnext = row < boxes_num ? sm[(size_t)row * cb + nb + 1] : 0ull;
+        }
         __syncthreads();
         if (t == 0) {
             unsigned long long d[kTile];
@@ -281,25 +521,32 @@ __global__ void __launch_bounds__(kSweepThreads)
         }
         __syncthreads();
         const unsigned long long kb = skeep;
-        // kept indices, ascending
         if (t < kTile && ((kb >> t) & 1ull)) kp[kept + __popcll(kb & ((1ull << t) - 1ull))] = nb * kTile + t;
         kept += __popcll(kb);
-        // OR the kept rows into the removal words of the later column blocks
-        for (int c = nb + 1 + t; c < cb; c += kSweepThreads) {
-            unsigned long long acc = 0ull, bits = kb;
-            while (bits) {
-                int i = __ffsll((long long)bits) - 1;
-                bits &= bits - 1ull;
-                acc |= sm[(size_t)(nb * kTile + i) * cb + c];
+        const bool rkept = (kb >> r) & 1ull;
+        for (int c0 = nb + 1; c0 < cb; c0 += 16 * kSweepInflight) {
+            if (c0 != nb + 1) {
+#pragma unroll
+                for (int k = 0; k < kSweepInflight; ++k) {
+                    int c = c0 + g + 16 * k;
+                    w[k] = (rvalid && c < cb) ? rowp[c] : 0ull;
+                }
             }
-            remv[c] |= acc;
+#pragma unroll
+            for (int k = 0; k < kSweepInflight; ++k) {
+                int c = c0 + g + 16 * k;  // uniform across the warp
+                if (c < cb) {
+                    unsigned long long v = rkept ? w[k] : 0ull;
+                    unsigned lo = __reduce_or_sync(0xffffffffu, (unsigned)v);
+                    unsigned hi = __reduce_or_sync(0xffffffffu, (unsigned)(v >> 32));
+                    if (lane == 0 && (lo | hi)) atomicOr(&remv[c], ((unsigned long long)hi << 32) | lo);
+                }
+            }
         }
         __syncthreads();
     }
-    // pad with keep[0] (:110-112)
-    __syncthreads();
-    const int first = kp[0];
-    for (int p = kept + t; p < boxes_num; p += kSweepThreads) kp[p] = first;
+    const int first = kp[0];  // written by this CTA before the last barrier; pad with keep[0] (:110-112)
+    for (int p = kept + t; p < boxes_num; p += kSweep2Threads) kp[p] = first;
     if (num_kept && t == 0) num_kept[scene] = kept;
 }
 
@@ -377,10 +624,31 @@ extern "C" int hf_oriented_nms_mask(const float *boxes, unsigned long long *mask
     return launch_mask(boxes, mask, 1, boxes_num, nms_overlap_thresh, upper_only, true, (cudaStream_t)stream);
 }
 
+namespace hf {
+namespace {
+struct NmsWorkspace {
+    size_t mask_off, rec_off, lite_off, pairs_off, count_off, total;
+    unsigned long long cap;
+};
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+NmsWorkspace nms_workspace(int scenes, int boxes_num) {
+    NmsWorkspace w{};
+    size_t S = (size_t)scenes, N = (size_t)boxes_num, cb = (N + kTile - 1) / kTile;
+    w.cap = (unsigned long long)(S * N * 64);  // listed pairs; anything beyond is clipped inside the filter kernel
+    w.mask_off = 0;
+    w.rec_off = align256(w.mask_off + S * N * cb * sizeof(unsigned long long));
+    w.lite_off = align256(w.rec_off + S * N * kRec * sizeof(float));
+    w.pairs_off = align256(w.lite_off + S * N * kLite * sizeof(float));
+    w.count_off = align256(w.pairs_off + (size_t)w.cap * sizeof(unsigned long long));
+    w.total = w.count_off + 256;
+    return w;
+}
+}  // namespace
+}  // namespace hf
+
 extern "C" size_t hf_oriented_nms_workspace_bytes(int scenes, int boxes_num) {
     if (scenes <= 0 || boxes_num <= 0) return 0;
-    size_t cb = ((size_t)boxes_num + hf::kTile - 1) / hf::kTile;
-    return (size_t)scenes * boxes_num * cb * sizeof(unsigned long long);
+    return hf::nms_workspace(scenes, boxes_num).total;
 }
 
 extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int *keep,
@@ -389,25 +657,45 @@ extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, fl
     HF_REQUIRE(nms_overlap_thresh >= 0, "Need nms_threshold >= 0");
     HF_REQUIRE(boxes_num > 0 && scenes >= 0, "OrientendNMS expects (N, 5) boxes shape");
     HF_REQUIRE(boxes && keep, "OrientedNMS: null pointer");
+    HF_REQUIRE(scenes <= 65535 && boxes_num < (1 << 22), "OrientedNMS: at most 65535 scenes of < 4194304 boxes");
     if (scenes == 0) return HF_OK;
-    size_t need = hf_oriented_nms_workspace_bytes(scenes, boxes_num);
-    if (!workspace || workspace_bytes < need) {
-        set_error("OrientedNMS: workspace of %zu bytes required, got %zu", need, workspace ? workspace_bytes : (size_t)0);
+    const NmsWorkspace w = nms_workspace(scenes, boxes_num);
+    if (!workspace || workspace_bytes < w.total) {
+        set_error("OrientedNMS: workspace of %zu bytes required, got %zu", w.total, workspace ? workspace_bytes : (size_t)0);
         return HF_ERR_WORKSPACE;
     }
-    cudaStream_t s = (cudaStream_t)stream;
-    unsigned long long *mask = static_cast<unsigned long long *>(workspace);
-    int rc = launch_mask(boxes, mask, scenes, boxes_num, nms_overlap_thresh, 1, false, s);
-    if (rc != HF_OK) return rc;
+    HF_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "OrientedNMS: workspace must be 16-byte aligned");
     const int cb = (boxes_num + kTile - 1) / kTile;
     size_t smem = (size_t)cb * sizeof(unsigned long long);
     if (smem > 200 * 1024) {
         set_error("OrientedNMS: %d boxes exceed the sweep kernel's shared memory", boxes_num);
         return HF_ERR_UNSUPPORTED;
     }
+    cudaStream_t s = (cudaStream_t)stream;
+    char *base = static_cast<char *>(workspace);
+    unsigned long long *mask = reinterpret_cast<unsigned long long *>(base + w.mask_off);
+    float *rec = reinterpret_cast<float *>(base + w.rec_off);
+    float *lite = reinterpret_cast<float *>(base + w.lite_off);
+    NmsLists lists;
+    lists.pairs = reinterpret_cast<unsigned long long *>(base + w.pairs_off);
+    lists.count = reinterpret_cast<unsigned long long *>(base + w.count_off);
+    lists.cap = w.cap;
+    // the clip kernel ORs bits into the mask; the pair counter starts at 0
+    HF_CUDA_OK(cudaMemsetAsync(mask, 0, (size_t)scenes * boxes_num * cb * sizeof(unsigned long long), s));
+    HF_CUDA_OK(cudaMemsetAsync(lists.count, 0, sizeof(unsigned long long), s));
+    const long long total = (long long)scenes * boxes_num;
+    nms_prepare_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(total, boxes, rec, lite);
+    HF_LAUNCH_OK("nms_prepare_kernel");
+    dim3 fgrid((cb + kChunk - 1) / kChunk, cb, scenes);
+    nms_filter_kernel<<<fgrid, 256, 0, s>>>(boxes_num, nms_overlap_thresh, rec, lite, mask, lists);
+    HF_LAUNCH_OK("nms_filter_kernel");
+    unsigned long long want = (w.cap + 255) / 256;
+    unsigned cgrid = (unsigned)(want < (unsigned long long)num_sms() * 8 ? want : (unsigned long long)num_sms() * 8);
+    nms_clip_kernel<<<cgrid, 256, 0, s>>>(boxes_num, nms_overlap_thresh, rec, mask, lists);
+    HF_LAUNCH_OK("nms_clip_kernel");
     if (smem > 40 * 1024)
-        HF_CUDA_OK(cudaFuncSetAttribute(nms_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nms_sweep_kernel<<<scenes, kSweepThreads, smem, s>>>(boxes_num, mask, keep, num_kept);
-    HF_LAUNCH_OK("nms_sweep_kernel");
+        HF_CUDA_OK(cudaFuncSetAttribute(nms_sweep_kernel2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    nms_sweep_kernel2<<<scenes, kSweep2Threads, smem, s>>>(boxes_num, mask, keep, num_kept);
+    HF_LAUNCH_OK("nms_sweep_kernel2");
     return HF_OK;
 }

@@ -59,18 +59,30 @@ __device__ __forceinline__ uint32_t tie_decode(uint32_t lo) {
 
 constexpr int kMsgBytes = 20;  // {lo, hi, x, y} + {z}
 
+// Per iteration (the sequential critical path, m-1 of them):
+//   1. every thread updates the running min-distance of its PTS points and keeps only the
+//      MAX VALUE (8 instructions per point; no index bookkeeping);
+//   2. warp max (one redux.sync) -> shared -> ONE __syncthreads -> CTA max (one redux.sync);
+//   3. only the warp that owns the CTA maximum recovers WHICH point it is (the reference's
+//      tie-break as an explicit key) and pushes {key, xyz} to every CTA of the cluster with
+//      st.async (DSMEM), completing on the receivers' mbarriers; all other warps go straight
+//      to the wait.  If several warps hold the same maximum (duplicate points) a second
+//      barrier decides between them — rare, and uniform across the CTA;
+//   4. every warp picks the cluster maximum of the <= 8 received candidates with two
+//      redux.sync and reads the winner's coordinates as a shared-memory broadcast.
 template <int CLUSTER, int THREADS, int PTS>
 __global__ void __launch_bounds__(THREADS, 1)
     fps_cluster_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out) {
-    static_assert(THREADS % 512 == 0, "a thread's points must share one (k mod 512) slot");
-    constexpr int CAP = THREADS * PTS;  // points held by one CTA
+    constexpr int CAP = THREADS * PTS;  // points held by one CTA (a power of two)
     constexpr int NW = THREADS / 32;
+    static_assert((CAP & (CAP - 1)) == 0, "CAP must be a power of two");
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *sx = reinterpret_cast<float *>(smem_raw);
     float *sy = sx + CAP;
     float *sz = sy + CAP;
-    __shared__ unsigned long long wkey[2][32];
+    __shared__ uint32_t wmax[2][32];
+    __shared__ uint32_t cand[2];
     __shared__ __align__(16) uint32_t slots[2][8][8];
     __shared__ __align__(8) uint64_t bars[2];
 
@@ -92,24 +104,22 @@ __global__ void __launch_bounds__(THREADS, 1)
             td[p] = 1e38f;  // tf_sampling_g.cu:118
         } else {
             x[p] = y[p] = z[p] = 0.f;
-            td[p] = -1.f;  // padding: min(d,-1) = -1 never beats best = -1 (strict >)
+            td[p] = -1.f;  // padding never wins: its key is (0, 0), below every real point's
         }
         sx[p * THREADS + t] = x[p];
         sy[p * THREADS + t] = y[p];
         sz[p * THREADS + t] = z[p];
     }
-    if (CLUSTER > 1) {
-        if (t == 0) {
-            mbar_init(&bars[0], 1);
-            mbar_init(&bars[1], 1);
-            mbar_fence_init();
-            mbar_arrive_expect_tx(&bars[0], CLUSTER * kMsgBytes);
-            mbar_arrive_expect_tx(&bars[1], CLUSTER * kMsgBytes);
-        }
-        cluster_sync_all();
-    } else {
-        __syncthreads();
+    if (t == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(&bars[0], CLUSTER * kMsgBytes);
+        mbar_arrive_expect_tx(&bars[1], CLUSTER * kMsgBytes);
+        cand[0] = cand[1] = 0u;
     }
+    if (CLUSTER > 1) cluster_sync_all();
+    else __syncthreads();
 
     // start at index 0 (tf_sampling_g.cu:114-116)
     float cx = data[0], cy = data[1], cz = data[2];
@@ -117,68 +127,79 @@ __global__ void __launch_bounds__(THREADS, 1)
 
     const int iters = m - 1;
     for (int it = 0; it < iters; ++it) {
-        float best = -1.f;
-        int bp = -1;
+        const int buf = it & 1;
+        // ---- 1. update ----
+        float mx = -1.f;
 #pragma unroll
         for (int p = 0; p < PTS; ++p) {
             float d = sqdist(x[p] - cx, y[p] - cy, z[p] - cz);
-            float d2 = fminf(d, td[p]);
-            td[p] = d2;
-            if (d2 > best) {  // strict: lowest k of this thread's slot wins (:146-149)
-                best = d2;
-                bp = p;
-            }
+            td[p] = fminf(d, td[p]);
+            mx = fmaxf(mx, td[p]);
         }
-        uint32_t hi = 0, lo = 0;
-        if (bp >= 0) {
-            hi = __float_as_uint(best);  // best >= +0: bit pattern is order preserving
-            lo = tie_word(base + bp * THREADS + t);
-        }
-        // warp arg-max on (hi, lo)
-        uint32_t mh = __reduce_max_sync(0xffffffffu, hi);
-        uint32_t ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
-        if (lane == 0) wkey[it & 1][warp] = ((unsigned long long)mh << 32) | ml;
+        // distances are >= +0, so their bit patterns order like unsigned ints; padding -> 0
+        const uint32_t hi = __float_as_uint(fmaxf(mx, 0.f));
+        // ---- 2. CTA max ----
+        const uint32_t wm = __reduce_max_sync(0xffffffffu, hi);
+        if (lane == 0) wmax[buf][warp] = wm;
         __syncthreads();
-        unsigned long long wk = lane < NW ? wkey[it & 1][lane] : 0ull;
-        uint32_t h2 = (uint32_t)(wk >> 32), l2 = (uint32_t)wk;
-        uint32_t ch = __reduce_max_sync(0xffffffffu, h2);
-        uint32_t cl = __reduce_max_sync(0xffffffffu, h2 == ch ? l2 : 0u);
-
+        if (t == 0) cand[buf ^ 1] = 0u;  // next iteration's tie buffer (its last readers are behind this barrier)
+        const uint32_t v = lane < NW ? wmax[buf][lane] : 0u;
+        const uint32_t cm = __reduce_max_sync(0xffffffffu, v);
+        const unsigned owners = __ballot_sync(0xffffffffu, lane < NW && v == cm);
+        // ---- 3. owner warp: recover the point, push ----
+        bool push = false;
+        uint32_t wl = 0u;
+        if (wm == cm) {  // warp-uniform
+            uint32_t lo = 0u;
+            if (hi == cm && mx >= 0.f) {
+#pragma unroll
+                for (int p = 0; p < PTS; ++p) {
+                    uint32_t w = tie_word(base + p * THREADS + t);
+                    if (td[p] == mx && w > lo) lo = w;
+                }
+            }
+            wl = __reduce_max_sync(0xffffffffu, lo);
+            push = true;
+        }
+        if (owners & (owners - 1u)) {  // several warps hold the CTA maximum: CTA-uniform slow path
+            if (push && lane == 0) atomicMax(&cand[buf], wl);
+            __syncthreads();
+            const uint32_t c = cand[buf];
+            // c == 0: no real point in this CTA (all padding) -> warp 0 reports the empty key
+            push = push && c == wl && (c != 0u || warp == 0);
+        }
+        if (push && lane < CLUSTER) {
+            float wx = 0.f, wy = 0.f, wz = 0.f;
+            if (wl != 0u) {
+                uint32_t li = tie_decode(wl) - base;
+                wx = sx[li];
+                wy = sy[li];
+                wz = sz[li];
+            }
+            uint32_t dst = mapa_u32(smem_u32(&slots[buf][rank][0]), (uint32_t)lane);
+            uint32_t dbar = mapa_u32(smem_u32(&bars[buf]), (uint32_t)lane);
+            st_async_v4(dst, wl, wl != 0u ? cm : 0u, __float_as_uint(wx), __float_as_uint(wy), dbar);
+            st_async_b32(dst + 16, __float_as_uint(wz), dbar);
+        }
+        // ---- 4. cluster max ----
+        mbar_wait(&bars[buf], (uint32_t)(it >> 1) & 1u);
+        if (t == 0 && it + 2 < iters) mbar_arrive_expect_tx(&bars[buf], CLUSTER * kMsgBytes);
         uint32_t win;
         if (CLUSTER == 1) {
-            win = tie_decode(cl);
-            uint32_t li = win - base;
-            cx = sx[li];
-            cy = sy[li];
-            cz = sz[li];
+            win = tie_decode(slots[buf][0][0]);
+            cx = __uint_as_float(slots[buf][0][2]);
+            cy = __uint_as_float(slots[buf][0][3]);
+            cz = __uint_as_float(slots[buf][0][4]);
         } else {
-            const int buf = it & 1;
-            if (warp == 0 && lane < CLUSTER) {
-                float wx = 0.f, wy = 0.f, wz = 0.f;
-                if ((ch | cl) != 0u) {
-                    uint32_t li = tie_decode(cl) - base;
-                    wx = sx[li];
-                    wy = sy[li];
-                    wz = sz[li];
-                }
-                uint32_t dst = mapa_u32(smem_u32(&slots[buf][rank][0]), (uint32_t)lane);
-                uint32_t dbar = mapa_u32(smem_u32(&bars[buf]), (uint32_t)lane);
-                st_async_v4(dst, cl, ch, __float_as_uint(wx), __float_as_uint(wy), dbar);
-                st_async_b32(dst + 16, __float_as_uint(wz), dbar);
+            uint32_t klo = 0u, khi = 0u;
+            if (lane < CLUSTER) {
+                klo = slots[buf][lane][0];
+                khi = slots[buf][lane][1];
             }
-            mbar_wait(&bars[buf], (uint32_t)(it >> 1) & 1u);
-            if (t == 0 && it + 2 < iters) mbar_arrive_expect_tx(&bars[buf], CLUSTER * kMsgBytes);
-            unsigned long long bk = 0ull;
-            int bq = 0;
-#pragma unroll
-            for (int q = 0; q < CLUSTER; ++q) {
-                unsigned long long kq = *reinterpret_cast<const unsigned long long *>(&slots[buf][q][0]);
-                if (kq > bk) {
-                    bk = kq;
-                    bq = q;
-                }
-            }
-            win = tie_decode((uint32_t)bk);
+            const uint32_t gh = __reduce_max_sync(0xffffffffu, khi);
+            const uint32_t gl = __reduce_max_sync(0xffffffffu, khi == gh ? klo : 0u);
+            win = tie_decode(gl);
+            const uint32_t bq = win / CAP;
             cx = __uint_as_float(slots[buf][bq][2]);
             cy = __uint_as_float(slots[buf][bq][3]);
             cz = __uint_as_float(slots[buf][bq][4]);
@@ -275,8 +296,20 @@ int launch_fps(int b, int n, int m, const float *inp, int *out, cudaStream_t str
     return HF_OK;
 }
 
+int g_threads_override = 0;
+
 template <int CLUSTER>
 int dispatch_pts(int per_cta, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {
+    // 256-thread CTAs halve the per-iteration reduction overhead (8 warps instead of 16);
+    // 512-thread CTAs hide more latency.  Heuristic: 256 threads while a thread holds <= 8 points.
+    const bool t256 = g_threads_override == 256 || (g_threads_override == 0 && per_cta <= 2048);
+    if (t256 && per_cta <= 4096) {
+        if (per_cta <= 256) return launch_fps<CLUSTER, 256, 1>(b, n, m, inp, out, s);
+        if (per_cta <= 512) return launch_fps<CLUSTER, 256, 2>(b, n, m, inp, out, s);
+        if (per_cta <= 1024) return launch_fps<CLUSTER, 256, 4>(b, n, m, inp, out, s);
+        if (per_cta <= 2048) return launch_fps<CLUSTER, 256, 8>(b, n, m, inp, out, s);
+        return launch_fps<CLUSTER, 256, 16>(b, n, m, inp, out, s);
+    }
     if (per_cta <= 512) return launch_fps<CLUSTER, 512, 1>(b, n, m, inp, out, s);
     if (per_cta <= 1024) return launch_fps<CLUSTER, 512, 2>(b, n, m, inp, out, s);
     if (per_cta <= 2048) return launch_fps<CLUSTER, 512, 4>(b, n, m, inp, out, s);
@@ -289,6 +322,7 @@ int dispatch_pts(int per_cta, int b, int n, int m, const float *inp, int *out, c
 }  // namespace hf
 
 extern "C" void hf_fps_set_cluster(int cluster) { hf::g_cluster_override = cluster; }
+extern "C" void hf_fps_set_threads(int threads) { hf::g_threads_override = threads; }
 
 extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
                                         hf_stream_t stream) {

@@ -55,6 +55,8 @@ int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp,
                              hf_stream_t stream);
 /* Tuning override for the FPS launch shape (cluster size 1/2/4/8, 0 = heuristic). */
 void hf_fps_set_cluster(int cluster);
+/* Tuning override for the FPS CTA size (256 or 512 threads, 0 = heuristic). */
+void hf_fps_set_threads(int threads);
 
 /* Replaces gatherpointLauncher(b,n,m,inp,idx,out), sampling/tf_sampling_g.cu:206.
  * inp (b,n,3), idx (b,m) -> out (b,m,3). */
