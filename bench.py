@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--table", action="store_true", help="also print a per-launch table to stderr")
+    ap.add_argument("--serial", action="store_true",
+                    help="issue the whole chain on one stream in program order (default: independent branches overlap on streams)")
     return ap.parse_args()
 
 
@@ -89,6 +91,7 @@ def config_dict(args, cfg, n_gpus):
         "global_scans": args.batch * n_gpus,
         "points_per_scan": cfg.points,
         "sharding": "batch slices, one per GPU, no collective" if n_gpus > 1 else "single GPU",
+        "issue": "one stream, program order" if args.serial else "independent branches of the chain on 5 CUDA streams",
         "l2": "no explicit flush: one step reads 0.45 GB and writes 5.6 GB per GPU, far beyond the 126 MB L2",
     }
 
@@ -351,10 +354,11 @@ def run_b200(args):
         return float(t.item())
 
     # ---- resident-input throughput (value) + per-launch events (roofline) ----
+    overlap = not args.serial
     probe = EventProbe(torch)
     probe.enabled = False
     for _ in range(max(args.warmup, 3)):
-        chain.run_chain(resident, cfg, probe)
+        chain.run_chain(resident, cfg, probe, overlap=overlap)
     probe.enabled = True
     barrier()
     clocks = ClockSampler(local).start() if rank == 0 else None
@@ -362,7 +366,7 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(args.steps):
-        chain.run_chain(resident, cfg, probe)
+        chain.run_chain(resident, cfg, probe, overlap=overlap)
     ev1.record()
     barrier()
     launches = hf.launch_count() - l0
@@ -370,6 +374,13 @@ def run_b200(args):
     launches = int(sum_over_ranks(launches))
     ops = probe.summarise(args.steps)
     probe.enabled = False
+    # each launch timed ALONE (one stream, program order) — outside the timed region, for the per-kernel table
+    alone = EventProbe(torch)
+    for _ in range(min(args.steps, 5)):
+        chain.run_chain(resident, cfg, alone, overlap=False)
+    torch.cuda.synchronize()
+    alone_ms = {o["launch"]: o["ms"] for o in alone.summarise(min(args.steps, 5))}
+    serial_step_ms = sum(o["ms"] * o["per_step"] for o in alone.summarise(min(args.steps, 5)))
 
     # ---- end to end: host buffers in, host-consumed results out, through the public op API ----
     e2e = None
@@ -383,7 +394,7 @@ def run_b200(args):
                 t0 = time.perf_counter()
                 e0.record()
             d = chain.to_device_from_pinned(pinned, dev)
-            res = chain.run_chain(d, cfg)
+            res = chain.run_chain(d, cfg, overlap=overlap)
             outs = chain.host_results(res, cfg)
             if out_host is None:
                 out_host = [torch.empty(o.shape, dtype=o.dtype, pin_memory=True) for o in outs]
@@ -406,17 +417,23 @@ def run_b200(args):
         return 0
 
     hbm_peak, hbm_src = peaks()
-    for o in ops:
-        sec = o["ms"] / 1e3
+    def rate(o, ms_launch):
+        sec = ms_launch / 1e3
         if o["bound"] == "hbm" and sec > 0:
-            o["achieved"], o["unit"], o["peak"] = o["bytes"] / sec / 1e9, "GB/s", hbm_peak
-        elif o["bound"] == "fp32" and sec > 0 and o["flops"]:
-            o["achieved"], o["unit"], o["peak"] = o["flops"] / sec / 1e12, "TFLOP/s", FP32_PEAK_TFLOPS
-        else:
-            o["achieved"], o["unit"], o["peak"] = None, None, None
+            return o["bytes"] / sec / 1e9, "GB/s", hbm_peak
+        if o["bound"] == "fp32" and sec > 0 and o["flops"]:
+            return o["flops"] / sec / 1e12, "TFLOP/s", FP32_PEAK_TFLOPS
+        return None, None, None
+
+    for o in ops:
+        o["achieved"], o["unit"], o["peak"] = rate(o, o["ms"])
         o["frac"] = (o["achieved"] / o["peak"]) if o["achieved"] else None
-        o["share_of_step"] = o["ms"] * o["per_step"] / (ms / args.steps)
-    ops.sort(key=lambda o: -o["ms"] * o["per_step"])
+        o["ms_alone"] = alone_ms.get(o["launch"])
+        a = rate(o, o["ms_alone"])[0] if o["ms_alone"] else None
+        o["frac_alone"] = (a / o["peak"]) if a and o["peak"] else None
+        # share of the serial (one-stream) step: with overlap the in-region durations add up to more than the step
+        o["share_of_step"] = (o["ms_alone"] or o["ms"]) * o["per_step"] / serial_step_ms
+    ops.sort(key=lambda o: -(o["ms_alone"] or o["ms"]) * o["per_step"])
     own = [o for o in ops if o["bound"] != "other"]
     top = own[0]
     top_hbm = max((o for o in own if o["bound"] == "hbm"), key=lambda o: o["ms"])
@@ -424,6 +441,7 @@ def run_b200(args):
     def roof(o):
         return {"kernel": o["launch"], "bound": o["bound"], "achieved": o["achieved"], "peak": o["peak"],
                 "unit": o["unit"], "frac": o["frac"], "traffic": None, "ms_per_launch": o["ms"],
+                "ms_per_launch_alone": o["ms_alone"], "frac_alone": o["frac_alone"],
                 "algorithmic_bytes": o["bytes"], "algorithmic_flops": o["flops"],
                 "peak_source": hbm_src if o["bound"] == "hbm" else "derived 148 SM x 128 lanes x 2 x 1.965 GHz (not measured)",
                 "share_of_step": o["share_of_step"]}
@@ -434,16 +452,17 @@ def run_b200(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args, cfg, n_gpus), "clocks": clk, "e2e": e2e, "gpu_launches": launches,
         "roofline": roof(top), "roofline_hbm": roof(top_hbm),
-        "roofline_ops": [{k: o[k] for k in ("launch", "bound", "ms", "per_step", "achieved", "unit", "frac", "share_of_step")}
-                         for o in ops],
+        "roofline_ops": [{k: o[k] for k in ("launch", "bound", "ms", "ms_alone", "per_step", "achieved", "unit", "frac",
+                                            "frac_alone", "share_of_step")} for o in ops],
+        "serial_ms_per_step": serial_step_ms,
     }
     if not args.no_cpu_baseline:
         cb, _ = time_cpu(args, cfg, host_np, 1, 0)
         line["cpu_baseline"] = cb
     if args.table:
         for o in ops:
-            sys.stderr.write("%-34s %-5s %9.4f ms x%d  %s %s  frac=%s  share=%.3f\n" % (
-                o["launch"], o["bound"], o["ms"], o["per_step"],
+            sys.stderr.write("%-34s %-5s %9.4f ms (alone %9.4f) x%d  %s %s  frac=%s  share=%.3f\n" % (
+                o["launch"], o["bound"], o["ms"], o["ms_alone"] or 0.0, o["per_step"],
                 ("%.1f" % o["achieved"]) if o["achieved"] else "-", o["unit"] or "",
                 ("%.3f" % o["frac"]) if o["frac"] else "-", o["share_of_step"]))
     print(json.dumps(line))

@@ -129,60 +129,144 @@ class _NoProbe:
         return False
 
 
-def run_chain(dev, cfg, probe=None):
+class _Lanes:
+    """The CUDA streams one chain pass is spread over (cached per device).
+
+    The SA sampling chain fps_1 -> gather_1 -> fps_2 -> ... -> gather_4 is strictly sequential
+    and latency bound (one cluster per scan); everything else only depends on one of its
+    intermediate results or on nothing at all.  Issuing those on side streams lets their CTAs
+    fill the SM resources the sampling CTAs leave idle:
+        crit   fps / gather_point of every level                      (high priority)
+        group  query_ball_point + group_point x2 of level l           (after gather_l)
+        fp     three_nn of every level as soon as its two clouds exist, then the
+               three_interpolate calls coarse -> fine (the order the real network needs)
+        crop   pc_crop_and_sample                                      (independent)
+        nms    oriented_nms                                            (independent)
+    """
+
+    _cache = {}
+
+    def __init__(self, device):
+        lo, hi = -1, 0
+        self.crit = torch.cuda.Stream(device=device, priority=lo)
+        self.group = torch.cuda.Stream(device=device, priority=hi)
+        self.fp = torch.cuda.Stream(device=device, priority=hi)
+        self.crop = torch.cuda.Stream(device=device, priority=hi)
+        self.nms = torch.cuda.Stream(device=device, priority=hi)
+
+    @classmethod
+    def get(cls, device):
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+        if key not in cls._cache:
+            cls._cache[key] = cls(device)
+        return cls._cache[key]
+
+    def all(self):
+        return (self.crit, self.group, self.fp, self.crop, self.nms)
+
+
+def _fp_weights(dist):
+    dist = torch.clamp_min(dist, 1e-10)  # pointnet_util.py:304-307
+    inv = 1.0 / dist
+    return dist, inv / inv.sum(dim=2, keepdim=True)
+
+
+def run_chain(dev, cfg, probe=None, overlap=True):
     """Run the chain on device-resident inputs `dev` (see make_host_inputs).  Returns a dict of results.
+
+    overlap=True spreads the independent branches of the chain over CUDA streams (see _Lanes);
+    the caller's current stream waits for all of them before this function returns, so the
+    results are ordered on the current stream as usual.  overlap=False issues every op on the
+    current stream in the reference's program order.
 
     `probe(name, **shape)` (optional) must return a context manager; every libhfops launch runs
     inside one, named after its kernel family, with the shape figures its algorithmic
     bytes / flops are computed from.
     """
     probe = probe or _NoProbe()
+    device = dev["xyz"].device
+    main = torch.cuda.current_stream(device)
+    if overlap:
+        lanes = _Lanes.get(device)
+        crit, s_group, s_fp, s_crop, s_nms = lanes.all()
+        start = torch.cuda.Event()
+        start.record(main)
+        for s in lanes.all():
+            s.wait_event(start)
+    else:
+        crit = s_group = s_fp = s_crop = s_nms = main
+    on = torch.cuda.stream
+
+    def after(stream, event):
+        if overlap:
+            stream.wait_event(event)
+
+    def mark(stream):
+        if not overlap:
+            return None
+        e = torch.cuda.Event()
+        e.record(stream)
+        return e
+
     res = {}
     xyz = [dev["xyz"]]
     fps_idx = []
     feats = [dev["intensity"]] + list(dev["sa_feats"][1:])
     b = dev["xyz"].shape[0]
+    # independent branches first, so their CTAs are queued behind the sampling chain from the start
+    if cfg.with_nms:
+        with on(s_nms), probe("oriented_nms", b=b, nb=cfg.nms_boxes):
+            keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
+        res["nms_keep"] = keep[:, : cfg.post_nms]
+        res["nms_num"] = num
+    if cfg.with_crop:
+        with on(s_crop), probe("pc_crop_and_sample", b=b, p=cfg.points, c=cfg.crop_channels,
+                               nb=dev["crop_boxes"].shape[0], r=cfg.crop_resize):
+            res["crop"] = pc_crop_and_sample(dev["xyz"], dev["crop_fts"], dev["intensity"], dev["fg_mask"],
+                                             dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
     # ---- set abstraction ----
+    nn = [None] * 4
     for l in range(4):
         n, m, ns = xyz[l].shape[1], cfg.npoint[l], cfg.nsample
-        with probe("fps", level=l + 1, b=b, n=n, m=m):
-            idx = farthest_point_sample(m, xyz[l])
-        with probe("gather_point", level=l + 1, b=b, n=n, m=m):
-            new_xyz = gather_point(xyz[l], idx)
-        with probe("query_ball_point", level=l + 1, b=b, n=n, m=m, ns=ns):
-            gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz)
-        with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
-            gxyz = group_point(xyz[l], gidx)
-        with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
-            gfeat = group_point(feats[l], gidx)
+        with on(crit):
+            with probe("fps", level=l + 1, b=b, n=n, m=m):
+                idx = farthest_point_sample(m, xyz[l])
+            with probe("gather_point", level=l + 1, b=b, n=n, m=m):
+                new_xyz = gather_point(xyz[l], idx)
+        have_xyz = mark(crit)
+        after(s_group, have_xyz)
+        with on(s_group):
+            with probe("query_ball_point", level=l + 1, b=b, n=n, m=m, ns=ns):
+                gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz)
+            with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
+                gxyz = group_point(xyz[l], gidx)
+            with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
+                gfeat = group_point(feats[l], gidx)
+        # three_nn of FP level l+1 (unknown = level l cloud, known = level l+1 cloud) is geometry only
+        after(s_fp, have_xyz)
+        with on(s_fp):
+            with probe("three_nn", level=l + 1, b=b, n=n, m=m):
+                dist, nidx = three_nn(xyz[l], new_xyz)
+            with probe("fp_weights_torch", level=l + 1, b=b, n=n):
+                dist, w = _fp_weights(dist)
+        nn[l] = (dist, nidx, w)
         fps_idx.append(idx)
         xyz.append(new_xyz)
         res["sa%d" % (l + 1)] = (gidx, cnt, gxyz, gfeat)
     res["fps_idx"] = fps_idx
     res["xyz_levels"] = xyz
-    # ---- feature propagation, coarse to fine ----
-    for j in range(4):
-        unknown, known = xyz[3 - j], xyz[4 - j]
-        n, m, c = unknown.shape[1], known.shape[1], dev["fp_feats"][j].shape[2]
-        with probe("three_nn", level=4 - j, b=b, n=n, m=m):
-            dist, idx = three_nn(unknown, known)
-        with probe("fp_weights_torch", level=4 - j, b=b, n=n):
-            dist = torch.clamp_min(dist, 1e-10)  # pointnet_util.py:304-307
-            inv = 1.0 / dist
-            w = inv / inv.sum(dim=2, keepdim=True)
-        with probe("three_interpolate", level=4 - j, b=b, n=n, m=m, c=c):
-            out = three_interpolate(dev["fp_feats"][j], idx, w)
-        res["fp%d" % (4 - j)] = (dist, idx, out)
-    if cfg.with_crop:
-        with probe("pc_crop_and_sample", b=b, p=cfg.points, c=cfg.crop_channels, nb=dev["crop_boxes"].shape[0],
-                   r=cfg.crop_resize):
-            res["crop"] = pc_crop_and_sample(dev["xyz"], dev["crop_fts"], dev["intensity"], dev["fg_mask"],
-                                             dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
-    if cfg.with_nms:
-        with probe("oriented_nms", b=b, nb=cfg.nms_boxes):
-            keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
-        res["nms_keep"] = keep[:, : cfg.post_nms]
-        res["nms_num"] = num
+    # ---- feature propagation, coarse to fine (pointnet_util.py:289-330) ----
+    with on(s_fp):
+        for j in range(4):
+            lvl = 3 - j  # unknown cloud = xyz[lvl], known = xyz[lvl + 1]
+            dist, nidx, w = nn[lvl]
+            n, m, c = xyz[lvl].shape[1], xyz[lvl + 1].shape[1], dev["fp_feats"][j].shape[2]
+            with probe("three_interpolate", level=lvl + 1, b=b, n=n, m=m, c=c):
+                out = three_interpolate(dev["fp_feats"][j], nidx, w)
+            res["fp%d" % (lvl + 1)] = (dist, nidx, out)
+    if overlap:
+        for s in lanes.all():
+            main.wait_event(mark(s))
     return res
 
 

@@ -324,3 +324,28 @@ def test_nms_full_size_properties(cuda):
     # idempotence: NMS of the survivors keeps them all
     again, num2 = oriented_nms_batch(boxes[kept][None], 0.8, return_num_kept=True)
     assert int(num2[0]) == k
+
+
+# ---------------------------------------------------------------- the chain
+def test_chain_on_streams_equals_chain_in_program_order(cuda):
+    """The multi-stream issue order of chain.run_chain must not change a single output bit."""
+    from heterofusionrcnn_b200 import chain
+
+    cfg = chain.ChainConfig().scaled(4096)
+    cfg.crop_boxes, cfg.crop_resize, cfg.crop_channels, cfg.nms_boxes = 32, 128, 32, 1500
+    dev = chain.to_device(chain.make_host_inputs(cfg, batch=3, seed=5), cuda)
+
+    def flat(res):
+        out = []
+        for k in sorted(res):
+            v = res[k]
+            out += [(k, t) for t in (v if isinstance(v, (list, tuple)) else [v])]
+        return out
+
+    for _ in range(3):  # repeated: a missing dependency would show up as a race
+        a = flat(chain.run_chain(dev, cfg, overlap=False))
+        b = flat(chain.run_chain(dev, cfg, overlap=True))
+        torch.cuda.synchronize()
+        assert len(a) == len(b)
+        for (ka, ta), (kb, tb) in zip(a, b):
+            assert ka == kb and torch.equal(ta, tb), ka

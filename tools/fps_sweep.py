@@ -37,10 +37,11 @@ def main():
         xyz, _ = synthetic.make_scans(3, b, n)
         x = torch.from_numpy(xyz).to(dev)
         ref = None
-        for cluster in (0, 1, 2, 4, 8):
-            for threads in (0, 256, 512):
+        for variant, cluster, threads in [(v, c, th) for v in (0, 1) for c in (0, 1, 2, 4, 8) for th in (256, 512)]:
+            if True:
                 if n // max(cluster, 1) > 8192 and cluster != 0:
                     continue
+                lib.hf_fps_set_variant(variant)
                 lib.hf_fps_set_cluster(cluster)
                 lib.hf_fps_set_threads(threads)
                 try:
@@ -52,10 +53,11 @@ def main():
                 if ref is None:
                     ref = out
                 same = bool(torch.equal(out, ref))
-                print("n=%6d m=%5d b=%2d cluster=%d threads=%3d  %8.4f ms  %7.1f ns/iter  same=%s" % (
-                    n, m, b, cluster, threads, ms, ms * 1e6 / (m - 1), same))
+                print("n=%6d m=%5d b=%2d variant=%d cluster=%d threads=%3d  %8.4f ms  %7.1f ns/iter  same=%s" % (
+                    n, m, b, variant, cluster, threads, ms, ms * 1e6 / (m - 1), same))
         lib.hf_fps_set_cluster(0)
         lib.hf_fps_set_threads(0)
+        lib.hf_fps_set_variant(0)
 
 
 if __name__ == "__main__":
