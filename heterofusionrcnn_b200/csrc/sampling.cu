@@ -70,6 +70,10 @@ constexpr int kMsgBytes = 20;  // {lo, hi, x, y} + {z}
 //      barrier decides between them — rare, and uniform across the CTA;
 //   4. every warp picks the cluster maximum of the <= 8 received candidates with two
 //      redux.sync and reads the winner's coordinates as a shared-memory broadcast.
+// Measured alternative (profiles/r1_fps_sweep_v3_polling_vs_mbarrier.txt): plain remote
+// stores of self-tagged 64-bit words with receivers spinning on ld.volatile.shared was
+// 1.6-2.2x SLOWER per iteration than st.async + mbarrier (the HW-sleeping try_wait keeps
+// the issue slots free for the warps that still compute), so it was dropped.
 template <int CLUSTER, int THREADS, int PTS>
 __global__ void __launch_bounds__(THREADS, 1)
     fps_cluster_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out) {
@@ -209,163 +213,6 @@ __global__ void __launch_bounds__(THREADS, 1)
     if (CLUSTER > 1) cluster_sync_all();  // no CTA may exit while peers can still push into it
 }
 
-// ---- variant 1: tagged 64-bit words + shared-memory polling instead of st.async/mbarrier ----
-// Every message word is one naturally aligned 64-bit store (single-copy atomic) that
-// carries its own tag, so no ordering between the words is needed and no barrier object
-// sits on the critical path:
-//   word 0 = { tie word , distance bits | parity << 31 }      (distance >= +0: bit 31 is free)
-//   word 1..3 = { x | y | z , iteration + 1 }
-// Receivers spin on their OWN shared memory (ld.volatile.shared, ~30 cycles per probe).
-__device__ __forceinline__ void st_cluster_u64(uint32_t raddr, unsigned long long v) {
-    asm volatile("st.volatile.shared::cluster.u64 [%0], %1;" ::"r"(raddr), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_volatile_shared_u64(const unsigned long long *p) {
-    unsigned long long v;
-    asm volatile("ld.volatile.shared.u64 %0, [%1];" : "=l"(v) : "r"(smem_u32(p)) : "memory");
-    return v;
-}
-
-template <int CLUSTER, int THREADS, int PTS>
-__global__ void __launch_bounds__(THREADS, 1)
-    fps_poll_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out) {
-    constexpr int CAP = THREADS * PTS;
-    constexpr int NW = THREADS / 32;
-    static_assert((CAP & (CAP - 1)) == 0, "CAP must be a power of two");
-
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float *sx = reinterpret_cast<float *>(smem_raw);
-    float *sy = sx + CAP;
-    float *sz = sy + CAP;
-    __shared__ uint32_t wmax[2][32];
-    __shared__ uint32_t cand[2];
-    __shared__ __align__(16) unsigned long long slots[2][8][4];
-
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const uint32_t rank = CLUSTER > 1 ? cluster_ctarank() : 0u;
-    const int scene = blockIdx.x / CLUSTER;
-    const float *data = inp + (size_t)scene * n * 3;
-    int *idxs = out + (size_t)scene * m;
-    const uint32_t base = rank * CAP;
-
-    float x[PTS], y[PTS], z[PTS], td[PTS];
-#pragma unroll
-    for (int p = 0; p < PTS; ++p) {
-        uint32_t k = base + p * THREADS + t;
-        if (k < (uint32_t)n) {
-            x[p] = data[(size_t)k * 3 + 0];
-            y[p] = data[(size_t)k * 3 + 1];
-            z[p] = data[(size_t)k * 3 + 2];
-            td[p] = 1e38f;
-        } else {
-            x[p] = y[p] = z[p] = 0.f;
-            td[p] = -1.f;
-        }
-        sx[p * THREADS + t] = x[p];
-        sy[p * THREADS + t] = y[p];
-        sz[p * THREADS + t] = z[p];
-    }
-    if (t < 64) (&slots[0][0][0])[t] = (t & 3) == 0 ? (1ull << 63) : 0ull;  // parity 1 / tag 0: never expected first
-    if (t == 0) cand[0] = cand[1] = 0u;
-    if (CLUSTER > 1) cluster_sync_all();
-    else __syncthreads();
-
-    float cx = data[0], cy = data[1], cz = data[2];
-    if (rank == 0 && t == 0) idxs[0] = 0;
-
-    const int iters = m - 1;
-    for (int it = 0; it < iters; ++it) {
-        const int buf = it & 1;
-        const uint32_t par = ((uint32_t)it >> 1) & 1u;
-        float mx = -1.f;
-#pragma unroll
-        for (int p = 0; p < PTS; ++p) {
-            float d = sqdist(x[p] - cx, y[p] - cy, z[p] - cz);
-            td[p] = fminf(d, td[p]);
-            mx = fmaxf(mx, td[p]);
-        }
-        const uint32_t hi = __float_as_uint(fmaxf(mx, 0.f));
-        const uint32_t wm = __reduce_max_sync(0xffffffffu, hi);
-        if (lane == 0) wmax[buf][warp] = wm;
-        __syncthreads();
-        if (t == 0) cand[buf ^ 1] = 0u;
-        const uint32_t v = lane < NW ? wmax[buf][lane] : 0u;
-        const uint32_t cm = __reduce_max_sync(0xffffffffu, v);
-        const unsigned owners = __ballot_sync(0xffffffffu, lane < NW && v == cm);
-        bool push = false;
-        uint32_t wl = 0u;
-        if (wm == cm) {
-            uint32_t lo = 0u;
-            if (hi == cm && mx >= 0.f) {
-#pragma unroll
-                for (int p = 0; p < PTS; ++p) {
-                    uint32_t w = tie_word(base + p * THREADS + t);
-                    if (td[p] == mx && w > lo) lo = w;
-                }
-            }
-            wl = __reduce_max_sync(0xffffffffu, lo);
-            push = true;
-        }
-        if (owners & (owners - 1u)) {
-            if (push && lane == 0) atomicMax(&cand[buf], wl);
-            __syncthreads();
-            const uint32_t c = cand[buf];
-            push = push && c == wl && (c != 0u || warp == 0);
-        }
-        const uint32_t tag = (uint32_t)it + 1u;
-        if (push && lane < CLUSTER) {
-            float wx = 0.f, wy = 0.f, wz = 0.f;
-            if (wl != 0u) {
-                uint32_t li = tie_decode(wl) - base;
-                wx = sx[li];
-                wy = sy[li];
-                wz = sz[li];
-            }
-            const unsigned long long k0 = ((unsigned long long)((wl != 0u ? cm : 0u) | (par << 31)) << 32) | wl;
-            const unsigned long long tg = (unsigned long long)tag << 32;
-            if (CLUSTER > 1) {
-                uint32_t dst = mapa_u32(smem_u32(&slots[buf][rank][0]), (uint32_t)lane);
-                st_cluster_u64(dst + 8, tg | __float_as_uint(wx));
-                st_cluster_u64(dst + 16, tg | __float_as_uint(wy));
-                st_cluster_u64(dst + 24, tg | __float_as_uint(wz));
-                st_cluster_u64(dst, k0);
-            } else {
-                volatile unsigned long long *d = &slots[buf][0][0];
-                d[1] = tg | __float_as_uint(wx);
-                d[2] = tg | __float_as_uint(wy);
-                d[3] = tg | __float_as_uint(wz);
-                d[0] = k0;
-            }
-        }
-        // ---- cluster max: spin on the local copies of the CLUSTER candidates ----
-        unsigned long long k0 = 0ull;
-        if (lane < CLUSTER) {
-            do {
-                k0 = ld_volatile_shared_u64(&slots[buf][lane][0]);
-            } while ((uint32_t)(k0 >> 63) != par);
-        }
-        uint32_t bq = 0, win;
-        if (CLUSTER == 1) {
-            k0 = __shfl_sync(0xffffffffu, k0, 0);
-            win = tie_decode((uint32_t)k0);
-        } else {
-            const uint32_t khi = (uint32_t)(k0 >> 32) & 0x7fffffffu, klo = (uint32_t)k0;
-            const uint32_t gh = __reduce_max_sync(0xffffffffu, khi);
-            const uint32_t gl = __reduce_max_sync(0xffffffffu, khi == gh ? klo : 0u);
-            win = tie_decode(gl);
-            bq = win / CAP;
-        }
-        unsigned long long c1, c2, c3;
-        do { c1 = ld_volatile_shared_u64(&slots[buf][bq][1]); } while ((uint32_t)(c1 >> 32) != tag);
-        do { c2 = ld_volatile_shared_u64(&slots[buf][bq][2]); } while ((uint32_t)(c2 >> 32) != tag);
-        do { c3 = ld_volatile_shared_u64(&slots[buf][bq][3]); } while ((uint32_t)(c3 >> 32) != tag);
-        cx = __uint_as_float((uint32_t)c1);
-        cy = __uint_as_float((uint32_t)c2);
-        cz = __uint_as_float((uint32_t)c3);
-        if (rank == 0 && t == 0) idxs[it + 1] = (int)win;
-    }
-    if (CLUSTER > 1) cluster_sync_all();
-}
-
 // Fallback for clouds larger than the on-chip capacity (n > 8 * 512 * 16): one CTA per
 // scene slot, running distances in a caller-provided global scratch (32*n floats, the
 // reference's own temp contract, tf_sampling.cpp:115).
@@ -430,11 +277,10 @@ __global__ void gather_point_kernel(long long total, int n, int m, const float *
 }
 
 int g_cluster_override = 0;
-int g_variant = 0;  // 0 = st.async + mbarrier exchange, 1 = tagged words + polling
 
 template <int CLUSTER, int THREADS, int PTS>
 int launch_fps(int b, int n, int m, const float *inp, int *out, cudaStream_t stream) {
-    auto kern = g_variant == 0 ? fps_cluster_kernel<CLUSTER, THREADS, PTS> : fps_poll_kernel<CLUSTER, THREADS, PTS>;
+    auto kern = fps_cluster_kernel<CLUSTER, THREADS, PTS>;
     size_t smem = (size_t)3 * THREADS * PTS * sizeof(float);
     if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
@@ -481,7 +327,6 @@ int dispatch_pts(int per_cta, int b, int n, int m, const float *inp, int *out, c
 
 extern "C" void hf_fps_set_cluster(int cluster) { hf::g_cluster_override = cluster; }
 extern "C" void hf_fps_set_threads(int threads) { hf::g_threads_override = threads; }
-extern "C" void hf_fps_set_variant(int variant) { hf::g_variant = variant; }
 
 extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
                                         hf_stream_t stream) {

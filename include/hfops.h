@@ -57,8 +57,6 @@ int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp,
 void hf_fps_set_cluster(int cluster);
 /* Tuning override for the FPS CTA size (256 or 512 threads, 0 = heuristic). */
 void hf_fps_set_threads(int threads);
-/* Tuning override for the FPS cluster exchange (0 = st.async + mbarrier, 1 = tagged words + polling). */
-void hf_fps_set_variant(int variant);
 
 /* Replaces gatherpointLauncher(b,n,m,inp,idx,out), sampling/tf_sampling_g.cu:206.
  * inp (b,n,3), idx (b,m) -> out (b,m,3). */

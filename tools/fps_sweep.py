@@ -37,11 +37,10 @@ def main():
         xyz, _ = synthetic.make_scans(3, b, n)
         x = torch.from_numpy(xyz).to(dev)
         ref = None
-        for variant, cluster, threads in [(v, c, th) for v in (0, 1) for c in (0, 1, 2, 4, 8) for th in (256, 512)]:
+        for variant, cluster, threads in [(v, c, th) for v in (0,) for c in (0, 1, 2, 4, 8) for th in (256, 512)]:
             if True:
                 if n // max(cluster, 1) > 8192 and cluster != 0:
                     continue
-                lib.hf_fps_set_variant(variant)
                 lib.hf_fps_set_cluster(cluster)
                 lib.hf_fps_set_threads(threads)
                 try:
@@ -57,7 +56,6 @@ def main():
                     n, m, b, variant, cluster, threads, ms, ms * 1e6 / (m - 1), same))
         lib.hf_fps_set_cluster(0)
         lib.hf_fps_set_threads(0)
-        lib.hf_fps_set_variant(0)
 
 
 if __name__ == "__main__":
