@@ -411,6 +411,18 @@ def run_b200(args):
                "copied_out": "FPS indices (4 levels), ball-query counts, NMS keep lists + counts, crop non_empty flags"}
     clk = clocks.stop() if clocks else None
 
+    # the only cross-rank step of the path: the final host gather of the host-consumed results (untimed)
+    from heterofusionrcnn_b200 import shard
+
+    fin = chain.run_chain(resident, cfg, overlap=overlap)
+    torch.cuda.synchronize()
+    gathered = shard.gather_to_host({"nms_keep": fin["nms_keep"].cpu().numpy(), "nms_num": fin["nms_num"].cpu().numpy()},
+                                    rank, world)
+    if rank == 0:
+        total = shard.concat_scene_results(gathered)
+        assert total["nms_keep"].shape == (args.batch * n_gpus, cfg.post_nms), total["nms_keep"].shape
+    del fin
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
