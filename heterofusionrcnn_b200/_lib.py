@@ -28,6 +28,7 @@ SIGNATURES = {
     "hf_farthest_point_sample": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_fps_set_cluster": (None, [_c_int]),
     "hf_fps_set_threads": (None, [_c_int]),
+    "hf_fps_set_variant": (None, [_c_int, _c_int, _c_int]),
     "hf_gather_point": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_query_ball_point": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_group_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),

@@ -19,6 +19,9 @@
 #include "common.cuh"
 
 namespace hf {
+// fps_bucket.cu: the bucket-pruned kernel (default for clouds it covers)
+int fps_bucket_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int w_req, int j_req);
+
 namespace {
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -301,6 +304,7 @@ int launch_fps(int b, int n, int m, const float *inp, int *out, cudaStream_t str
 }
 
 int g_threads_override = 0;
+int g_algo = 0, g_bucket_w = 0, g_bucket_j = 0;  // hf_fps_set_variant
 
 template <int CLUSTER>
 int dispatch_pts(int per_cta, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {
@@ -327,6 +331,11 @@ int dispatch_pts(int per_cta, int b, int n, int m, const float *inp, int *out, c
 
 extern "C" void hf_fps_set_cluster(int cluster) { hf::g_cluster_override = cluster; }
 extern "C" void hf_fps_set_threads(int threads) { hf::g_threads_override = threads; }
+extern "C" void hf_fps_set_variant(int algo, int warps, int buckets_per_warp) {
+    hf::g_algo = algo;
+    hf::g_bucket_w = warps;
+    hf::g_bucket_j = buckets_per_warp;
+}
 
 extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
                                         hf_stream_t stream) {
@@ -336,6 +345,17 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
     HF_REQUIRE(inp && out, "FarthestPointSample: null pointer");
     if (b == 0) return HF_OK;
     cudaStream_t s = (cudaStream_t)stream;
+
+    // The bucket-pruned kernel (fps_bucket.cu) is exact and touches ~1% of the cloud per
+    // iteration, but its per-iteration dependent chain (test -> bucket -> warp arg-max ->
+    // resolve -> exchange) currently costs 1.4k cycles against 1.2k for the plain kernel at
+    // n = 16384 (profiles/r1_fps_bucket_notes.md), so it is opt-in (hf_fps_set_variant(2,..)).
+    if (g_algo == 2) {
+        int rc = fps_bucket_dispatch(b, n, m, inp, out, s, g_bucket_w, g_bucket_j);
+        if (rc == HF_ERR_UNSUPPORTED)
+            set_error("FarthestPointSample: bucket kernel has no shape for n=%d warps=%d buckets/warp=%d", n, g_bucket_w, g_bucket_j);
+        return rc;
+    }
 
     // Cluster size: as many CTAs per scene as the GPU can co-schedule for this batch, but
     // not so many that a CTA holds < 1024 points (then the DSMEM exchange costs more than

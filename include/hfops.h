@@ -57,6 +57,10 @@ int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp,
 void hf_fps_set_cluster(int cluster);
 /* Tuning override for the FPS CTA size (256 or 512 threads, 0 = heuristic). */
 void hf_fps_set_threads(int threads);
+/* Tuning override for the FPS algorithm: algo 0 = heuristic, 1 = plain on-chip kernel
+ * (every point every iteration), 2 = bucket-pruned kernel with `warps` x `buckets_per_warp`
+ * buckets of 32 points per CTA (0,0 = heuristic shape).  Results are identical. */
+void hf_fps_set_variant(int algo, int warps, int buckets_per_warp);
 
 /* Replaces gatherpointLauncher(b,n,m,inp,idx,out), sampling/tf_sampling_g.cu:206.
  * inp (b,n,3), idx (b,m) -> out (b,m,3). */

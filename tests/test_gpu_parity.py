@@ -66,6 +66,51 @@ def test_fps_every_cluster_shape(cuda, oracle, cluster):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("n,m,dup,w,j", [(16384, 700, 3000, 16, 32), (16000, 300, 0, 32, 16), (8192, 300, 0, 8, 32),
+                                         (8000, 300, 500, 16, 16), (7000, 200, 0, 32, 8), (4096, 512, 0, 4, 32),
+                                         (4096, 512, 1000, 8, 16), (4000, 256, 0, 16, 8), (3000, 256, 0, 32, 4),
+                                         (2048, 256, 0, 4, 16), (2000, 256, 0, 8, 8), (1500, 200, 100, 16, 4),
+                                         (2048, 128, 0, 32, 2), (1024, 256, 0, 4, 8), (1024, 256, 0, 8, 4),
+                                         (1000, 128, 0, 16, 2), (512, 128, 0, 4, 4), (500, 64, 0, 8, 2),
+                                         (300, 64, 0, 16, 1), (256, 64, 0, 2, 4), (200, 300, 0, 4, 2), (37, 16, 0, 8, 1),
+                                         (1, 4, 0, 2, 4), (20000, 300, 0, 16, 32), (40000, 300, 3000, 16, 32),
+                                         (30000, 256, 0, 32, 16), (60000, 256, 0, 32, 16), (100000, 256, 0, 16, 32),
+                                         (131072, 200, 9000, 32, 16), (12000, 256, 0, 16, 16), (30000, 256, 0, 16, 16),
+                                         (65536, 256, 8000, 16, 16), (33000, 200, 0, 0, 0)])
+def test_fps_bucket_kernel_shapes(cuda, oracle, n, m, dup, w, j):
+    """Every instantiated shape of the bucket-pruned kernel (fps_bucket.cu), incl. clusters, ragged
+    sizes, duplicate-padded clouds (exact ties) and m > n, against the oracle."""
+    from heterofusionrcnn_b200 import _lib
+
+    xyz, _ = synthetic.make_scans(21 + n + m, 2, n, duplicate_pad=dup)
+    want = oracle.farthest_point_sample(m, xyz)
+    _lib.load().hf_fps_set_variant(2, w, j)
+    try:
+        got = N(farthest_point_sample(m, T(xyz, cuda)))
+    finally:
+        _lib.load().hf_fps_set_variant(0, 0, 0)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("n,m", [(16384, 4096), (65536, 16384)])
+def test_fps_bucket_equals_plain_kernel_full_size(cuda, n, m):
+    """BASELINE config 2 / config 5 sizes: the pruned kernel and the plain every-point kernel
+    (itself pinned against the oracle and the reference kernel) give identical indices."""
+    from heterofusionrcnn_b200 import _lib
+
+    xyz, _ = synthetic.make_scans(77, 2, n, duplicate_pad=n // 8)
+    x = T(xyz, cuda)
+    lib = _lib.load()
+    try:
+        lib.hf_fps_set_variant(1, 0, 0)
+        plain = farthest_point_sample(m, x)
+        lib.hf_fps_set_variant(2, 0, 0)
+        bucket = farthest_point_sample(m, x)
+    finally:
+        lib.hf_fps_set_variant(0, 0, 0)
+    assert torch.equal(plain, bucket)
+
+
 @needs_ref
 def test_fps_matches_reference_kernel_full_size(cuda):
     """BASELINE config 2 size, against the reference's own kernel on this GPU (ties included)."""

@@ -41,6 +41,7 @@ def main():
             if True:
                 if n // max(cluster, 1) > 8192 and cluster != 0:
                     continue
+                lib.hf_fps_set_variant(1, 0, 0)  # plain on-chip kernel
                 lib.hf_fps_set_cluster(cluster)
                 lib.hf_fps_set_threads(threads)
                 try:
@@ -56,6 +57,24 @@ def main():
                     n, m, b, variant, cluster, threads, ms, ms * 1e6 / (m - 1), same))
         lib.hf_fps_set_cluster(0)
         lib.hf_fps_set_threads(0)
+        lib.hf_fps_set_variant(0, 0, 0)
+        # bucket-pruned kernel (fps_bucket.cu): every shape whose capacity covers the cloud
+        per = n
+        while per > 16384:
+            per = (per + 1) // 2
+        for w, j in [(0, 0)] + [(w, j) for w in (2, 4, 8, 16, 32) for j in (1, 2, 4, 8, 16, 32)]:
+            if w and (w * 32 * j < per or w * 32 * j > 4 * max(per, 256)):
+                continue
+            lib.hf_fps_set_variant(2, w, j)
+            try:
+                out = farthest_point_sample(m, x)
+                ms = timeit(lambda: farthest_point_sample(m, x))
+            except Exception as ex:  # noqa: BLE001
+                continue
+            finally:
+                lib.hf_fps_set_variant(0, 0, 0)
+            print("n=%6d m=%5d b=%2d bucket w=%2d j=%2d  %8.4f ms  %7.1f ns/iter  same=%s" % (
+                n, m, b, w, j, ms, ms * 1e6 / (m - 1), bool(torch.equal(out, ref))))
 
 
 if __name__ == "__main__":
