@@ -39,6 +39,8 @@ SIGNATURES = {
     "hf_compute_bev_iou": (_c_int, [_c_int, _ptr, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_oriented_nms_mask": (_c_int, [_ptr, _ptr, _c_int, _c_float, _c_int, _ptr]),
     "hf_oriented_nms_workspace_bytes": (_size_t, [_c_int, _c_int]),
+    "hf_nms_set_spatial_sort": (None, [_c_int]),
+    "hf_oriented_nms_last_pair_count": (ctypes.c_longlong, [_c_int, _c_int, _ptr, _ptr]),
     "hf_oriented_nms": (_c_int, [_ptr, _c_int, _c_int, _c_float, _ptr, _ptr, _ptr, _size_t, _ptr]),
 }
 

@@ -272,4 +272,4 @@ def run_chain(dev, cfg, probe=None, overlap=True):
 
 def chain_launches(cfg):
     """Kernels of libhfops launched by one run_chain call."""
-    return 4 * 5 + 4 * 2 + (1 if cfg.with_crop else 0) + (4 if cfg.with_nms else 0)
+    return 4 * 5 + 4 * 2 + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)

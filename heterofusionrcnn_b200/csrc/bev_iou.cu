@@ -251,10 +251,17 @@ __global__ void __launch_bounds__(kBevThreads)
 // The 64x64-tile kernel above spends its time in the polygon clip of every pair whose
 // bounding circles touch (7% of the pairs of a 9000-proposal scene).  For the
 // *thresholded* question "iou > thresh" far fewer pairs need the exact clip:
-//   prepare  one thread per box: the per-box record of precompute_box (sin/cos, rotated
-//            corners, padded radius) + a compact 8-float "lite" record, written once per
-//            scene instead of once per tile;
-//   filter   per (row tile, chunk of column tiles): stage 1 bounding circles (column box in
+//   sort     one CTA per scene: Morton code of every box centre, bitonic sort in shared memory
+//            -> a spatial permutation.  Score order matters only to the sweep; WHICH pairs
+//            overlap does not depend on the order they are enumerated in, and in Morton order
+//            a tile of 64 consecutive boxes is spatially compact;
+//   prepare  one thread per box, in sorted order: the per-box record of precompute_box
+//            (sin/cos, rotated corners, padded radius) + a compact 8-float "lite" record,
+//            written once per scene instead of once per tile, + per 64-box tile the bounding
+//            rectangle of its padded circles;
+//   filter   per row tile: column tiles whose bounding rectangle is disjoint from the row
+//            tile's cannot hold a touching pair and are skipped whole (~95% of the tile pairs
+//            of a 9000-proposal scene).  For the others: stage 1 bounding circles (column box in
 //            registers, row boxes broadcast from shared memory, warp-private ballot
 //            compaction, no atomics); stage 2 a separating-axis UPPER BOUND on the overlap
 //            (intersection is contained in A cut by B's extent along A's axes and vice
@@ -262,48 +269,212 @@ __global__ void __launch_bounds__(kBevThreads)
 //            below the threshold have bit 0 without clipping.  Survivors are appended to a
 //            global pair list (one atomicAdd per CTA flush);
 //   clip     one thread per surviving pair, full warps, both records in registers; exact
-//            reference arithmetic (overlap_pre); atomicOr of the suppression bit;
+//            reference arithmetic (overlap_pre) with the box of lower ORIGINAL index as the
+//            reference's `a` (the clip is not bit-symmetric in its arguments); atomicOr of
+//            the suppression bit at the pair's original (score-order) indices;
 //   sweep    see nms_sweep_kernel2.
 // The bound only ever removes pairs whose exact IoU is below the threshold by a margin
 // (1e-3 relative + float slack), so the mask — and the keep list — are unchanged.
 // ===================================================================================
 constexpr int kRec = 24;    // full record: kPre floats + hx, hy, area, pad (96 B, float4 aligned)
-constexpr int kLite = 8;    // cx, cy, radius, hx, hy, cos, sin, area
-constexpr int kLitePad = 9; // shared-memory row stride (conflict-free for 32 consecutive boxes)
-constexpr int kChunk = 8;   // column tiles per filter CTA
-constexpr int kList2Cap = 8192;
+constexpr int kLite = 8;    // cx, cy, radius, hx, hy, cos, sin, mb (see lite_area / cheap_passes)
 
-__global__ void __launch_bounds__(256)
-    nms_prepare_kernel(long long total, const float *__restrict__ boxes, float *__restrict__ rec,
-                       float *__restrict__ lite) {
-    long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= total) return;
-    float pre[kRec];
-    precompute_box(boxes + g * 5, pre);
-    float hx = (pre[2] - pre[0]) * 0.5f, hy = (pre[3] - pre[1]) * 0.5f;
-    pre[20] = hx;
-    pre[21] = hy;
-    pre[22] = (pre[2] - pre[0]) * (pre[3] - pre[1]);
-    pre[23] = 0.f;
-    float4 *o = reinterpret_cast<float4 *>(rec + g * kRec);
-#pragma unroll
-    for (int k = 0; k < kRec / 4; ++k) o[k] = make_float4(pre[4 * k], pre[4 * k + 1], pre[4 * k + 2], pre[4 * k + 3]);
-    float4 *l = reinterpret_cast<float4 *>(lite + g * kLite);
-    l[0] = make_float4(pre[5], pre[6], pre[19], hx);
-    l[1] = make_float4(hy, pre[7], pre[8], pre[22]);
+constexpr int kSortThreads = 1024;
+constexpr int kSortCells = 4096;  // 64 x 64 grid over the bounding rectangle of the centres, Morton order
+
+__device__ __forceinline__ uint32_t spread6(uint32_t v) {  // 6 bits -> every second bit
+    v &= 63u;
+    v = (v | (v << 4)) & 0x0F0Fu;
+    v = (v | (v << 2)) & 0x3333u;
+    v = (v | (v << 1)) & 0x5555u;
+    return v;
 }
 
-// Separating-axis upper bound.  A, B: lite records.  true = the exact test iou > thresh is
-// certainly false (overlap bound too small), so the pair needs no clip.
+// perm[scene][p] = original index of the box at sorted position p: a counting sort of the box
+// centres into a 64 x 64 grid walked in Morton order (one CTA per scene, any boxes_num).
+// Positions inside one cell are handed out by atomicAdd, so the permutation may differ from
+// run to run; the NMS result does not depend on it (see clip_pair).  tmp: boxes_num u64 per scene.
+__global__ void __launch_bounds__(kSortThreads)
+    nms_sort_kernel(int boxes_num, const float *__restrict__ boxes, int *__restrict__ perm,
+                    unsigned long long *__restrict__ tmp_all) {
+    __shared__ int hist[kSortCells];
+    __shared__ float red[4][32];
+    __shared__ int wsum[32];
+    const int scene = blockIdx.x, t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const float *sb = boxes + (size_t)scene * boxes_num * 5;
+    unsigned long long *tmp = tmp_all + (size_t)scene * boxes_num;
+    int *pp = perm + (size_t)scene * boxes_num;
+    // ---- bounding rectangle of the centres (fminf/fmaxf skip NaN) ----
+    float x0 = INFINITY, y0 = INFINITY, x1 = -INFINITY, y1 = -INFINITY;
+    for (int i = t; i < boxes_num; i += kSortThreads) {
+        const float cx = (sb[i * 5] + sb[i * 5 + 2]) * 0.5f, cy = (sb[i * 5 + 1] + sb[i * 5 + 3]) * 0.5f;
+        x0 = fminf(x0, cx); y0 = fminf(y0, cy);
+        x1 = fmaxf(x1, cx); y1 = fmaxf(y1, cy);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        x0 = fminf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
+        y0 = fminf(y0, __shfl_xor_sync(0xffffffffu, y0, o));
+        x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+        y1 = fmaxf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+    }
+    if (lane == 0) {
+        red[0][warp] = x0; red[1][warp] = y0; red[2][warp] = x1; red[3][warp] = y1;
+    }
+    for (int c = t; c < kSortCells; c += kSortThreads) hist[c] = 0;
+    __syncthreads();
+    x0 = red[0][lane]; y0 = red[1][lane]; x1 = red[2][lane]; y1 = red[3][lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        x0 = fminf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
+        y0 = fminf(y0, __shfl_xor_sync(0xffffffffu, y0, o));
+        x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+        y1 = fmaxf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+    }
+    const float ext = fmaxf(x1 - x0, y1 - y0);  // square cells
+    const float inv = (ext > 0.f && ext < 1e30f) ? 63.999f / ext : 0.f;
+    // ---- cell of every box, rank inside the cell ----
+    for (int i = t; i < boxes_num; i += kSortThreads) {
+        const float cx = (sb[i * 5] + sb[i * 5 + 2]) * 0.5f, cy = (sb[i * 5 + 1] + sb[i * 5 + 3]) * 0.5f;
+        const uint32_t qx = min(__float2uint_rz(fmaxf((cx - x0) * inv, 0.f)), 63u);  // NaN -> 0
+        const uint32_t qy = min(__float2uint_rz(fmaxf((cy - y0) * inv, 0.f)), 63u);
+        const uint32_t cell = spread6(qx) | (spread6(qy) << 1);
+        const int r = atomicAdd(&hist[cell], 1);
+        tmp[i] = ((unsigned long long)cell << 32) | (unsigned)r;
+    }
+    __syncthreads();
+    // ---- exclusive scan of the 4096 counts: 4 per thread, warp scan, scan of the warp sums ----
+    int c0 = hist[4 * t], c1 = hist[4 * t + 1], c2 = hist[4 * t + 2], c3 = hist[4 * t + 3];
+    const int mine = c0 + c1 + c2 + c3;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int wincl = wsum[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, wincl, o);
+        if (lane >= o) wincl += v;
+    }
+    const int wbase = __shfl_sync(0xffffffffu, wincl, warp) - wsum[warp];
+    const int e0 = wbase + incl - mine;
+    __syncthreads();  // every thread has read its counts
+    hist[4 * t] = e0;
+    hist[4 * t + 1] = e0 + c0;
+    hist[4 * t + 2] = e0 + c0 + c1;
+    hist[4 * t + 3] = e0 + c0 + c1 + c2;
+    __syncthreads();
+    for (int i = t; i < boxes_num; i += kSortThreads) {
+        const unsigned long long v = tmp[i];
+        pp[hist[(uint32_t)(v >> 32)] + (int)(uint32_t)v] = i;
+    }
+}
+
+// One 64-thread CTA per tile of 64 boxes in sorted order (perm == nullptr: identity).
+// grid = (cb, scenes).  tile_box = bounding rectangle of the tile's padded circles, half_box =
+// the same for each half (32 boxes) of the tile: a tile that straddles two clusters is large,
+// its halves mostly are not.
+__global__ void __launch_bounds__(kTile)
+    nms_prepare_kernel(int boxes_num, const float *__restrict__ boxes, const int *__restrict__ perm,
+                       float *__restrict__ rec, float *__restrict__ lite, float4 *__restrict__ tile_box,
+                       float4 *__restrict__ half_box, float pad_scale) {
+    __shared__ float4 wbox[2];
+    const int cb = (boxes_num + kTile - 1) / kTile;
+    const int scene = blockIdx.y, tile = blockIdx.x, t = threadIdx.x;
+    const int p = tile * kTile + t;
+    float bx0 = INFINITY, by0 = INFINITY, bx1 = -INFINITY, by1 = -INFINITY;
+    if (p < boxes_num) {
+        const size_t g = (size_t)scene * boxes_num + p;
+        const int src = perm ? perm[g] : p;
+        float pre[kRec];
+        precompute_box(boxes + ((size_t)scene * boxes_num + src) * 5, pre);
+        const float hx = (pre[2] - pre[0]) * 0.5f, hy = (pre[3] - pre[1]) * 0.5f;
+        pre[20] = hx;
+        pre[21] = hy;
+        pre[22] = (pre[2] - pre[0]) * (pre[3] - pre[1]);
+        pre[23] = 0.f;
+        float4 *o = reinterpret_cast<float4 *>(rec + g * kRec);
+#pragma unroll
+        for (int k = 0; k < kRec / 4; ++k) o[k] = make_float4(pre[4 * k], pre[4 * k + 1], pre[4 * k + 2], pre[4 * k + 3]);
+        float4 *l = reinterpret_cast<float4 *>(lite + g * kLite);
+        l[0] = make_float4(pre[5], pre[6], pre[19], hx);
+        l[1] = make_float4(hy, pre[7], pre[8], 5e-5f + 4e-6f * (fabsf(pre[5]) + fabsf(pre[6]) + pre[19]));
+        // thresh >= 0.5: centres of a passing pair are within rscale * min(r_a, r_b) <= rscale * (r_a + r_b)/2
+        bx0 = pre[5] - pre[19] * pad_scale;
+        by0 = pre[6] - pre[19] * pad_scale;
+        bx1 = pre[5] + pre[19] * pad_scale;
+        by1 = pre[6] + pre[19] * pad_scale;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        bx0 = fminf(bx0, __shfl_xor_sync(0xffffffffu, bx0, o));
+        by0 = fminf(by0, __shfl_xor_sync(0xffffffffu, by0, o));
+        bx1 = fmaxf(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+        by1 = fmaxf(by1, __shfl_xor_sync(0xffffffffu, by1, o));
+    }
+    if ((t & 31) == 0) {
+        wbox[t >> 5] = make_float4(bx0, by0, bx1, by1);
+        half_box[((size_t)scene * cb + tile) * 2 + (t >> 5)] = make_float4(bx0, by0, bx1, by1);  // boxes 32h .. 32h+31 of the tile
+    }
+    __syncthreads();
+    if (t == 0) {
+        const float4 a = wbox[0], b = wbox[1];
+        tile_box[(size_t)scene * cb + tile] =
+            make_float4(fminf(a.x, b.x), fminf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w));
+    }
+}
+
+// How far apart the centres of a pair with iou > tq >= 0.5 can be, as a fraction of the smaller
+// of the two bounding radii.  From the reflection bound (cheap_passes (3)) and the area-ratio
+// bound (1): 4 (ahx-|du|)(ahy-|dv|) >= 2|I| - |B| >= |A| (2 tq - 1)/tq, so |du| <= ahx (1 - g) and
+// |dv| <= ahy (1 - g) with g = (2 tq - 1)/tq, i.e. |offset| <= (1 - g) * half-diagonal, for both
+// boxes.  tq = 0.5 gives 1 (each centre inside the other box), tq = 0.85 gives 0.18.
+__host__ __device__ __forceinline__ float nms_rscale(float tq) { return tq >= 0.5f ? (1.f - tq) / tq : 1.f; }
+
+// Lite record (8 floats, 32 B): cx, cy, padded radius, hx, hy, cos, sin, mb.
+// mb = half of the slack a test on a pair needs for float error of the projections
+// (coordinates ~1e2 m -> ~1e-5) and the reference's 1e-5 inclusion margin: m = mb_a + mb_b.
+__device__ __forceinline__ float lite_area(const float *L) { return 4.f * L[3] * L[4]; }
+
+// Rotation-free necessary conditions for iou > thresh (stage 1).  a*/b*: the two lite records,
+// (dx,dy) = B's centre - A's; tq = thresh minus margin (> 0); tight = tq >= 0.5.
+// Every comparison is written so that NaN input PASSES (the exact clip then decides).
+//  (1) iou <= min area / max area.
+//  (2) tight: the intersection is a convex subset of each (centrally symmetric) box holding more
+//      than half of its area, so it contains both centres: each centre lies inside the other box.
+//  (3) reflection bound: with I = A n B and s the point reflection about B's centre, s(I) is inside
+//      B too, so |I n s(I)| >= 2|I| - |B|; and I n s(I) lies in A n s(A), where s(A) is A shifted by
+//      twice the centre offset: |A n s(A)| = 4 (ahx-|du|)+ (ahy-|dv|)+ in A's frame.  Hence
+//      |I| <= (|B| + 4 (ahx-|du|)+ (ahy-|dv|)+) / 2, and the same with the roles swapped.
+__device__ __forceinline__ bool cheap_passes(float dx, float dy, float ahx, float ahy, float aca, float asa, float aar,
+                                             float bhx, float bhy, float bca, float bsa, float bar, float m, float tq,
+                                             bool tight) {
+    // centre offset in A's frame (local x axis = (cos,-sin), local y axis = (sin,cos); :92-96) and in B's
+    const float du = fabsf(dx * aca - dy * asa), dv = fabsf(dx * asa + dy * aca);
+    const float du2 = fabsf(dx * bca - dy * bsa), dv2 = fabsf(dx * bsa + dy * bca);
+    bool ok = !(fminf(aar, bar) * 1.00001f + m < tq * fmaxf(aar, bar));
+    if (tight) ok = ok && !(du > ahx + m || dv > ahy + m || du2 > bhx + m || dv2 > bhy + m);
+    const float ra = 4.f * fmaxf(ahx - du + m, 0.f) * fmaxf(ahy - dv + m, 0.f);
+    const float rb = 4.f * fmaxf(bhx - du2 + m, 0.f) * fmaxf(bhy - dv2 + m, 0.f);
+    const float ubr = fminf(0.5f * (bar + ra), 0.5f * (aar + rb)) * 1.00001f + m;
+    const float dr = aar + bar - ubr;
+    return ok && !(dr > 0.f && ubr < tq * dr);
+}
+
+// Separating-axis upper bound (stage 2).  A, B: lite records.  true = the exact test iou > thresh
+// is certainly false (overlap bound too small), so the pair needs no clip.
 __device__ __forceinline__ bool sat_rejects(const float *A, const float *B, float tq) {
-    const float acx = A[0], acy = A[1], ahx = A[3], ahy = A[4], aca = A[5], asa = A[6], aar = A[7];
-    const float bcx = B[0], bcy = B[1], bhx = B[3], bhy = B[4], bca = B[5], bsa = B[6], bar = B[7];
+    const float acx = A[0], acy = A[1], ahx = A[3], ahy = A[4], aca = A[5], asa = A[6], aar = lite_area(A);
+    const float bcx = B[0], bcy = B[1], bhx = B[3], bhy = B[4], bca = B[5], bsa = B[6], bar = lite_area(B);
     if (!(ahx > 0.f && ahy > 0.f && bhx > 0.f && bhy > 0.f)) return false;  // degenerate input: always clip
     const float dx = bcx - acx, dy = bcy - acy;
+    const float m = A[7] + B[7];
     const float cd = fabsf(aca * bca + asa * bsa), sd = fabsf(asa * bca - aca * bsa);
-    // slack: float error of the projections (coordinates ~1e2 m -> ~1e-5) + the 1e-5 inclusion margin
-    const float m = 1e-4f + 4e-6f * (fabsf(acx) + fabsf(acy) + fabsf(bcx) + fabsf(bcy) + A[2] + B[2]);
-    // in A's frame: local x axis = (cos,-sin), local y axis = (sin,cos)  (rotate_around_center, :92-96)
+    // in A's frame: the intersection is contained in A cut by B's extent along A's axes
     float du = dx * aca - dy * asa, dv = dx * asa + dy * aca;
     float eu = bhx * cd + bhy * sd + m, ev = bhx * sd + bhy * cd + m;
     float ou = fminf(ahx, du + eu) - fmaxf(-ahx, du - eu);
@@ -322,9 +493,96 @@ __device__ __forceinline__ bool sat_rejects(const float *A, const float *B, floa
     return ub < tq * denom;  // iou <= ub/denom < tq <= thresh - margin
 }
 
-// Exact test of one pair on full records held in registers; sets the mask bit.
-__device__ __forceinline__ void clip_pair(const float *__restrict__ rec, unsigned long long *__restrict__ mask,
-                                          int cb, int row, int col, float thresh) {
+// Liang-Barsky: parameter range [t0,t1] of the segment p + t*d, t in [0,1], inside the
+// axis-aligned rectangle [-hx,hx] x [-hy,hy].  Empty when t0 >= t1.
+__device__ __forceinline__ void clip_to_rect(float px, float py, float dx, float dy, float hx, float hy, float &t0,
+                                             float &t1) {
+    // a (nearly) parallel segment gets a huge finite slope: inside -> (-huge, +huge), outside -> empty
+    const float ix = fabsf(dx) > 1e-12f ? __frcp_rn(dx) : 1e12f;
+    const float iy = fabsf(dy) > 1e-12f ? __frcp_rn(dy) : 1e12f;
+    const float ax = (-hx - px) * ix, bx = (hx - px) * ix;
+    const float ay = (-hy - py) * iy, by = (hy - py) * iy;
+    t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), 0.f);
+    t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), 1.f);
+}
+
+// Area of the intersection of two rotated rectangles by Green's theorem: the boundary of A n B
+// is made of the parts of A's edges inside B and the parts of B's edges inside A; each part is
+// one segment (convexity) found by clipping against an axis-aligned rectangle in the other
+// box's own frame, and contributes cross(P, Q)/2, all evaluated in A's frame.  Coincident edges
+// are counted twice, i.e. the result can only OVER-estimate — which is the safe side for its
+// one use, an upper bound that spares the exact (reference-arithmetic) clip.  A, B: lite records.
+__device__ __forceinline__ float green_overlap(const float *A, const float *B) {
+    const float ahx = A[3], ahy = A[4], aca = A[5], asa = A[6];
+    const float bhx = B[3], bhy = B[4], bca = B[5], bsa = B[6];
+    const float ox = B[0] - A[0], oy = B[1] - A[1];  // world offset of B's centre from A's
+    // relative rotation: B-local -> world is [[c,s],[-s,c]], world -> A-local is its transpose for A
+    const float rc = bca * aca + bsa * asa, rs = bsa * aca - bca * asa;
+    // B-local (u,v) -> A-local: ( u*rc + v*rs + tx, -u*rs + v*rc + ty ),  t = world->A-local of the offset
+    const float tx = ox * aca - oy * asa, ty = ox * asa + oy * aca;
+    // A-local (u,v) -> B-local: inverse rotation, and B's centre maps to the origin
+    const float sx = -(tx * rc - ty * rs), sy = -(tx * rs + ty * rc);
+    const float su[4] = {-1.f, 1.f, 1.f, -1.f}, sv[4] = {-1.f, -1.f, 1.f, 1.f};  // counter-clockwise corners
+    float acc = 0.f;
+    float bax[4], bay[4], abx[4], aby[4];  // B's corners in A's frame, A's corners in B's frame
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float u = su[k] * bhx, v = sv[k] * bhy;
+        bax[k] = u * rc + v * rs + tx;
+        bay[k] = -u * rs + v * rc + ty;
+        const float p = su[k] * ahx, q = sv[k] * ahy;
+        abx[k] = p * rc - q * rs + sx;
+        aby[k] = p * rs + q * rc + sy;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int k1 = (k + 1) & 3;
+        float t0, t1;
+        // edge k of B, clipped by A (in A's frame), integrated in A's frame
+        float dx = bax[k1] - bax[k], dy = bay[k1] - bay[k];
+        clip_to_rect(bax[k], bay[k], dx, dy, ahx, ahy, t0, t1);
+        if (t1 > t0) {
+            const float px = bax[k] + t0 * dx, py = bay[k] + t0 * dy, qx = bax[k] + t1 * dx, qy = bay[k] + t1 * dy;
+            acc += px * qy - py * qx;
+        }
+        // edge k of A, clipped by B (parameters from B's frame), integrated in A's frame
+        dx = abx[k1] - abx[k];
+        dy = aby[k1] - aby[k];
+        clip_to_rect(abx[k], aby[k], dx, dy, bhx, bhy, t0, t1);
+        if (t1 > t0) {
+            const float ex = (su[k1] - su[k]) * ahx, ey = (sv[k1] - sv[k]) * ahy;
+            const float px = su[k] * ahx + t0 * ex, py = sv[k] * ahy + t0 * ey, qx = su[k] * ahx + t1 * ex, qy = sv[k] * ahy + t1 * ey;
+            acc += px * qy - py * qx;
+        }
+    }
+    return 0.5f * acc;
+}
+
+// true = the exact test iou > thresh is certainly false: even an over-estimate of the true
+// intersection area (+1e-4 relative, +1e-4 m^2 for float error) stays below the threshold.
+// The reference's own polygon (edge crossings + contained corners) lies inside the true
+// intersection up to its 1e-5 margins, so its area cannot exceed the bound either.
+__device__ __forceinline__ bool area_rejects(const float *A, const float *B, float tq) {
+    if (!(tq > 0.f) || !(A[3] > 0.f && A[4] > 0.f && B[3] > 0.f && B[4] > 0.f)) return false;
+    const float est = green_overlap(A, B);
+    if (!(est == est)) return false;  // NaN: let the exact clip decide
+    const float aar = lite_area(A), bar = lite_area(B);
+    const float ub = fminf(est * 1.0001f + 1e-4f, fminf(aar, bar) * 1.00001f + 1e-4f);
+    const float denom = aar + bar - ub;
+    if (!(denom > 0.f)) return false;
+    return ub < tq * denom;
+}
+
+// Exact test of one pair on full records held in registers; sets the mask bit.  row/col are
+// SORTED positions; the reference's (a, b) = (lower, higher) ORIGINAL index, and the bit lives
+// at mask[a][b].
+__device__ __forceinline__ void clip_pair(const float *__restrict__ rec, const int *__restrict__ perm,
+                                          unsigned long long *__restrict__ mask, int cb, int row, int col, float thresh) {
+    int oa = perm ? __ldg(perm + row) : row, ob = perm ? __ldg(perm + col) : col;
+    if (oa > ob) {
+        int tmp = oa; oa = ob; ob = tmp;
+        tmp = row; row = col; col = tmp;
+    }
     float a[kRec], b[kRec];
     const float4 *pa = reinterpret_cast<const float4 *>(rec + (size_t)row * kRec);
     const float4 *pb = reinterpret_cast<const float4 *>(rec + (size_t)col * kRec);
@@ -335,123 +593,212 @@ __device__ __forceinline__ void clip_pair(const float *__restrict__ rec, unsigne
         b[4 * k] = vb.x; b[4 * k + 1] = vb.y; b[4 * k + 2] = vb.z; b[4 * k + 3] = vb.w;
     }
     float s = overlap_pre(a, b);
-    if (iou_from_overlap(a, b, s) > thresh) atomicOr(&mask[(size_t)row * cb + (col >> 6)], 1ull << (col & 63));
+    if (iou_from_overlap(a, b, s) > thresh) atomicOr(&mask[(size_t)oa * cb + (ob >> 6)], 1ull << (ob & 63));
 }
 
-__device__ __noinline__ void clip_pair_overflow(const float *rec, unsigned long long *mask, int cb, int row, int col,
-                                                float thresh) {
-    clip_pair(rec, mask, cb, row, col, thresh);
+__device__ __noinline__ void clip_pair_overflow(const float *rec, const int *perm, unsigned long long *mask, int cb,
+                                                int row, int col, float thresh) {
+    clip_pair(rec, perm, mask, cb, row, col, thresh);
 }
 
 struct NmsLists {
-    unsigned long long *pairs;  // [cap] (scene << 48) | (row << 24) | col
+    unsigned long long *pairs;  // [cap] (scene << 48) | (row << 24) | col, sorted positions
     unsigned long long *count;  // pairs appended so far (may exceed cap: the excess was clipped inline)
     unsigned long long cap;
 };
 
-// grid = (ceil(cb/kChunk), cb, scenes); CTA (chunk, rb) handles row tile rb against column tiles
-// ct in [max(rb, chunk*kChunk), (chunk+1)*kChunk).
-__global__ void __launch_bounds__(256, 4)
+// grid = (cb, scenes); CTA rb handles row tile rb (sorted order) against the column tiles
+// ct >= rb whose bounding rectangle touches its own.  After the tile list is built the eight
+// warps run without any CTA barrier: warp w owns the block (rows 16*(w>>1) .. +16) x (columns
+// 32*(w&1) .. +32) of every listed tile, keeps its 32 column records in registers (one per
+// lane, straight from global memory) and reads the row records as shared-memory broadcasts.
+//   stage 1  centre distance (see nms_rscale), ballot-compacted into a warp-private list;
+//   stage 2  rotation-free bounds (cheap_passes), then the separating-axis bound, full warps;
+//   stage 3  exact-area bound (green_overlap) on what is left, batched 32 at a time through a
+//            warp-private queue; the survivors go to the global pair list for the exact clip.
+constexpr int kTileListCap = 256;
+constexpr int kWarpQueue = 64;  // <= 31 left over + 32 from one stage-2 batch
+__global__ void __launch_bounds__(256, 3)
     nms_filter_kernel(int boxes_num, float thresh, const float *__restrict__ rec_all, const float *__restrict__ lite_all,
-                      unsigned long long *__restrict__ mask_all, NmsLists lists) {
-    __shared__ float rowl[kTile * kLitePad];
-    __shared__ float coll[kTile * kLitePad];
+                      const float4 *__restrict__ tile_box_all, const float4 *__restrict__ half_box_all,
+                      const int *__restrict__ perm_all, unsigned long long *__restrict__ mask_all, NmsLists lists) {
+    __shared__ __align__(16) float rowl[kTile * kLite];
     __shared__ unsigned short list1[8][512];
-    __shared__ unsigned int list2[kList2Cap];
-    __shared__ int n2s;
-    __shared__ unsigned long long flush_base;
+    __shared__ unsigned int wq[8][kWarpQueue];
+    __shared__ int tiles[kTileListCap];
+    __shared__ float4 rsubs[4];
+    __shared__ int ntiles;
 
     const int cb = (boxes_num + kTile - 1) / kTile;
-    const int rb = blockIdx.y, scene = blockIdx.z;
-    const int ct_lo = max(rb, (int)blockIdx.x * kChunk), ct_hi = min(cb, ((int)blockIdx.x + 1) * kChunk);
-    if (ct_lo >= ct_hi) return;
+    const int rb = blockIdx.x, scene = blockIdx.y;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const float *lite = lite_all + (size_t)scene * boxes_num * kLite;
     const float *rec = rec_all + (size_t)scene * boxes_num * kRec;
+    const int *perm = perm_all ? perm_all + (size_t)scene * boxes_num : nullptr;
+    const float4 *tbox = tile_box_all + (size_t)scene * cb;
+    const float4 *hbox = half_box_all + (size_t)scene * cb * 2;
     unsigned long long *mask = mask_all + (size_t)scene * boxes_num * cb;
     const int row_size = min(boxes_num - rb * kTile, kTile);
     const float tq = thresh * (1.f - 1e-3f) - 1e-6f;
+    // thresh >= 0.5 (with margin): a pair can only pass if each centre lies inside the other box, so
+    // the centres are no farther apart than the smaller bounding radius (see cheap_passes)
+    const bool tight = tq >= 0.5f;
+    const float rscale = nms_rscale(tq);
 
-    if (t == 0) n2s = 0;
-    for (int w = t; w < kTile * kLite; w += 256) {
-        int bx = w >> 3, f = w & 7;
-        rowl[bx * kLitePad + f] = bx < row_size ? lite[(size_t)(rb * kTile) * kLite + w] : 0.f;
+    for (int w = t; w < kTile * kLite; w += 256) rowl[w] = (w >> 3) < row_size ? lite[(size_t)(rb * kTile) * kLite + w] : 0.f;
+    __syncthreads();
+    // bounding rectangle of the 16 rows this warp tests in stage 1 (rows 16*(warp>>1) .. +16)
+    const int row0 = 16 * (warp >> 1);
+    float4 rsub;
+    {
+        const int i = row0 + (lane & 15);
+        const bool v = i < row_size;
+        const float cx = rowl[i * kLite], cy = rowl[i * kLite + 1], r = rowl[i * kLite + 2] * (tight ? 0.5f * rscale : 1.f);
+        float x0 = v ? cx - r : INFINITY, y0 = v ? cy - r : INFINITY, x1 = v ? cx + r : -INFINITY, y1 = v ? cy + r : -INFINITY;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+            x0 = fminf(x0, __shfl_xor_sync(0xffffffffu, x0, o));
+            y0 = fminf(y0, __shfl_xor_sync(0xffffffffu, y0, o));
+            x1 = fmaxf(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+            y1 = fmaxf(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+        }
+        rsub = make_float4(x0, y0, x1, y1);
+        if (lane == 0 && (warp & 1) == 0) rsubs[warp >> 1] = rsub;
     }
 
-    auto flush = [&]() {  // all threads; list2[0..n2s) -> global pair list (or clipped here when it is full)
-        __syncthreads();
-        const int n2 = n2s;
-        if (n2 > 0) {
-            if (t == 0) flush_base = atomicAdd(lists.count, (unsigned long long)n2);
-            __syncthreads();
-            const unsigned long long base = flush_base;
-            for (int q = t; q < n2; q += 256) {
-                unsigned int e = list2[q];
-                int row = rb * kTile + (int)(e & 63u), col = (int)(e >> 6);
-                if (base + q < lists.cap)
-                    lists.pairs[base + q] = ((unsigned long long)scene << 48) | ((unsigned long long)row << 24) | (unsigned)col;
-                else
-                    clip_pair_overflow(rec, mask, cb, row, col, thresh);
+    // ---- warp-private queue of pairs that passed stage 2 (entry = row-in-tile | sorted col << 6) ----
+    unsigned int *myq = wq[warp];
+    int nq = 0;  // warp-uniform
+    auto drain = [&](int keep_below) {  // stage 3 + output, 32 entries at a time, while nq > keep_below
+        while (nq > keep_below) {
+            const int take = min(nq, 32);
+            const int q = nq - take + lane;
+            bool pass = false;
+            unsigned int e = 0;
+            if (lane < take) {
+                e = myq[q];
+                const int i = (int)(e & 63u), col = (int)(e >> 6);
+                float bl[kLite];
+                const float4 b0 = __ldg(reinterpret_cast<const float4 *>(lite + (size_t)col * kLite));
+                const float4 b1 = __ldg(reinterpret_cast<const float4 *>(lite + (size_t)col * kLite) + 1);
+                bl[0] = b0.x; bl[1] = b0.y; bl[2] = b0.z; bl[3] = b0.w;
+                bl[4] = b1.x; bl[5] = b1.y; bl[6] = b1.z; bl[7] = b1.w;
+                pass = !area_rejects(rowl + i * kLite, bl, tq);
+            }
+            nq -= take;
+            const unsigned bal = __ballot_sync(0xffffffffu, pass);
+            if (bal) {
+                unsigned long long base = 0;
+                if (lane == 0) base = atomicAdd(lists.count, (unsigned long long)__popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0) + __popc(bal & ((1u << lane) - 1u));
+                if (pass) {
+                    const int row = rb * kTile + (int)(e & 63u), col = (int)(e >> 6);
+                    if (base < lists.cap)
+                        lists.pairs[base] = ((unsigned long long)scene << 48) | ((unsigned long long)row << 24) | (unsigned)col;
+                    else
+                        clip_pair_overflow(rec, perm, mask, cb, row, col, thresh);
+                }
             }
         }
-        __syncthreads();
-        if (t == 0) n2s = 0;
-        __syncthreads();
     };
 
-    for (int ct = ct_lo; ct < ct_hi; ++ct) {
-        const int col_size = min(boxes_num - ct * kTile, kTile);
-        __syncthreads();  // previous tile's readers of coll are done
-        for (int w = t; w < kTile * kLite; w += 256) {
-            int bx = w >> 3, f = w & 7;
-            coll[bx * kLitePad + f] = bx < col_size ? lite[(size_t)(ct * kTile) * kLite + w] : 0.f;
-        }
+    const float4 rbox = __ldg(tbox + rb);
+    for (int ct0 = rb; ct0 < cb; ct0 += kTileListCap) {
+        // ---- stage 0: which column tiles can hold a passing pair at all ----
+        __syncthreads();  // the previous pass's readers of tiles[] are done
+        if (t == 0) ntiles = 0;
         __syncthreads();
-        // ---- stage 1: bounding circles.  warp w: columns 32*(w&1)+lane, rows 16*(w>>1) .. +16
-        const int j = 32 * (warp & 1) + lane;
-        const float jcx = coll[j * kLitePad], jcy = coll[j * kLitePad + 1], jr = coll[j * kLitePad + 2];
-        const bool jvalid = j < col_size;
-        const bool diag = ct == rb;
-        int cnt1 = 0;
-        unsigned short *mine = list1[warp];
-#pragma unroll 4
-        for (int k = 0; k < 16; ++k) {
-            const int i = 16 * (warp >> 1) + k;
-            const float dx = rowl[i * kLitePad] - jcx, dy = rowl[i * kLitePad + 1] - jcy, rr = rowl[i * kLitePad + 2] + jr;
-            bool live = jvalid && i < row_size && (!diag || j > i) && !(dx * dx + dy * dy > rr * rr);
-            unsigned bal = __ballot_sync(0xffffffffu, live);
-            if (live) mine[cnt1 + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)((i << 6) | j);
-            cnt1 += __popc(bal);
-        }
-        __syncwarp();
-        // ---- stage 2: separating-axis bound on this warp's survivors
-        for (int q0 = 0; q0 < cnt1; q0 += 32) {
-            const int q = q0 + lane;
-            bool pass = false;
-            unsigned int entry = 0;
-            if (q < cnt1) {
-                const int e = mine[q], i = e >> 6, jj = e & 63;
-                pass = !sat_rejects(rowl + i * kLitePad, coll + jj * kLitePad, tq);
-                entry = (unsigned)i | ((unsigned)(ct * kTile + jj) << 6);
+        const int ct1 = min(cb, ct0 + kTileListCap);
+        {
+            const int ct = ct0 + t;
+            bool hit = false;
+            if (ct < ct1) {
+                const float4 cbx = __ldg(tbox + ct);
+                // negated so that a NaN rectangle is never culled
+                if (!(cbx.x > rbox.z || rbox.x > cbx.z || cbx.y > rbox.w || rbox.y > cbx.w)) {
+                    // refine: some (16 rows) x (32 columns) block must touch
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const float4 c = __ldg(hbox + (size_t)ct * 2 + h);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const float4 r = rsubs[g];
+                            hit = hit || !(c.x > r.z || r.x > c.z || c.y > r.w || r.y > c.w);
+                        }
+                    }
+                }
             }
-            unsigned bal = __ballot_sync(0xffffffffu, pass);
+            const unsigned bal = __ballot_sync(0xffffffffu, hit);
             if (bal) {
                 int base = 0;
-                if (lane == 0) base = atomicAdd(&n2s, __popc(bal));
+                if (lane == 0) base = atomicAdd(&ntiles, __popc(bal));
                 base = __shfl_sync(0xffffffffu, base, 0);
-                if (pass) list2[base + __popc(bal & ((1u << lane) - 1u))] = entry;
+                if (hit) tiles[base + __popc(bal & ((1u << lane) - 1u))] = ct;
             }
         }
-        // a tile adds at most 4096 entries: flush when the next one might not fit
         __syncthreads();
-        if (n2s > kList2Cap - kTile * kTile) flush();
+        const int nt = ntiles;
+        unsigned short *mine = list1[warp];
+        for (int ti = 0; ti < nt; ++ti) {  // no CTA barrier in here
+            const int ct = tiles[ti];
+            // this warp's block = 16 rows x 32 columns: skip it when the two rectangles are disjoint
+            const float4 csub = __ldg(hbox + (size_t)ct * 2 + (warp & 1));
+            if (csub.x > rsub.z || rsub.x > csub.z || csub.y > rsub.w || rsub.y > csub.w) continue;
+            const int j = 32 * (warp & 1) + lane, col = ct * kTile + j;
+            const bool jvalid = col < boxes_num;
+            float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f);  // cx cy r hx of this lane's column box
+            if (jvalid) b0 = __ldg(reinterpret_cast<const float4 *>(lite + (size_t)col * kLite));
+            const bool diag = ct == rb;
+            // ---- stage 1: centre distance.  tight: |offset| <= rscale * min(r_a, r_b), else touching circles
+            int cnt1 = 0;
+#pragma unroll 4
+            for (int k = 0; k < 16; ++k) {
+                const int i = row0 + k;
+                const float4 a0 = *reinterpret_cast<const float4 *>(rowl + i * kLite);  // cx cy r hx (broadcast)
+                const float dx = b0.x - a0.x, dy = b0.y - a0.y;
+                const float rr = tight ? rscale * fminf(a0.z, b0.z) : a0.z + b0.z;
+                const bool live = jvalid && i < row_size && (!diag || j > i) && !(dx * dx + dy * dy > rr * rr);
+                const unsigned bal = __ballot_sync(0xffffffffu, live);
+                if (live) mine[cnt1 + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)((i << 6) | j);
+                cnt1 += __popc(bal);
+            }
+            __syncwarp();
+            // ---- stage 2: rotation-free bounds, then the separating-axis bound; survivors into the queue ----
+            for (int q0 = 0; q0 < cnt1; q0 += 32) {
+                const int q = q0 + lane;
+                bool pass = false;
+                unsigned int entry = 0;
+                if (q < cnt1) {
+                    const int e = mine[q], i = e >> 6, jj = e & 63, c2 = ct * kTile + jj;
+                    float bl[kLite];
+                    const float4 v0 = __ldg(reinterpret_cast<const float4 *>(lite + (size_t)c2 * kLite));
+                    const float4 v1 = __ldg(reinterpret_cast<const float4 *>(lite + (size_t)c2 * kLite) + 1);
+                    bl[0] = v0.x; bl[1] = v0.y; bl[2] = v0.z; bl[3] = v0.w;
+                    bl[4] = v1.x; bl[5] = v1.y; bl[6] = v1.z; bl[7] = v1.w;
+                    const float *al = rowl + i * kLite;
+                    const bool deg = !(al[3] > 0.f && al[4] > 0.f && bl[3] > 0.f && bl[4] > 0.f);  // degenerate box: always clip
+                    pass = deg || !(tq > 0.f) ||
+                           cheap_passes(bl[0] - al[0], bl[1] - al[1], al[3], al[4], al[5], al[6], lite_area(al), bl[3], bl[4],
+                                        bl[5], bl[6], lite_area(bl), al[7] + bl[7], tq, tight);
+                    pass = pass && !sat_rejects(al, bl, tq);
+                    entry = (unsigned)i | ((unsigned)c2 << 6);
+                }
+                const unsigned bal = __ballot_sync(0xffffffffu, pass);
+                if (pass) myq[nq + __popc(bal & ((1u << lane) - 1u))] = entry;  // nq <= 31 here, + 32 <= kWarpQueue
+                nq += __popc(bal);
+                __syncwarp();
+                drain(31);
+            }
+            __syncwarp();
+        }
     }
-    flush();
+    __syncwarp();
+    drain(0);
 }
 
 // One thread per listed pair (grid-stride over the list).
 __global__ void __launch_bounds__(256)
-    nms_clip_kernel(int boxes_num, float thresh, const float *__restrict__ rec_all,
+    nms_clip_kernel(int boxes_num, float thresh, const float *__restrict__ rec_all, const int *__restrict__ perm_all,
                     unsigned long long *__restrict__ mask_all, NmsLists lists) {
     const int cb = (boxes_num + kTile - 1) / kTile;
     unsigned long long n = *lists.count;
@@ -460,7 +807,8 @@ __global__ void __launch_bounds__(256)
          q += (unsigned long long)gridDim.x * 256) {
         unsigned long long e = lists.pairs[q];
         int scene = (int)(e >> 48), row = (int)((e >> 24) & 0xFFFFFFull), col = (int)(e & 0xFFFFFFull);
-        clip_pair(rec_all + (size_t)scene * boxes_num * kRec, mask_all + (size_t)scene * boxes_num * cb, cb, row, col, thresh);
+        clip_pair(rec_all + (size_t)scene * boxes_num * kRec, perm_all ? perm_all + (size_t)scene * boxes_num : nullptr,
+                  mask_all + (size_t)scene * boxes_num * cb, cb, row, col, thresh);
     }
 }
 
@@ -627,7 +975,7 @@ extern "C" int hf_oriented_nms_mask(const float *boxes, unsigned long long *mask
 namespace hf {
 namespace {
 struct NmsWorkspace {
-    size_t mask_off, rec_off, lite_off, pairs_off, count_off, total;
+    size_t mask_off, rec_off, lite_off, perm_off, tbox_off, pairs_off, count_off, total;
     unsigned long long cap;
 };
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -638,7 +986,9 @@ NmsWorkspace nms_workspace(int scenes, int boxes_num) {
     w.mask_off = 0;
     w.rec_off = align256(w.mask_off + S * N * cb * sizeof(unsigned long long));
     w.lite_off = align256(w.rec_off + S * N * kRec * sizeof(float));
-    w.pairs_off = align256(w.lite_off + S * N * kLite * sizeof(float));
+    w.perm_off = align256(w.lite_off + S * N * kLite * sizeof(float));
+    w.tbox_off = align256(w.perm_off + S * N * sizeof(int));
+    w.pairs_off = align256(w.tbox_off + S * cb * 3 * sizeof(float4));  // tile + 2 half-tile rectangles
     w.count_off = align256(w.pairs_off + (size_t)w.cap * sizeof(unsigned long long));
     w.total = w.count_off + 256;
     return w;
@@ -646,9 +996,30 @@ NmsWorkspace nms_workspace(int scenes, int boxes_num) {
 }  // namespace
 }  // namespace hf
 
+namespace hf {
+namespace {
+int g_nms_spatial_sort = 1;
+}
+}  // namespace hf
+extern "C" void hf_nms_set_spatial_sort(int on) { hf::g_nms_spatial_sort = on; }
+
 extern "C" size_t hf_oriented_nms_workspace_bytes(int scenes, int boxes_num) {
     if (scenes <= 0 || boxes_num <= 0) return 0;
     return hf::nms_workspace(scenes, boxes_num).total;
+}
+
+// Debug/measurement aid: number of pairs the last hf_oriented_nms call on this workspace sent
+// to the exact clip (read back from the workspace; synchronises the stream).
+extern "C" long long hf_oriented_nms_last_pair_count(int scenes, int boxes_num, const void *workspace, hf_stream_t stream) {
+    using namespace hf;
+    if (scenes <= 0 || boxes_num <= 0 || !workspace) return -1;
+    const NmsWorkspace w = nms_workspace(scenes, boxes_num);
+    unsigned long long v = 0;
+    if (cudaMemcpyAsync(&v, static_cast<const char *>(workspace) + w.count_off, sizeof(v), cudaMemcpyDeviceToHost,
+                        (cudaStream_t)stream) != cudaSuccess)
+        return -1;
+    if (cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) return -1;
+    return (long long)v;
 }
 
 extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int *keep,
@@ -676,6 +1047,8 @@ extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, fl
     unsigned long long *mask = reinterpret_cast<unsigned long long *>(base + w.mask_off);
     float *rec = reinterpret_cast<float *>(base + w.rec_off);
     float *lite = reinterpret_cast<float *>(base + w.lite_off);
+    int *perm = reinterpret_cast<int *>(base + w.perm_off);
+    float4 *tbox = reinterpret_cast<float4 *>(base + w.tbox_off);
     NmsLists lists;
     lists.pairs = reinterpret_cast<unsigned long long *>(base + w.pairs_off);
     lists.count = reinterpret_cast<unsigned long long *>(base + w.count_off);
@@ -683,15 +1056,23 @@ extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, fl
     // the clip kernel ORs bits into the mask; the pair counter starts at 0
     HF_CUDA_OK(cudaMemsetAsync(mask, 0, (size_t)scenes * boxes_num * cb * sizeof(unsigned long long), s));
     HF_CUDA_OK(cudaMemsetAsync(lists.count, 0, sizeof(unsigned long long), s));
-    const long long total = (long long)scenes * boxes_num;
-    nms_prepare_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(total, boxes, rec, lite);
+    // spatial order: counting sort of the centres (the pair list region doubles as its scratch)
+    if (g_nms_spatial_sort) {
+        nms_sort_kernel<<<scenes, kSortThreads, 0, s>>>(boxes_num, boxes, perm, lists.pairs);
+        HF_LAUNCH_OK("nms_sort_kernel");
+    } else {
+        perm = nullptr;
+    }
+    float4 *hbox = tbox + (size_t)scenes * cb;
+    const float tq = nms_overlap_thresh * (1.f - 1e-3f) - 1e-6f;  // same expression as in the filter kernel
+    nms_prepare_kernel<<<dim3(cb, scenes), kTile, 0, s>>>(boxes_num, boxes, perm, rec, lite, tbox, hbox,
+                                                          tq >= 0.5f ? 0.5f * nms_rscale(tq) : 1.f);
     HF_LAUNCH_OK("nms_prepare_kernel");
-    dim3 fgrid((cb + kChunk - 1) / kChunk, cb, scenes);
-    nms_filter_kernel<<<fgrid, 256, 0, s>>>(boxes_num, nms_overlap_thresh, rec, lite, mask, lists);
+    nms_filter_kernel<<<dim3(cb, scenes), 256, 0, s>>>(boxes_num, nms_overlap_thresh, rec, lite, tbox, hbox, perm, mask, lists);
     HF_LAUNCH_OK("nms_filter_kernel");
     unsigned long long want = (w.cap + 255) / 256;
     unsigned cgrid = (unsigned)(want < (unsigned long long)num_sms() * 8 ? want : (unsigned long long)num_sms() * 8);
-    nms_clip_kernel<<<cgrid, 256, 0, s>>>(boxes_num, nms_overlap_thresh, rec, mask, lists);
+    nms_clip_kernel<<<cgrid, 256, 0, s>>>(boxes_num, nms_overlap_thresh, rec, perm, mask, lists);
     HF_LAUNCH_OK("nms_clip_kernel");
     if (smem > 40 * 1024)
         HF_CUDA_OK(cudaFuncSetAttribute(nms_sweep_kernel2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -143,6 +143,14 @@ size_t hf_oriented_nms_workspace_bytes(int scenes, int boxes_num);
 int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh,
                     int *keep, int *num_kept, void *workspace, size_t workspace_bytes,
                     hf_stream_t stream);
+/* Tuning override: 0 = enumerate pairs in score order (no spatial sort, no tile culling to
+ * speak of), 1 = Morton order (default).  Results are identical. */
+void hf_nms_set_spatial_sort(int on);
+/* Measurement aid: how many box pairs the last hf_oriented_nms call that used `workspace`
+ * sent to the exact polygon clip (the rest were settled by the bounding tests).
+ * Synchronises `stream`; -1 on error. */
+long long hf_oriented_nms_last_pair_count(int scenes, int boxes_num, const void *workspace,
+                                          hf_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -333,6 +333,23 @@ def test_oriented_nms_matches_oracle(cuda, oracle, n, thresh, clusters):
         assert want.tolist() == [0, 1, 0]
 
 
+@pytest.mark.parametrize("n,thresh", [(2500, 0.85), (9000, 0.8), (700, 0.01)])
+def test_oriented_nms_spatial_sort_changes_nothing(cuda, n, thresh):
+    """Enumerating the pairs in Morton order (tile culling) or in score order gives the same keep lists."""
+    from heterofusionrcnn_b200 import _lib
+
+    boxes = T(np.stack([synthetic.make_nms_boxes(400 + s, n, 9) for s in range(3)]), cuda)
+    lib = _lib.load()
+    try:
+        lib.hf_nms_set_spatial_sort(0)
+        k0, n0 = oriented_nms_batch(boxes, thresh, return_num_kept=True)
+        lib.hf_nms_set_spatial_sort(1)
+        k1, n1 = oriented_nms_batch(boxes, thresh, return_num_kept=True)
+    finally:
+        lib.hf_nms_set_spatial_sort(1)
+    assert torch.equal(n0, n1) and torch.equal(k0, k1)
+
+
 def test_oriented_nms_mask_matches_oracle_and_sweep(cuda, oracle):
     boxes = synthetic.make_nms_boxes(12, 900, 5)
     wmask = oracle.oriented_nms_mask(boxes, 0.6)
