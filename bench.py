@@ -54,6 +54,11 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--table", action="store_true", help="also print a per-launch table to stderr")
+    ap.add_argument("--inflight", type=int, default=2,
+                    help="e2e leg: batches kept in flight, so that a batch's host->device copies overlap the previous batch's kernels")
+    ap.add_argument("--resident-inflight", type=int, default=1,
+                    help="resident leg: batches kept in flight (measured: 2 is slower than 1 - the second batch's FPS "
+                         "clusters cannot be gang-scheduled while the first batch's bulk kernels fill every SM)")
     ap.add_argument("--serial", action="store_true",
                     help="issue the whole chain on one stream in program order (default: independent branches overlap on streams)")
     return ap.parse_args()
@@ -91,7 +96,9 @@ def config_dict(args, cfg, n_gpus):
         "global_scans": args.batch * n_gpus,
         "points_per_scan": cfg.points,
         "sharding": "batch slices, one per GPU, no collective" if n_gpus > 1 else "single GPU",
-        "issue": "one stream, program order" if args.serial else "independent branches of the chain on 5 CUDA streams",
+        "issue": "one stream, program order" if args.serial else
+                 "independent branches of the chain on 5 CUDA streams, %d batch(es) in flight (e2e leg: %d)" % (
+                     max(1, args.resident_inflight), max(1, args.inflight)),
         "l2": "no explicit flush: one step reads 0.45 GB and writes 5.6 GB per GPU, far beyond the 126 MB L2",
     }
 
@@ -355,10 +362,13 @@ def run_b200(args):
 
     # ---- resident-input throughput (value) + per-launch events (roofline) ----
     overlap = not args.serial
+    depth = max(1, args.resident_inflight) if overlap else 1
     probe = EventProbe(torch)
     probe.enabled = False
+    pipe = chain.ChainPipeline(cfg, depth=depth, overlap=overlap)
     for _ in range(max(args.warmup, 3)):
-        chain.run_chain(resident, cfg, probe, overlap=overlap)
+        pipe.submit(resident, probe)
+    pipe.drain()
     probe.enabled = True
     barrier()
     clocks = ClockSampler(local).start() if rank == 0 else None
@@ -366,7 +376,8 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     for _ in range(args.steps):
-        chain.run_chain(resident, cfg, probe, overlap=overlap)
+        pipe.submit(resident, probe)
+    pipe.drain()
     ev1.record()
     barrier()
     launches = hf.launch_count() - l0
@@ -386,34 +397,54 @@ def run_b200(args):
     e2e = None
     if not args.no_e2e:
         h2d = nbytes_of(pinned)
-        out_host = None
+        depth = max(1, args.inflight) if overlap else 1
+        pipe = chain.ChainPipeline(cfg, depth=depth, overlap=overlap)
+        out_streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]
+        out_host = [None] * depth
+        main = torch.cuda.current_stream(dev)
         for it in range(max(args.warmup, 3) + args.steps):
             if it == max(args.warmup, 3):
+                for st in out_streams:
+                    main.wait_stream(st)
+                pipe.drain()
                 barrier()
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 t0 = time.perf_counter()
                 e0.record()
-            d = chain.to_device_from_pinned(pinned, dev)
-            res = chain.run_chain(d, cfg, overlap=overlap)
-            outs = chain.host_results(res, cfg)
-            if out_host is None:
-                out_host = [torch.empty(o.shape, dtype=o.dtype, pin_memory=True) for o in outs]
-            for o, h in zip(outs, out_host):
-                h.copy_(o, non_blocking=True)
+            slot = it % depth
+            d = chain.to_device_from_pinned(pinned, dev)  # on the current stream: overlaps the previous batch's kernels
+            res = pipe.submit(d, None)
+            st = out_streams[slot]
+            for e in res["_done"]:
+                st.wait_event(e)
+            if not res["_done"]:
+                st.wait_stream(main)
+            with torch.cuda.stream(st):  # device->host copies of this batch's host-consumed results
+                outs = chain.host_results(res, cfg)
+                if out_host[slot] is None:
+                    out_host[slot] = [torch.empty(o.shape, dtype=o.dtype, pin_memory=True) for o in outs]
+                for o, h in zip(outs, out_host[slot]):
+                    h.copy_(o, non_blocking=True)
+        for st in out_streams:
+            main.wait_stream(st)
+        pipe.drain()
         e1.record()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3
         e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0))
         e2e = {"value": args.batch * n_gpus * args.steps / (e2e_ms / 1e3), "unit": UNIT,
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": nbytes_of(out_host), "ms_per_step": e2e_ms / args.steps,
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": nbytes_of(out_host[0]), "ms_per_step": e2e_ms / args.steps,
                "wall_ms_per_step": wall_ms / args.steps,
                "copied_in": "every input tensor of the step (scans, stand-in feature maps, masks, boxes) from pinned host memory",
-               "copied_out": "FPS indices (4 levels), ball-query counts, NMS keep lists + counts, crop non_empty flags"}
+               "copied_out": "FPS indices (4 levels), ball-query counts, NMS keep lists + counts, crop non_empty flags",
+               "pipelining": "%d batches in flight: a batch's host->device copies overlap the previous batch's kernels" % depth}
+        del pipe
     clk = clocks.stop() if clocks else None
 
     # the only cross-rank step of the path: the final host gather of the host-consumed results (untimed)
     from heterofusionrcnn_b200 import shard
 
+    torch.cuda.synchronize()
     fin = chain.run_chain(resident, cfg, overlap=overlap)
     torch.cuda.synchronize()
     gathered = shard.gather_to_host({"nms_keep": fin["nms_keep"].cpu().numpy(), "nms_num": fin["nms_num"].cpu().numpy()},

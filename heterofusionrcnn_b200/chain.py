@@ -155,8 +155,8 @@ class _Lanes:
         self.nms = torch.cuda.Stream(device=device, priority=hi)
 
     @classmethod
-    def get(cls, device):
-        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    def get(cls, device, slot=0):
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device(), slot)
         if key not in cls._cache:
             cls._cache[key] = cls(device)
         return cls._cache[key]
@@ -171,13 +171,18 @@ def _fp_weights(dist):
     return dist, inv / inv.sum(dim=2, keepdim=True)
 
 
-def run_chain(dev, cfg, probe=None, overlap=True):
+def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
     """Run the chain on device-resident inputs `dev` (see make_host_inputs).  Returns a dict of results.
 
     overlap=True spreads the independent branches of the chain over CUDA streams (see _Lanes);
     the caller's current stream waits for all of them before this function returns, so the
     results are ordered on the current stream as usual.  overlap=False issues every op on the
     current stream in the reference's program order.
+
+    Batches are independent, so a caller can keep several in flight: `slot` selects a separate
+    set of streams and join=False returns without making the current stream wait — the events
+    of the pass are in res["_done"] instead (see ChainPipeline).  The sampling chain of one
+    batch is latency bound and leaves most of the GPU idle; the next batch's fills it.
 
     `probe(name, **shape)` (optional) must return a context manager; every libhfops launch runs
     inside one, named after its kernel family, with the shape figures its algorithmic
@@ -187,7 +192,7 @@ def run_chain(dev, cfg, probe=None, overlap=True):
     device = dev["xyz"].device
     main = torch.cuda.current_stream(device)
     if overlap:
-        lanes = _Lanes.get(device)
+        lanes = _Lanes.get(device, slot)
         crit, s_group, s_fp, s_crop, s_nms = lanes.all()
         start = torch.cuda.Event()
         start.record(main)
@@ -265,9 +270,48 @@ def run_chain(dev, cfg, probe=None, overlap=True):
                 out = three_interpolate(dev["fp_feats"][j], nidx, w)
             res["fp%d" % (lvl + 1)] = (dist, nidx, out)
     if overlap:
-        for s in lanes.all():
-            main.wait_event(mark(s))
+        done = [mark(s) for s in lanes.all()]
+        if join:
+            for e in done:
+                main.wait_event(e)
+        res["_done"] = done
+    else:
+        res["_done"] = []
     return res
+
+
+class ChainPipeline:
+    """Keeps up to `depth` batches in flight on separate stream sets.
+
+    submit() issues one pass and returns its results dict; before a slot is reused the host
+    waits for the pass that used it last and only then drops its tensors, so memory handed back
+    to the allocator is never still being read on another stream.  drain() makes the current
+    stream wait for everything in flight.
+    """
+
+    def __init__(self, cfg, depth=2, overlap=True):
+        self.cfg, self.depth, self.overlap = cfg, max(1, depth), overlap
+        self.inflight = [None] * self.depth
+        self.k = 0
+
+    def submit(self, dev, probe=None):
+        slot = self.k % self.depth
+        self.k += 1
+        old = self.inflight[slot]
+        if old is not None:
+            for e in old[1]["_done"]:
+                e.synchronize()
+            self.inflight[slot] = None
+        res = run_chain(dev, self.cfg, probe, overlap=self.overlap, slot=slot, join=not self.overlap or self.depth == 1)
+        self.inflight[slot] = (dev, res)  # the inputs stay referenced as long as the pass may read them
+        return res
+
+    def drain(self):
+        main = torch.cuda.current_stream()
+        for item in self.inflight:
+            if item is not None:
+                for e in item[1]["_done"]:
+                    main.wait_event(e)
 
 
 def chain_launches(cfg):
