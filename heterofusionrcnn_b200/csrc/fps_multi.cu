@@ -1,0 +1,317 @@
+// fps_multi.cu — multi-pick farthest point sampling for sm_100a (the default FPS kernel).
+//
+// Replaces sampling/tf_sampling_g.cu:105-170 of the reference; same results bit for bit.
+//
+// Why: FPS is m-1 strictly sequential arg-max steps.  On a B200 one step of a 16384-point
+// cloud is ~130 cycles of arithmetic (the cloud lives in registers, spread over a cluster of
+// 8 SMs) and ~1000 cycles of reduction + DSMEM exchange latency (profiles/r1_ncu_full_v5).
+// This kernel pays that latency once per ROUND and takes up to K = 8 picks out of it.
+//
+// Exactness of taking several picks from one arg-max exchange.  Let td[] be the running
+// minimum distances after the picks so far and key(j) = (td[j], tie(j)) the reference's total
+// order (max distance, then lowest index mod 512, then lowest index; tf_sampling_g.cu:146-163).
+// The reference's next pick is r1 = argmax key.  Let r2 be the arg-max over the remaining
+// points.  Picking r1 replaces td[j] by min(td[j], d(r1, j)), which never raises a key.  So if
+// d(r1, r2) >= td[r2] (r2 is untouched by the update; fminf(d, td) returns td bit for bit) and
+// td[r2] > 0 (already-picked points, whose td is 0, stay below it), r2 is still the arg-max
+// after the update: it IS the reference's following pick.  By induction r_i is the i-th next
+// pick as long as d(r_j, r_i) >= td[r_i] for every j < i.  The first candidate that fails the
+// test ends the round; picks it would have made are found by the next round's exchange.
+//
+// Candidates.  Every warp (a "group") reports the best point it holds, and the value `sec` of
+// its second best.  Sorted by key, candidate r_i is the true i-th arg-max unless a point hidden
+// behind an already accepted candidate of the same warp beats it, so r_i is also required to
+// satisfy td[r_i] > sec(g) for the warps g of r_1..r_{i-1}.  All tests are conservative: a
+// failed test only ends the round early, it never changes an index.
+//
+// Machinery per round (no __syncthreads and no cluster barrier in the loop):
+//   1. every thread lowers the td of its PTS register-resident points against the A centres
+//      accepted last round (A x PTS x 7 FP32 instructions);
+//   2. per thread top-2 + which point; warp arg-max with redux.sync; the owning lane pushes
+//      {x, y, z, sec, tie word, td bits} (24 B) into the warp's slot in EVERY CTA of the
+//      cluster with st.async (DSMEM), completing on the receiver's mbarrier;
+//   3. every warp waits on its CTA's mbarrier, ranks the <= 64 candidates by 64-bit key with
+//      one pass of broadcast shared-memory reads, and tests the 28 (i > j) pairs of the top 8
+//      on 28 lanes at once; one ballot gives the number A of accepted picks;
+//   4. CTA 0 writes the A indices; everyone reads the A centres from the slots next round.
+// Measured on 16 x (16384 -> 4096): 6.2 picks per round.
+#include "common.cuh"
+
+namespace hf {
+namespace {
+
+constexpr int MP_K = 8;         // candidates examined (and at most accepted) per round
+constexpr int MP_MSG = 24;      // bytes pushed per warp, per destination CTA, per round
+constexpr int MP_SLOT_W = 8;    // 32-bit words reserved per slot (32 B, keeps slots 16 B aligned)
+
+__device__ __forceinline__ uint32_t mp_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void mp_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::
+                     : "memory");
+}
+__device__ __forceinline__ uint32_t mp_mapa(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mp_st_async_v4(uint32_t raddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d,
+                                               uint32_t rbar) {
+    asm volatile(
+        "st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1,%2,%3,%4}, [%5];" ::"r"(
+            raddr),
+        "r"(a), "r"(b), "r"(c), "r"(d), "r"(rbar)
+        : "memory");
+}
+__device__ __forceinline__ void mp_st_async_v2(uint32_t raddr, uint32_t a, uint32_t b, uint32_t rbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1,%2}, [%3];" ::"r"(
+                     raddr),
+                 "r"(a), "r"(b), "r"(rbar)
+                 : "memory");
+}
+// Low word of the composite key: larger = preferred.  Encodes (k mod 512, k) ascending.
+__device__ __forceinline__ uint32_t mp_tie_word(uint32_t k) { return ~(((k & 511u) << 23) | (k >> 9)); }
+__device__ __forceinline__ uint32_t mp_tie_decode(uint32_t lo) {
+    uint32_t inv = ~lo;
+    return ((inv & 0x7FFFFFu) << 9) | (inv >> 23);
+}
+
+// Thread -> point mapping.  A CTA holds CAP = T*PTS consecutive points (base a multiple of
+// 512), a thread holds PTS of them: register p = s*Q + q is local point 512*q + T*s + t
+// (s < S = 512/T stripes, q < Q = PTS/S).  So (k mod 512) = T*s + t and the reference's tie
+// order among one thread's points is simply ascending p.
+template <int C, int W, int PTS>
+__global__ void __launch_bounds__(W * 32, 1)
+    fps_multi_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out) {
+    constexpr int T = W * 32, S = 512 / T, Q = PTS / S, CAP = T * PTS, G = C * W, NC = (G + 31) / 32;
+    static_assert(S >= 1 && PTS % S == 0 && Q >= 1, "PTS must be a multiple of 512 / threads");
+    static_assert(G <= 64, "at most 64 warps per scene");
+    static_assert(PTS <= 32, "the equal-to-max mask is 32 bits");
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *sx = reinterpret_cast<float *>(smem_raw);
+    float *sy = sx + CAP;
+    float *sz = sy + CAP;
+    __shared__ __align__(16) uint32_t slots[2][G][MP_SLOT_W];  // {x, y, z, sec | tie word, td bits, -, -}
+    __shared__ __align__(8) uint64_t bars[2];
+    __shared__ __align__(8) uint8_t pos[W][8];  // per warp: rank -> slot of the top 8 candidates
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t rank = C > 1 ? mp_ctarank() : 0u;
+    const int scene = blockIdx.x / C;
+    const float *data = inp + (size_t)scene * n * 3;
+    int *idxs = out + (size_t)scene * m;
+    const uint32_t base = rank * CAP;
+
+    float x[PTS], y[PTS], z[PTS], td[PTS];
+#pragma unroll
+    for (int p = 0; p < PTS; ++p) {
+        const int li = 512 * (p % Q) + T * (p / Q) + t;
+        const uint32_t k = base + li;
+        if (k < (uint32_t)n) {
+            x[p] = data[(size_t)k * 3 + 0];
+            y[p] = data[(size_t)k * 3 + 1];
+            z[p] = data[(size_t)k * 3 + 2];
+            td[p] = 1e38f;  // tf_sampling_g.cu:118
+        } else {
+            x[p] = y[p] = z[p] = 0.f;
+            td[p] = -1.f;  // padding: never a candidate
+        }
+        sx[li] = x[p];
+        sy[li] = y[p];
+        sz[li] = z[p];
+    }
+    for (int i = t; i < 2 * G * MP_SLOT_W; i += T) (&slots[0][0][0])[i] = 0u;
+    if (lane < 8) pos[warp][lane] = 0;
+    __syncthreads();
+    if (t == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(&bars[0], G * MP_MSG);
+        mbar_arrive_expect_tx(&bars[1], G * MP_MSG);
+        // round 0 reads its single centre (point 0, tf_sampling_g.cu:114-116) like any other round
+        slots[1][0][0] = __float_as_uint(data[0]);
+        slots[1][0][1] = __float_as_uint(data[1]);
+        slots[1][0][2] = __float_as_uint(data[2]);
+    }
+    if (rank == 0 && t == 0) idxs[0] = 0;
+    if (C > 1) mp_cluster_sync();
+    else __syncthreads();
+
+    // remote addresses of this warp's slot (buffer 0) and of barrier 0 in every CTA of the cluster
+    uint32_t rslot[C], rbar[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        rslot[c] = mp_mapa(smem_u32(&slots[0][rank * W + warp][0]), (uint32_t)c);
+        rbar[c] = mp_mapa(smem_u32(&bars[0]), (uint32_t)c);
+    }
+    // lane q < 28 tests candidate pair (pi, pj), pi > pj, q = pi*(pi-1)/2 + pj
+    int pi = 1, pj = 0;
+    for (int q = 0; q < lane && q < 27; ++q) {
+        if (++pj == pi) {
+            ++pi;
+            pj = 0;
+        }
+    }
+
+    uint64_t posw = 0;  // the 8 bytes of pos[warp]
+    int A = 1, done = 1;
+    for (int round = 0; done < m; ++round) {
+        const int buf = round & 1;
+        const uint32_t(*cs)[MP_SLOT_W] = slots[buf ^ 1];  // centres accepted last round
+        // ---- 1. lower td against the A new centres ----
+        float4 cn = *reinterpret_cast<const float4 *>(cs[(uint32_t)posw & 0xffu]);
+        for (int i = 0; i < A; ++i) {
+            const float4 c = cn;
+            if (i + 1 < A) cn = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * (i + 1))) & 0xffu]);
+#pragma unroll
+            for (int p = 0; p < PTS; ++p) td[p] = fminf(sqdist(x[p] - c.x, y[p] - c.y, z[p] - c.z), td[p]);
+        }
+        // ---- 2. this thread's best point and the value of its second best ----
+        float m1 = td[0];
+#pragma unroll
+        for (int p = 1; p < PTS; ++p) m1 = fmaxf(m1, td[p]);
+        uint32_t eqm = 0u;
+        float m2 = -1.f;
+#pragma unroll
+        for (int p = 0; p < PTS; ++p) {
+            const bool e = td[p] == m1;
+            eqm |= e ? (1u << p) : 0u;
+            m2 = fmaxf(m2, e ? -1.f : td[p]);
+        }
+        if (eqm & (eqm - 1u)) m2 = m1;  // two points share the maximum
+        const int bp = __ffs(eqm) - 1;  // first in the reference's tie order
+        const bool have = m1 >= 0.f;    // false: only padding here
+        const uint32_t hi = have ? __float_as_uint(m1) : 0u;
+        const uint32_t h2 = m2 >= 0.f ? __float_as_uint(m2) : 0u;
+        // ---- warp arg-max ----
+        const uint32_t wm = __reduce_max_sync(0xffffffffu, hi);
+        const unsigned eq = __ballot_sync(0xffffffffu, have && hi == wm);
+        uint32_t ws = __reduce_max_sync(0xffffffffu, (have && hi == wm) ? h2 : hi);
+        const int li = 512 * (bp % Q) + T * (bp / Q) + t;
+        const uint32_t mylo = mp_tie_word(base + li);
+        int L = __ffs(eq) - 1;
+        if (eq & (eq - 1u)) {  // several lanes hold the warp maximum (duplicate points): rare, warp-uniform
+            ws = wm;
+            const uint32_t wl = __reduce_max_sync(0xffffffffu, ((eq >> lane) & 1u) ? mylo : 0u);
+            L = __ffs(__ballot_sync(0xffffffffu, ((eq >> lane) & 1u) && mylo == wl)) - 1;
+        }
+        // ---- push the warp's candidate to every CTA ----
+        if (lane == (L < 0 ? 0 : L)) {
+            uint32_t mx = 0u, my = 0u, mz = 0u, mlo = 0u, mhi = 0u;
+            if (L >= 0) {
+                mx = __float_as_uint(sx[li]);
+                my = __float_as_uint(sy[li]);
+                mz = __float_as_uint(sz[li]);
+                mlo = mylo;
+                mhi = wm;
+            }
+            const uint32_t so = (uint32_t)buf * (G * MP_SLOT_W * 4), bo = (uint32_t)buf * 8;
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                mp_st_async_v4(rslot[c] + so, mx, my, mz, ws, rbar[c] + bo);
+                mp_st_async_v2(rslot[c] + so + 16, mlo, mhi, rbar[c] + bo);
+            }
+        }
+        // ---- 3. wait for all G candidates ----
+        mbar_wait(&bars[buf], (uint32_t)(round >> 1) & 1u);
+        if (t == 0) mbar_arrive_expect_tx(&bars[buf], G * MP_MSG);  // for round + 2
+        const uint32_t(*sl)[MP_SLOT_W] = slots[buf];
+        uint64_t key[NC];
+        uint32_t rk[NC];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const int s = lane + 32 * c;
+            key[c] = s < G ? *reinterpret_cast<const uint64_t *>(&sl[s][4]) : 0ull;
+            rk[c] = 0u;
+        }
+#pragma unroll
+        for (int s = 0; s < G; ++s) {
+            const uint64_t ks = *reinterpret_cast<const uint64_t *>(&sl[s][4]);
+#pragma unroll
+            for (int c = 0; c < NC; ++c) rk[c] += ks > key[c] ? 1u : 0u;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int c = 0; c < NC; ++c)
+            if (lane + 32 * c < G && rk[c] < (uint32_t)MP_K) pos[warp][rk[c]] = (uint8_t)(lane + 32 * c);
+        __syncwarp();
+        posw = *reinterpret_cast<const uint64_t *>(&pos[warp][0]);
+        // ---- pair tests: candidate pi survives the acceptance of candidate pj? ----
+        const uint32_t *ca = sl[(uint32_t)(posw >> (8 * pi)) & 0xffu];
+        const uint32_t *cb = sl[(uint32_t)(posw >> (8 * pj)) & 0xffu];
+        const float4 va = *reinterpret_cast<const float4 *>(ca);
+        const float4 vb = *reinterpret_cast<const float4 *>(cb);
+        const uint32_t hia = ca[5];
+        const bool viol = pi >= G || hia == 0u || __float_as_uint(vb.w) >= hia ||
+                          sqdist(va.x - vb.x, va.y - vb.y, va.z - vb.z) < __uint_as_float(hia);
+        const unsigned vm = __ballot_sync(0xffffffffu, lane < 28 && viol);
+        const int first_bad = __shfl_sync(0xffffffffu, pi, vm ? __ffs(vm) - 1 : 0);
+        A = vm ? first_bad : MP_K;
+        A = min(A, m - done);
+        // ---- 4. emit ----
+        if (rank == 0 && warp == 0 && lane < A)
+            idxs[done + lane] = (int)mp_tie_decode(sl[(uint32_t)(posw >> (8 * lane)) & 0xffu][4]);
+        done += A;
+    }
+    if (C > 1) mp_cluster_sync();  // no CTA may exit while peers can still push into it
+}
+
+template <int C, int W, int PTS>
+int launch_fps_multi(int b, int n, int m, const float *inp, int *out, cudaStream_t stream) {
+    auto kern = fps_multi_kernel<C, W, PTS>;
+    const size_t smem = (size_t)3 * W * 32 * PTS * sizeof(float);
+    if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)b * C);
+    cfg.blockDim = dim3(W * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    HF_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, n, m, inp, out));
+    HF_LAUNCH_OK("fps_multi_kernel");
+    return HF_OK;
+}
+
+template <int C>
+int dispatch_multi(int per, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {
+    if (per <= 512) return launch_fps_multi<C, 4, 4>(b, n, m, inp, out, s);
+    if (per <= 1024) return launch_fps_multi<C, 4, 8>(b, n, m, inp, out, s);
+    if (per <= 2048) return launch_fps_multi<C, 4, 16>(b, n, m, inp, out, s);
+    if (per <= 4096) return launch_fps_multi<C, 4, 32>(b, n, m, inp, out, s);
+    if (per <= 8192) return launch_fps_multi<C, 8, 32>(b, n, m, inp, out, s);
+    return HF_ERR_UNSUPPORTED;
+}
+
+}  // namespace
+
+// Launch the multi-pick FPS.  cluster_req = 0 -> as many CTAs per scene as keep >= 512 points
+// in each (the minimum a CTA holds); returns HF_ERR_UNSUPPORTED for clouds beyond 8 x 8192 points.
+int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req) {
+    int cluster = 1;
+    if (cluster_req == 1 || cluster_req == 2 || cluster_req == 4 || cluster_req == 8) {
+        cluster = cluster_req;
+    } else {
+        while (cluster < 8 && n > 512 * cluster) cluster <<= 1;
+    }
+    while (cluster < 8 && (n + cluster - 1) / cluster > 8192) cluster <<= 1;
+    const int per = (n + cluster - 1) / cluster;
+    switch (cluster) {
+        case 1: return dispatch_multi<1>(per, b, n, m, inp, out, s);
+        case 2: return dispatch_multi<2>(per, b, n, m, inp, out, s);
+        case 4: return dispatch_multi<4>(per, b, n, m, inp, out, s);
+        default: return dispatch_multi<8>(per, b, n, m, inp, out, s);
+    }
+}
+
+}  // namespace hf

@@ -21,6 +21,8 @@
 namespace hf {
 // fps_bucket.cu: the bucket-pruned kernel (default for clouds it covers)
 int fps_bucket_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int w_req, int j_req);
+// fps_multi.cu: the multi-pick kernel (default for clouds of up to 65536 points)
+int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req);
 
 namespace {
 
@@ -355,6 +357,18 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
         if (rc == HF_ERR_UNSUPPORTED)
             set_error("FarthestPointSample: bucket kernel has no shape for n=%d warps=%d buckets/warp=%d", n, g_bucket_w, g_bucket_j);
         return rc;
+    }
+
+    // Default (algo 0; 3 = forced): the multi-pick kernel of fps_multi.cu, several picks per
+    // DSMEM exchange.  algo 1 = the one-pick-per-exchange cluster kernel below, which also
+    // serves clouds the multi-pick kernel has no shape for.
+    if (g_algo == 0 || g_algo == 3) {
+        int rc = fps_multi_dispatch(b, n, m, inp, out, s, g_cluster_override);
+        if (rc != HF_ERR_UNSUPPORTED) return rc;
+        if (g_algo == 3) {
+            set_error("FarthestPointSample: multi-pick kernel has no shape for n=%d", n);
+            return rc;
+        }
     }
 
     // Cluster size: as many CTAs per scene as the GPU can co-schedule for this batch, but

@@ -111,6 +111,50 @@ def test_fps_bucket_equals_plain_kernel_full_size(cuda, n, m):
     assert torch.equal(plain, bucket)
 
 
+@pytest.mark.parametrize("n,m,dup,cluster", [(16384, 700, 3000, 0), (16384, 300, 0, 4), (16000, 300, 0, 2), (8192, 300, 0, 1),
+                                             (8000, 300, 500, 8), (7000, 200, 0, 2), (4096, 512, 0, 0), (4096, 512, 1000, 1),
+                                             (4000, 256, 0, 2), (3000, 256, 0, 4), (2048, 256, 0, 0), (2000, 256, 0, 1),
+                                             (1500, 200, 100, 8), (1024, 256, 0, 0), (1000, 128, 0, 1), (512, 128, 0, 0),
+                                             (500, 64, 0, 8), (300, 64, 0, 2), (256, 64, 0, 0), (200, 300, 0, 0),
+                                             (37, 16, 0, 4), (1, 4, 0, 0), (3, 7, 0, 2), (20000, 300, 0, 0),
+                                             (40000, 300, 3000, 0), (30000, 256, 0, 4), (60000, 256, 0, 0),
+                                             (65536, 256, 8000, 8), (33000, 200, 0, 0), (700, 700, 0, 0), (5000, 1, 0, 0)])
+def test_fps_multi_pick_kernel_shapes(cuda, oracle, n, m, dup, cluster):
+    """Every instantiated shape of the multi-pick kernel (fps_multi.cu), incl. every cluster size,
+    ragged sizes, duplicate-padded clouds (exact ties) and m > n, against the oracle."""
+    from heterofusionrcnn_b200 import _lib
+
+    xyz, _ = synthetic.make_scans(31 + n + m, 2, n, duplicate_pad=dup)
+    want = oracle.farthest_point_sample(m, xyz)
+    _lib.load().hf_fps_set_variant(3, 0, 0)
+    _lib.load().hf_fps_set_cluster(cluster)
+    try:
+        got = N(farthest_point_sample(m, T(xyz, cuda)))
+    finally:
+        _lib.load().hf_fps_set_cluster(0)
+        _lib.load().hf_fps_set_variant(0, 0, 0)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("n,m,b", [(16384, 4096, 16), (65536, 16384, 3), (4096, 4096, 20)])
+def test_fps_multi_pick_equals_plain_kernel_full_size(cuda, n, m, b):
+    """BASELINE config 2 / config 5 sizes: the multi-pick kernel and the one-pick-per-exchange
+    kernel (itself pinned against the oracle and the reference kernel) give identical indices."""
+    from heterofusionrcnn_b200 import _lib
+
+    xyz, _ = synthetic.make_scans(78, b, n, duplicate_pad=n // 8)
+    x = T(xyz, cuda)
+    lib = _lib.load()
+    try:
+        lib.hf_fps_set_variant(1, 0, 0)
+        plain = farthest_point_sample(m, x)
+        lib.hf_fps_set_variant(3, 0, 0)
+        multi = farthest_point_sample(m, x)
+    finally:
+        lib.hf_fps_set_variant(0, 0, 0)
+    assert torch.equal(plain, multi)
+
+
 @needs_ref
 def test_fps_matches_reference_kernel_full_size(cuda):
     """BASELINE config 2 size, against the reference's own kernel on this GPU (ties included)."""
