@@ -142,13 +142,9 @@ __global__ void __launch_bounds__(W * 32, 1)
     if (C > 1) mp_cluster_sync();
     else __syncthreads();
 
-    // remote addresses of this warp's slot (buffer 0) and of barrier 0 in every CTA of the cluster
-    uint32_t rslot[C], rbar[C];
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-        rslot[c] = mp_mapa(smem_u32(&slots[0][rank * W + warp][0]), (uint32_t)c);
-        rbar[c] = mp_mapa(smem_u32(&bars[0]), (uint32_t)c);
-    }
+    // lane c < C pushes to CTA c: remote address of this warp's slot (buffer 0) and of barrier 0 there
+    const uint32_t rslot = mp_mapa(smem_u32(&slots[0][rank * W + warp][0]), (uint32_t)(lane % C));
+    const uint32_t rbar = mp_mapa(smem_u32(&bars[0]), (uint32_t)(lane % C));
     // lane q < 28 tests candidate pair (pi, pj), pi > pj, q = pi*(pi-1)/2 + pj
     int pi = 1, pj = 0;
     for (int q = 0; q < lane && q < 27; ++q) {
@@ -157,64 +153,80 @@ __global__ void __launch_bounds__(W * 32, 1)
             pj = 0;
         }
     }
+    const int sh_i = 8 * pi, sh_j = 8 * pj;
 
-    uint64_t posw = 0;  // the 8 bytes of pos[warp]
+    uint64_t posw = 0;  // the 8 bytes of pos[warp]: slot of the candidate of rank 0..7
     int A = 1, done = 1;
     for (int round = 0; done < m; ++round) {
         const int buf = round & 1;
         const uint32_t(*cs)[MP_SLOT_W] = slots[buf ^ 1];  // centres accepted last round
-        // ---- 1. lower td against the A new centres ----
-        float4 cn = *reinterpret_cast<const float4 *>(cs[(uint32_t)posw & 0xffu]);
-        for (int i = 0; i < A; ++i) {
-            const float4 c = cn;
-            if (i + 1 < A) cn = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * (i + 1))) & 0xffu]);
+        // ---- 1. lower td against the A new centres, two at a time (min is exact in any order) ----
+        {
+            int i = 0;
+            float4 c0 = *reinterpret_cast<const float4 *>(cs[(uint32_t)posw & 0xffu]);
+            float4 c1 = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> 8) & 0xffu]);
+            for (; i + 2 <= A; i += 2) {
+                const float4 a = c0, b2 = c1;
+                // prefetch the next pair (ranks i+2, i+3 <= 7; stale bytes beyond A are valid slot numbers)
+                c0 = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * ((i + 2) & 7))) & 0xffu]);
+                c1 = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * ((i + 3) & 7))) & 0xffu]);
 #pragma unroll
-            for (int p = 0; p < PTS; ++p) td[p] = fminf(sqdist(x[p] - c.x, y[p] - c.y, z[p] - c.z), td[p]);
+                for (int p = 0; p < PTS; ++p)
+                    td[p] = fminf(fminf(sqdist(x[p] - a.x, y[p] - a.y, z[p] - a.z),
+                                        sqdist(x[p] - b2.x, y[p] - b2.y, z[p] - b2.z)),
+                                  td[p]);
+            }
+            if (i < A) {
+#pragma unroll
+                for (int p = 0; p < PTS; ++p) td[p] = fminf(sqdist(x[p] - c0.x, y[p] - c0.y, z[p] - c0.z), td[p]);
+            }
         }
         // ---- 2. this thread's best point and the value of its second best ----
         float m1 = td[0];
 #pragma unroll
         for (int p = 1; p < PTS; ++p) m1 = fmaxf(m1, td[p]);
+        const bool have = m1 >= 0.f;  // false: only padding here
+        const uint32_t hi = have ? __float_as_uint(m1) : 0u;
+        const uint32_t wm = __reduce_max_sync(0xffffffffu, hi);  // warp maximum (in flight during the scan below)
         uint32_t eqm = 0u;
-        float m2 = -1.f;
+        float m2a = -1.f, m2b = -1.f;
 #pragma unroll
         for (int p = 0; p < PTS; ++p) {
             const bool e = td[p] == m1;
-            eqm |= e ? (1u << p) : 0u;
-            m2 = fmaxf(m2, e ? -1.f : td[p]);
+            eqm += e ? (1u << p) : 0u;
+            if (p & 1) m2b = fmaxf(m2b, e ? -1.f : td[p]);
+            else m2a = fmaxf(m2a, e ? -1.f : td[p]);
         }
+        float m2 = fmaxf(m2a, m2b);
         if (eqm & (eqm - 1u)) m2 = m1;  // two points share the maximum
         const int bp = __ffs(eqm) - 1;  // first in the reference's tie order
-        const bool have = m1 >= 0.f;    // false: only padding here
-        const uint32_t hi = have ? __float_as_uint(m1) : 0u;
         const uint32_t h2 = m2 >= 0.f ? __float_as_uint(m2) : 0u;
-        // ---- warp arg-max ----
-        const uint32_t wm = __reduce_max_sync(0xffffffffu, hi);
-        const unsigned eq = __ballot_sync(0xffffffffu, have && hi == wm);
-        uint32_t ws = __reduce_max_sync(0xffffffffu, (have && hi == wm) ? h2 : hi);
+        const bool top = have && hi == wm;
+        const unsigned eq = __ballot_sync(0xffffffffu, top);
+        uint32_t ws = __reduce_max_sync(0xffffffffu, top ? h2 : hi);  // second best of the warp
         const int li = 512 * (bp % Q) + T * (bp / Q) + t;
-        const uint32_t mylo = mp_tie_word(base + li);
         int L = __ffs(eq) - 1;
         if (eq & (eq - 1u)) {  // several lanes hold the warp maximum (duplicate points): rare, warp-uniform
             ws = wm;
-            const uint32_t wl = __reduce_max_sync(0xffffffffu, ((eq >> lane) & 1u) ? mylo : 0u);
-            L = __ffs(__ballot_sync(0xffffffffu, ((eq >> lane) & 1u) && mylo == wl)) - 1;
+            const uint32_t mylo = mp_tie_word(base + li);
+            const uint32_t wl = __reduce_max_sync(0xffffffffu, top ? mylo : 0u);
+            L = __ffs(__ballot_sync(0xffffffffu, top && mylo == wl)) - 1;
         }
-        // ---- push the warp's candidate to every CTA ----
-        if (lane == (L < 0 ? 0 : L)) {
-            uint32_t mx = 0u, my = 0u, mz = 0u, mlo = 0u, mhi = 0u;
-            if (L >= 0) {
-                mx = __float_as_uint(sx[li]);
-                my = __float_as_uint(sy[li]);
-                mz = __float_as_uint(sz[li]);
-                mlo = mylo;
-                mhi = wm;
-            }
-            const uint32_t so = (uint32_t)buf * (G * MP_SLOT_W * 4), bo = (uint32_t)buf * 8;
-#pragma unroll
-            for (int c = 0; c < C; ++c) {
-                mp_st_async_v4(rslot[c] + so, mx, my, mz, ws, rbar[c] + bo);
-                mp_st_async_v2(rslot[c] + so + 16, mlo, mhi, rbar[c] + bo);
+        // ---- push the warp's candidate: lane c sends it to CTA c ----
+        {
+            const int wli = __shfl_sync(0xffffffffu, li, L < 0 ? 0 : L);
+            if (lane < C) {
+                uint32_t mx = 0u, my = 0u, mz = 0u, mlo = 0u, mhi = 0u;
+                if (L >= 0) {
+                    mx = __float_as_uint(sx[wli]);
+                    my = __float_as_uint(sy[wli]);
+                    mz = __float_as_uint(sz[wli]);
+                    mlo = mp_tie_word(base + wli);
+                    mhi = wm;
+                }
+                const uint32_t so = (uint32_t)buf * (G * MP_SLOT_W * 4), bo = (uint32_t)buf * 8;
+                mp_st_async_v4(rslot + so, mx, my, mz, ws, rbar + bo);
+                mp_st_async_v2(rslot + so + 16, mlo, mhi, rbar + bo);
             }
         }
         // ---- 3. wait for all G candidates ----
@@ -222,37 +234,43 @@ __global__ void __launch_bounds__(W * 32, 1)
         if (t == 0) mbar_arrive_expect_tx(&bars[buf], G * MP_MSG);  // for round + 2
         const uint32_t(*sl)[MP_SLOT_W] = slots[buf];
         uint64_t key[NC];
-        uint32_t rk[NC];
+        uint32_t rk[NC][4];
 #pragma unroll
         for (int c = 0; c < NC; ++c) {
             const int s = lane + 32 * c;
             key[c] = s < G ? *reinterpret_cast<const uint64_t *>(&sl[s][4]) : 0ull;
-            rk[c] = 0u;
+            rk[c][0] = rk[c][1] = rk[c][2] = rk[c][3] = 0u;
         }
 #pragma unroll
         for (int s = 0; s < G; ++s) {
             const uint64_t ks = *reinterpret_cast<const uint64_t *>(&sl[s][4]);
 #pragma unroll
-            for (int c = 0; c < NC; ++c) rk[c] += ks > key[c] ? 1u : 0u;
+            for (int c = 0; c < NC; ++c) rk[c][s & 3] += ks > key[c] ? 1u : 0u;  // 4 independent chains
         }
         __syncwarp();
 #pragma unroll
-        for (int c = 0; c < NC; ++c)
-            if (lane + 32 * c < G && rk[c] < (uint32_t)MP_K) pos[warp][rk[c]] = (uint8_t)(lane + 32 * c);
+        for (int c = 0; c < NC; ++c) {
+            const uint32_t r = (rk[c][0] + rk[c][1]) + (rk[c][2] + rk[c][3]);
+            if (lane + 32 * c < G && r < (uint32_t)MP_K) pos[warp][r] = (uint8_t)(lane + 32 * c);
+        }
         __syncwarp();
         posw = *reinterpret_cast<const uint64_t *>(&pos[warp][0]);
-        // ---- pair tests: candidate pi survives the acceptance of candidate pj? ----
-        const uint32_t *ca = sl[(uint32_t)(posw >> (8 * pi)) & 0xffu];
-        const uint32_t *cb = sl[(uint32_t)(posw >> (8 * pj)) & 0xffu];
+        // ---- pair tests: does candidate pi survive the acceptance of candidate pj? (branch free) ----
+        const uint32_t *ca = sl[(uint32_t)(posw >> sh_i) & 0xffu];
+        const uint32_t *cb = sl[(uint32_t)(posw >> sh_j) & 0xffu];
         const float4 va = *reinterpret_cast<const float4 *>(ca);
         const float4 vb = *reinterpret_cast<const float4 *>(cb);
         const uint32_t hia = ca[5];
-        const bool viol = pi >= G || hia == 0u || __float_as_uint(vb.w) >= hia ||
-                          sqdist(va.x - vb.x, va.y - vb.y, va.z - vb.z) < __uint_as_float(hia);
+        const float dab = sqdist(va.x - vb.x, va.y - vb.y, va.z - vb.z);
+        const bool viol = (pi >= G) | (hia == 0u) | (__float_as_uint(vb.w) >= hia) | (dab < __uint_as_float(hia));
         const unsigned vm = __ballot_sync(0xffffffffu, lane < 28 && viol);
-        const int first_bad = __shfl_sync(0xffffffffu, pi, vm ? __ffs(vm) - 1 : 0);
-        A = vm ? first_bad : MP_K;
-        A = min(A, m - done);
+        {
+            // first violating pair f (lanes are ordered by pi) -> pi(f) = number of accepted candidates
+            const int f = __ffs(vm) - 1;
+            const int row = 1 + (f >= 1) + (f >= 3) + (f >= 6) + (f >= 10) + (f >= 15) + (f >= 21);
+            A = vm ? row : MP_K;
+            A = min(A, m - done);
+        }
         // ---- 4. emit ----
         if (rank == 0 && warp == 0 && lane < A)
             idxs[done + lane] = (int)mp_tie_decode(sl[(uint32_t)(posw >> (8 * lane)) & 0xffu][4]);
