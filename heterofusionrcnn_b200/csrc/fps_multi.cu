@@ -79,17 +79,25 @@ __device__ __forceinline__ uint32_t mp_tie_decode(uint32_t lo) {
     return ((inv & 0x7FFFFFu) << 9) | (inv >> 23);
 }
 
-// Thread -> point mapping.  A CTA holds CAP = T*PTS consecutive points (base a multiple of
-// 512), a thread holds PTS of them: register p = s*Q + q is local point 512*q + T*s + t
-// (s < S = 512/T stripes, q < Q = PTS/S).  So (k mod 512) = T*s + t and the reference's tie
-// order among one thread's points is simply ascending p.
+// Thread -> point mapping.  The cluster's TT = C*T threads cover C*T*PTS points.  Thread slot
+// u = g + G*lane (g = the warp's group number rank*W + warp) owns residue(s) r = k mod 512 and
+// every R-th block of 512 points:  register p = s*Q + q  is point  k = 512*(u/512 + R*q) + (u%512 + TT*s)
+// with S = max(1, 512/TT) residues per thread, R = max(1, TT/512) threads per residue, Q = PTS/S.
+//   * a thread's points share k mod 512 (or have ascending residues), so the reference's tie
+//     order among them is simply ascending p;
+//   * CONSECUTIVE indices live in consecutive groups.  This matters: the deeper levels of a
+//     PointNet++ stack sample a cloud that is already in FPS order, where the picks are
+//     0, 1, 2, ...; were they in the same warp, its one candidate per round would allow a
+//     single pick per round.
 template <int C, int W, int PTS>
 __global__ void __launch_bounds__(W * 32, 1)
     fps_multi_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out) {
-    constexpr int T = W * 32, S = 512 / T, Q = PTS / S, CAP = T * PTS, G = C * W, NC = (G + 31) / 32;
-    static_assert(S >= 1 && PTS % S == 0 && Q >= 1, "PTS must be a multiple of 512 / threads");
+    constexpr int T = W * 32, TT = C * T, S = TT < 512 ? 512 / TT : 1, R = TT >= 512 ? TT / 512 : 1, Q = PTS / S;
+    constexpr int G = C * W, NC = (G + 31) / 32;
+    static_assert(PTS % S == 0 && Q >= 1, "PTS must be a multiple of the residues per thread");
     static_assert(G <= 64, "at most 64 warps per scene");
     static_assert(PTS <= 32, "the equal-to-max mask is 32 bits");
+    constexpr int CAP = T * PTS;  // points held by one CTA
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *sx = reinterpret_cast<float *>(smem_raw);
@@ -104,13 +112,18 @@ __global__ void __launch_bounds__(W * 32, 1)
     const int scene = blockIdx.x / C;
     const float *data = inp + (size_t)scene * n * 3;
     int *idxs = out + (size_t)scene * m;
-    const uint32_t base = rank * CAP;
+    const uint32_t grp = rank * W + warp;  // this warp's group = its slot number
+    // point held in register p of the thread with slot u
+    auto kof = [](uint32_t u, int p) -> uint32_t {
+        return 512u * (u / 512u + (uint32_t)R * (uint32_t)(p % Q)) + (u % 512u + (uint32_t)TT * (uint32_t)(p / Q));
+    };
+    const uint32_t u = grp + (uint32_t)G * lane;
 
     float x[PTS], y[PTS], z[PTS], td[PTS];
 #pragma unroll
     for (int p = 0; p < PTS; ++p) {
-        const int li = 512 * (p % Q) + T * (p / Q) + t;
-        const uint32_t k = base + li;
+        const int li = p * T + t;  // local copy, conflict free
+        const uint32_t k = kof(u, p);
         if (k < (uint32_t)n) {
             x[p] = data[(size_t)k * 3 + 0];
             y[p] = data[(size_t)k * 3 + 1];
@@ -143,7 +156,7 @@ __global__ void __launch_bounds__(W * 32, 1)
     else __syncthreads();
 
     // lane c < C pushes to CTA c: remote address of this warp's slot (buffer 0) and of barrier 0 there
-    const uint32_t rslot = mp_mapa(smem_u32(&slots[0][rank * W + warp][0]), (uint32_t)(lane % C));
+    const uint32_t rslot = mp_mapa(smem_u32(&slots[0][grp][0]), (uint32_t)(lane % C));
     const uint32_t rbar = mp_mapa(smem_u32(&bars[0]), (uint32_t)(lane % C));
     // lane q < 28 tests candidate pair (pi, pj), pi > pj, q = pi*(pi-1)/2 + pj
     int pi = 1, pj = 0;
@@ -204,24 +217,25 @@ __global__ void __launch_bounds__(W * 32, 1)
         const bool top = have && hi == wm;
         const unsigned eq = __ballot_sync(0xffffffffu, top);
         uint32_t ws = __reduce_max_sync(0xffffffffu, top ? h2 : hi);  // second best of the warp
-        const int li = 512 * (bp % Q) + T * (bp / Q) + t;
         int L = __ffs(eq) - 1;
         if (eq & (eq - 1u)) {  // several lanes hold the warp maximum (duplicate points): rare, warp-uniform
             ws = wm;
-            const uint32_t mylo = mp_tie_word(base + li);
+            const uint32_t mylo = mp_tie_word(kof(u, bp));
             const uint32_t wl = __reduce_max_sync(0xffffffffu, top ? mylo : 0u);
             L = __ffs(__ballot_sync(0xffffffffu, top && mylo == wl)) - 1;
         }
         // ---- push the warp's candidate: lane c sends it to CTA c ----
         {
-            const int wli = __shfl_sync(0xffffffffu, li, L < 0 ? 0 : L);
+            const int wl_ = L < 0 ? 0 : L;
+            const int wbp = __shfl_sync(0xffffffffu, bp, wl_);
             if (lane < C) {
                 uint32_t mx = 0u, my = 0u, mz = 0u, mlo = 0u, mhi = 0u;
                 if (L >= 0) {
+                    const int wli = wbp * T + warp * 32 + wl_;
                     mx = __float_as_uint(sx[wli]);
                     my = __float_as_uint(sy[wli]);
                     mz = __float_as_uint(sz[wli]);
-                    mlo = mp_tie_word(base + wli);
+                    mlo = mp_tie_word(kof(grp + (uint32_t)G * wl_, wbp));
                     mhi = wm;
                 }
                 const uint32_t so = (uint32_t)buf * (G * MP_SLOT_W * 4), bo = (uint32_t)buf * 8;
@@ -313,14 +327,18 @@ int dispatch_multi(int per, int b, int n, int m, const float *inp, int *out, cud
 
 }  // namespace
 
-// Launch the multi-pick FPS.  cluster_req = 0 -> as many CTAs per scene as keep >= 512 points
-// in each (the minimum a CTA holds); returns HF_ERR_UNSUPPORTED for clouds beyond 8 x 8192 points.
+// Launch the multi-pick FPS.  cluster_req = 0 -> measured heuristic (tools/fps_multi_sweep.py):
+// 1 CTA up to 512 points, 2 up to 2048, 4 up to 4096, else 8; halved while the batch would not
+// fit the GPU in one wave and a CTA still holds <= 4096 points.  Returns HF_ERR_UNSUPPORTED
+// for clouds beyond 8 x 8192 points.
 int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req) {
     int cluster = 1;
     if (cluster_req == 1 || cluster_req == 2 || cluster_req == 4 || cluster_req == 8) {
         cluster = cluster_req;
     } else {
-        while (cluster < 8 && n > 512 * cluster) cluster <<= 1;
+        cluster = n <= 512 ? 1 : n <= 2048 ? 2 : n <= 4096 ? 4 : 8;
+        const int sms = num_sms();
+        while (cluster > 1 && (long long)b * cluster > sms && (n + cluster / 2 - 1) / (cluster / 2) <= 4096) cluster >>= 1;
     }
     while (cluster < 8 && (n + cluster - 1) / cluster > 8192) cluster <<= 1;
     const int per = (n + cluster - 1) / cluster;

@@ -13,7 +13,7 @@ import torch
 
 import heterofusionrcnn_b200 as hf
 from heterofusionrcnn_b200 import synthetic
-from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample
+from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample, gather_point
 
 
 def timeit(fn, reps=5):
@@ -37,6 +37,9 @@ def main():
                     (65536, 16384, 2), (65536, 16384, 16), (16384, 4096, 64)]:
         xyz, _ = synthetic.make_scans(3, b, n)
         x = torch.from_numpy(xyz).to(dev)
+        if n < 16384:  # deeper levels of the chain see a cloud in FPS order: build it the way the chain does
+            x0 = torch.from_numpy(synthetic.make_scans(3, b, 16384)[0]).to(dev)
+            x = gather_point(x0, farthest_point_sample(n, x0))
         ref = None
         for algo, cluster in [(1, 0), (3, 0), (3, 1), (3, 2), (3, 4), (3, 8)]:
             lib.hf_fps_set_variant(algo, 0, 0)
