@@ -15,7 +15,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 160 -c 110 --csv --
 echo "launch list rc=$?"
 $PROF > $OUT/${TAG}_plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on \
-    -k 'regex:crop_kernel|group_point_vec4|three_interpolate_nlc_vec4|fps_cluster|nms_filter|nms_clip|nms_sweep|three_nn_kernel|query_ball' \
+    -k 'regex:crop_kernel|group_point_vec4|three_interpolate_nlc_vec4|fps_cluster|fps_multi|nms_filter|nms_clip|nms_sweep|three_nn_kernel|query_ball' \
     -s 69 -c 23 -o $OUT/${TAG}_full $PROF > $OUT/${TAG}_ncu2.log 2>&1
 echo "full capture rc=$?"
 ls -la $OUT
