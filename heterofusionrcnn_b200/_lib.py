@@ -31,6 +31,11 @@ SIGNATURES = {
     "hf_fps_set_variant": (None, [_c_int, _c_int, _c_int]),
     "hf_gather_point": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_query_ball_point": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "hf_spatial_workspace_bytes": (_size_t, [_c_int, _c_int, _c_int]),
+    "hf_spatial_set_mode": (None, [_c_int]),
+    "hf_query_ball_point_ws": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t,
+                                        _ptr]),
+    "hf_three_nn_ws": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
     "hf_group_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_nn": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_interpolate": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),

@@ -1,0 +1,631 @@
+// spatial.cu — query_ball_point and three_nn with exact spatial pruning, for sm_100a.
+//
+// Same results as the every-pair kernels in grouping.cu / interpolate.cu (and therefore as
+// grouping/tf_grouping_g.cu:3-36 and interpolate/tf_interpolate_g.cu:22-65 of the reference),
+// a different algorithm.  The reference tests every (query, candidate) pair: 16 x 4096 x 16384
+// = 1.07e9 distance evaluations per op at BASELINE config 2, of which a few thousand per query
+// can possibly matter.  Here both clouds of a call are first sorted along a Hilbert curve and
+// cut into BUCKETS of 32 consecutive points with their bounding boxes (cloud_index_kernel, one
+// CTA per scene and cloud, radix sort in shared memory).  A warp then owns one bucket of 32
+// queries and visits a candidate bucket only if
+//      LB = sqdist(per-axis gap between the two boxes)  <  threshold
+// (ball query: the radius threshold; three_nn: the worst third-best distance of its 32 lanes).
+// Every IEEE operation involved is monotone and LB uses the SAME operation sequence as the
+// point distances (common.cuh:sqdist), so LB <= fl(d(q, c)) holds for every query q of the
+// warp and candidate c of the bucket: a skipped bucket cannot contain a hit, no slack needed.
+//
+// Order independence.  Buckets are visited in curve order, not index order, so the reference's
+// "first in index order wins" rules are restated on explicit keys:
+//   * ball query: all hits are collected, the nsample SMALLEST indices are kept and written in
+//     ascending order (= the first nsample hits of an ascending scan, tf_grouping_g.cu:15-33);
+//   * three_nn: candidates are ranked by (distance, index) lexicographically (= strict '<'
+//     insertion during an ascending scan, tf_interpolate_g.cu:50-61).
+//
+// The caller provides the workspace (hf_spatial_workspace_bytes); clouds beyond 16384 points
+// or calls too small to pay for the sort take the every-pair kernels.
+#include <limits.h>
+#include <math.h>
+
+#include "common.cuh"
+
+namespace hf {
+float ball_threshold(float radius);  // grouping.cu
+
+namespace {
+
+constexpr int kIdxThreads = 1024;
+constexpr int kIdxMaxE = 16;                        // sort elements per thread
+constexpr int kMaxIndexed = kIdxMaxE * kIdxThreads;  // 16384 points per cloud fit the shared-memory sort
+constexpr int kHistPitch = 257;                     // hist[warp][digit], padded: conflict free by digit and by warp
+constexpr int kHistWords = 32 * kHistPitch;
+constexpr size_t kIdxSmem = (size_t)kMaxIndexed * 4 + (size_t)kHistWords * 4 + (size_t)kMaxIndexed * 2;  // 128 KB
+
+__device__ __forceinline__ int sp_f2ord(float f) {
+    int i = __float_as_int(f);
+    return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+__device__ __forceinline__ float sp_ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
+// Position of cell (x, y, z) (8 bits each) along a 3-D Hilbert curve.  Unlike a Morton curve it
+// has no jumps: 32 consecutive points always form one connected, compact run, so no bucket box
+// straddles half the scene.  The curve is the one Skilling's transpose algorithm produces, run
+// here as its 24-state machine: entry [state*8 + octant] = next state << 3 | curve digit, octant
+// = the (x, y, z) bits of one level, most significant level first.  (Table derived by
+// enumerating Skilling's curve; any locality-preserving order would be equally exact.)
+__constant__ unsigned char kHilbertLut[192] = {
+    8, 17, 27, 2, 39, 46, 52, 5, 56, 71, 73, 86, 91, 20, 10, 13, 48, 1, 103, 110, 115, 18, 12, 21,
+    126, 129, 29, 26, 79, 80, 140, 3, 148, 43, 37, 34, 127, 128, 78, 81, 156, 45, 35, 42, 31, 6, 160, 105,
+    72, 87, 139, 4, 57, 70, 50, 53, 0, 171, 111, 76, 49, 58, 102, 61, 180, 143, 83, 184, 69, 54, 66, 97,
+    16, 123, 9, 74, 47, 60, 38, 77, 132, 95, 85, 14, 67, 144, 82, 33, 142, 55, 185, 96, 93, 116, 90, 11,
+    188, 107, 175, 176, 101, 98, 62, 65, 164, 109, 119, 22, 99, 106, 152, 41, 174, 177, 63, 64, 117, 114, 92, 19,
+    30, 125, 161, 122, 7, 172, 104, 75, 130, 25, 133, 166, 179, 136, 84, 191, 94, 15, 141, 28, 145, 32, 138, 51,
+    146, 155, 149, 36, 137, 24, 190, 167, 154, 157, 147, 44, 169, 182, 120, 135, 162, 165, 121, 134, 187, 108, 168, 183,
+    118, 173, 23, 124, 153, 170, 40, 59, 178, 113, 131, 88, 181, 158, 68, 151, 186, 163, 89, 112, 189, 100, 150, 159,
+};
+__device__ __forceinline__ uint32_t sp_hilbert24(const unsigned char *lut, uint32_t x, uint32_t y, uint32_t z) {
+    uint32_t state = 0u, h = 0u;
+#pragma unroll
+    for (int l = 7; l >= 0; --l) {
+        const uint32_t oct = (((x >> l) & 1u) << 2) | (((y >> l) & 1u) << 1) | ((z >> l) & 1u);
+        const uint32_t e = lut[state * 8u + oct];
+        h = (h << 3) | (e & 7u);
+        state = e >> 3;
+    }
+    return h;
+}
+
+struct CloudDesc {
+    const float *xyz;  // (b, n, 3)
+    float4 *sorted;    // (b, npad) {x, y, z, original index as int bits}; padding = {NaN, NaN, NaN, -1}
+    float4 *boxes;     // (b, npad/32, 2) {lo.xyz, smallest original index in the bucket}, {hi.xyz, -}
+    int n, npad, per_thread;  // points, rounded up to 32, sort elements per thread = ceil(n / 1024)
+};
+
+// grid = (b, 2): blockIdx.y selects the cloud.  dynamic smem = kIdxSmem.
+__global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc ca, CloudDesc cb) {
+    extern __shared__ __align__(16) unsigned char idx_smem[];
+    uint32_t *code = reinterpret_cast<uint32_t *>(idx_smem);               // [np] Hilbert position
+    uint32_t *hist = code + kIdxMaxE * kIdxThreads;                         // [32 warps][257]
+    unsigned short *sidx = reinterpret_cast<unsigned short *>(hist + kHistWords);  // [np] original index
+    __shared__ int red[6][32];
+    __shared__ uint32_t wsum[32];
+    __shared__ unsigned char hlut[192];
+    const CloudDesc cd = blockIdx.y == 0 ? ca : cb;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+#ifdef HF_SPATIAL_DEBUG
+    long long tk[12]; int ntk = 0;
+#define TICK() do { __syncthreads(); tk[ntk++] = clock64(); } while (0)
+#else
+#define TICK() do {} while (0)
+#endif
+    TICK();
+    const int scene = blockIdx.x;
+    const int n = cd.n;
+    const float *data = cd.xyz + (size_t)scene * n * 3;
+    if (t < 192) hlut[t] = kHilbertLut[t];  // read after the barriers of the bounding box pass
+
+    // ---- bounding box -> cubic quantisation ----
+    int mn0 = INT_MAX, mn1 = INT_MAX, mn2 = INT_MAX, mx0 = INT_MIN, mx1 = INT_MIN, mx2 = INT_MIN;
+    for (int i = t; i < n; i += kIdxThreads) {
+        const int o0 = sp_f2ord(data[(size_t)i * 3]), o1 = sp_f2ord(data[(size_t)i * 3 + 1]),
+                  o2 = sp_f2ord(data[(size_t)i * 3 + 2]);
+        mn0 = min(mn0, o0); mx0 = max(mx0, o0);
+        mn1 = min(mn1, o1); mx1 = max(mx1, o1);
+        mn2 = min(mn2, o2); mx2 = max(mx2, o2);
+    }
+    mn0 = __reduce_min_sync(0xffffffffu, mn0); mx0 = __reduce_max_sync(0xffffffffu, mx0);
+    mn1 = __reduce_min_sync(0xffffffffu, mn1); mx1 = __reduce_max_sync(0xffffffffu, mx1);
+    mn2 = __reduce_min_sync(0xffffffffu, mn2); mx2 = __reduce_max_sync(0xffffffffu, mx2);
+    if (lane == 0) {
+        red[0][warp] = mn0; red[1][warp] = mn1; red[2][warp] = mn2;
+        red[3][warp] = mx0; red[4][warp] = mx1; red[5][warp] = mx2;
+    }
+    __syncthreads();
+    int l0 = red[0][lane], l1 = red[1][lane], l2 = red[2][lane], h0 = red[3][lane], h1 = red[4][lane], h2 = red[5][lane];
+    l0 = __reduce_min_sync(0xffffffffu, l0); l1 = __reduce_min_sync(0xffffffffu, l1); l2 = __reduce_min_sync(0xffffffffu, l2);
+    h0 = __reduce_max_sync(0xffffffffu, h0); h1 = __reduce_max_sync(0xffffffffu, h1); h2 = __reduce_max_sync(0xffffffffu, h2);
+    const float lo0 = sp_ord2f(l0), lo1 = sp_ord2f(l1), lo2 = sp_ord2f(l2);
+    const float ext = fmaxf(fmaxf(sp_ord2f(h0) - lo0, sp_ord2f(h1) - lo1), sp_ord2f(h2) - lo2);
+    const float inv = (ext > 0.f && ext < 1e30f) ? 255.f / ext : 0.f;  // 256 cubic cells per axis
+
+    TICK();
+    // ---- (Hilbert position, index) pairs, LSD radix sort in shared memory: 3 passes of 8 bits ----
+    // A warp owns a contiguous chunk of E*32 elements; its per-digit counters are private
+    // (hist[warp][digit]), ranks inside a 32-element row come from ballots, so every pass is
+    // stable without atomics.  Each thread keeps its E elements in registers across the scatter,
+    // so the pass is in place.
+    const int E = cd.per_thread;  // elements per thread, <= kIdxMaxE
+    const int np = E * kIdxThreads;
+    for (int i = t; i < np; i += kIdxThreads) {
+        uint32_t c = 0x00FFFFFFu;  // padding sorts last
+        if (i < n) {
+            const uint32_t qx = min(__float2uint_rz((data[(size_t)i * 3] - lo0) * inv), 255u);
+            const uint32_t qy = min(__float2uint_rz((data[(size_t)i * 3 + 1] - lo1) * inv), 255u);
+            const uint32_t qz = min(__float2uint_rz((data[(size_t)i * 3 + 2] - lo2) * inv), 255u);
+            c = sp_hilbert24(hlut, qx, qy, qz);
+        }
+        code[i] = c;
+        sidx[i] = (unsigned short)i;
+    }
+    const unsigned lt_mask = (1u << lane) - 1u;
+    TICK();
+    for (int pass = 0; pass < 3; ++pass) {
+        const int shift = 8 * pass;
+        for (int i = t; i < kHistWords; i += kIdxThreads) hist[i] = 0u;
+        __syncthreads();
+        uint32_t myc[kIdxMaxE], off[kIdxMaxE];
+        unsigned short myi[kIdxMaxE];
+        // (a) independent: digit peers of every element of this thread (off[] holds the peer mask for now)
+#pragma unroll
+        for (int it = 0; it < kIdxMaxE; ++it) {
+            if (it < E) {  // uniform
+                const int e = (warp * E + it) * 32 + lane;
+                myc[it] = code[e];
+                myi[it] = sidx[e];
+                const uint32_t d = (myc[it] >> shift) & 255u;
+                // lanes of this row with the same digit (8 ballots; match.any costs one round per distinct value)
+                unsigned peers = 0xffffffffu;
+#pragma unroll
+                for (int bit = 0; bit < 8; ++bit) {
+                    const unsigned bal = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
+                    peers &= ((d >> bit) & 1u) ? bal : ~bal;
+                }
+                off[it] = peers;
+            }
+        }
+        // (b) the warp's counters, row by row in order: offset = elements of this digit seen so far
+#pragma unroll
+        for (int it = 0; it < kIdxMaxE; ++it) {
+            if (it < E) {
+                const uint32_t d = (myc[it] >> shift) & 255u;
+                const unsigned peers = off[it];
+                const uint32_t base = hist[warp * kHistPitch + d];
+                __syncwarp();
+                if ((peers & lt_mask) == 0u) hist[warp * kHistPitch + d] = base + __popc(peers);
+                __syncwarp();
+                off[it] = base + __popc(peers & lt_mask);
+            }
+        }
+        __syncthreads();
+        {  // exclusive scan in (digit, warp) order: thread t owns digit t/4, warps (t%4)*8 .. +7
+            const int sd = t >> 2, sw0 = (t & 3) * 8;
+            uint32_t v[8], sum = 0u;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                v[k] = hist[(sw0 + k) * kHistPitch + sd];
+                sum += v[k];
+            }
+            uint32_t inc = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += up;
+            }
+            if (lane == 31) wsum[warp] = inc;
+            __syncthreads();
+            uint32_t wtot = wsum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t up = __shfl_up_sync(0xffffffffu, wtot, o);
+                if (lane >= o) wtot += up;
+            }
+            uint32_t run = inc - sum + (warp > 0 ? __shfl_sync(0xffffffffu, wtot, warp - 1) : 0u);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                hist[(sw0 + k) * kHistPitch + sd] = run;
+                run += v[k];
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int it = 0; it < kIdxMaxE; ++it) {
+            if (it < E) {
+                const uint32_t d = (myc[it] >> shift) & 255u;
+                const uint32_t dst = hist[warp * kHistPitch + d] + off[it];
+                code[dst] = myc[it];
+                sidx[dst] = myi[it];
+            }
+        }
+        __syncthreads();
+        TICK();
+    }
+
+    // ---- sorted copy + bucket boxes (a warp writes one bucket per step) ----
+    float4 *sorted = cd.sorted + (size_t)scene * cd.npad;
+    float4 *boxes = cd.boxes + (size_t)scene * (cd.npad / 32) * 2;
+    const float qnan = __int_as_float(0x7FC00000);
+    for (int i0 = t; i0 < cd.npad; i0 += 4 * kIdxThreads) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {  // the 12 gathers of a step are in flight together
+            const int i = i0 + u * kIdxThreads;
+            v[u] = make_float4(qnan, qnan, qnan, __int_as_float(-1));
+            if (i < n) {
+                const int src = (int)sidx[i];
+                v[u].x = __ldg(&data[(size_t)src * 3]);
+                v[u].y = __ldg(&data[(size_t)src * 3 + 1]);
+                v[u].z = __ldg(&data[(size_t)src * 3 + 2]);
+                v[u].w = __int_as_float(src);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * kIdxThreads;
+            if (i >= cd.npad) break;  // warp uniform: npad is a multiple of 32
+            const bool real = i < n;
+            sorted[i] = v[u];
+            // bucket box + smallest original index: 7 redux.sync on order-preserving integer images
+            const int ox = sp_f2ord(v[u].x), oy = sp_f2ord(v[u].y), oz = sp_f2ord(v[u].z);
+            const float bx0 = sp_ord2f(__reduce_min_sync(0xffffffffu, real ? ox : INT_MAX));
+            const float by0 = sp_ord2f(__reduce_min_sync(0xffffffffu, real ? oy : INT_MAX));
+            const float bz0 = sp_ord2f(__reduce_min_sync(0xffffffffu, real ? oz : INT_MAX));
+            const float bx1 = sp_ord2f(__reduce_max_sync(0xffffffffu, real ? ox : INT_MIN));
+            const float by1 = sp_ord2f(__reduce_max_sync(0xffffffffu, real ? oy : INT_MIN));
+            const float bz1 = sp_ord2f(__reduce_max_sync(0xffffffffu, real ? oz : INT_MIN));
+            const int imin = __reduce_min_sync(0xffffffffu, real ? __float_as_int(v[u].w) : INT_MAX);
+            if (lane == 0) {
+                boxes[(i >> 5) * 2] = make_float4(bx0, by0, bz0, __int_as_float(imin));
+                boxes[(i >> 5) * 2 + 1] = make_float4(bx1, by1, bz1, 0.f);
+            }
+        }
+    }
+    TICK();
+#ifdef HF_SPATIAL_DEBUG
+    if (t == 0 && blockIdx.x == 0)
+        printf("cloud %d n=%d: bbox %lld keys %lld pass %lld %lld %lld final %lld\n", blockIdx.y, n, tk[1] - tk[0], tk[2] - tk[1],
+               tk[3] - tk[2], tk[4] - tk[3], tk[5] - tk[4], tk[6] - tk[5]);
+#endif
+}
+
+// Lower bound of sqdist over all (query in box q, candidate in box c) pairs; same op sequence as sqdist.
+__device__ __forceinline__ float box_gap2(const float4 &qlo, const float4 &qhi, const float4 &clo, const float4 &chi) {
+    const float gx = fmaxf(0.f, fmaxf(clo.x - qhi.x, qlo.x - chi.x));
+    const float gy = fmaxf(0.f, fmaxf(clo.y - qhi.y, qlo.y - chi.y));
+    const float gz = fmaxf(0.f, fmaxf(clo.z - qhi.z, qlo.z - chi.z));
+    return sqdist(gx, gy, gz);
+}
+
+constexpr int kSqWarps = 4;  // warps (= query buckets) per CTA of the two query kernels
+
+// Stage candidate bucket `cb` (32 x float4) into this warp's shared-memory tile.
+__device__ __forceinline__ void stage_bucket(float4 *tile, const float4 *sortedC, int cb, int lane) {
+    const float4 v = __ldg(&sortedC[(size_t)cb * 32 + lane]);
+    __syncwarp();  // the previous bucket's readers are done
+    tile[lane] = v;
+    __syncwarp();
+}
+
+// Lower bound of sqdist between one query point and every candidate in a box (same op sequence).
+__device__ __forceinline__ float point_gap2(const float4 &q, const float4 &clo, const float4 &chi) {
+    const float gx = fmaxf(0.f, fmaxf(clo.x - q.x, q.x - chi.x));
+    const float gy = fmaxf(0.f, fmaxf(clo.y - q.y, q.y - chi.y));
+    const float gz = fmaxf(0.f, fmaxf(clo.z - q.z, q.z - chi.z));
+    return sqdist(gx, gy, gz);
+}
+
+// ---- ball query: CTA = 32 curve-consecutive queries (lane = one query), 4 warps ---------
+// The 4 warps split the candidate buckets (groups of 32 buckets round robin), each collecting
+// its own hit rows; the rows are merged at the end.  Two-level pruning: (1) lane l tests
+// candidate bucket g*32+l against the CTA's query box, one ballot per 32 buckets; (2) every
+// surviving bucket is tested against each lane's own query point and visited only if some lane
+// can reach it.  Hit rows live in shared memory, transposed: slot s of lane l at
+// rows[s * 33 + l] (conflict free for the owner and for the coalesced write-out).
+// grid = (query buckets, b).  dynamic smem = 5 row buffers of nsample*33 ints + 4 tiles.
+__global__ void __launch_bounds__(kSqWarps * 32)
+    ball_query_indexed_kernel(int m, int nsample, float thr2, int nbq, int nbc, const float4 *__restrict__ sortedQ,
+                              const float4 *__restrict__ boxesQ, const float4 *__restrict__ sortedC,
+                              const float4 *__restrict__ boxesC, int *__restrict__ idx, int *__restrict__ pts_cnt) {
+    extern __shared__ __align__(16) unsigned char sq_smem[];
+    __shared__ int cnts[kSqWarps + 1][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int scene = blockIdx.y;
+    const int qb = blockIdx.x;
+    float4 *tile = reinterpret_cast<float4 *>(sq_smem) + warp * 32;
+    int *rows_all = reinterpret_cast<int *>(sq_smem + kSqWarps * 32 * sizeof(float4));
+    int *rows = rows_all + (size_t)warp * nsample * 33;
+    int *merged = rows_all + (size_t)kSqWarps * nsample * 33;
+    sortedQ += (size_t)scene * nbq * 32;
+    boxesQ += (size_t)scene * nbq * 2;
+    sortedC += (size_t)scene * nbc * 32;
+    boxesC += (size_t)scene * nbc * 2;
+
+    const float4 q = sortedQ[(size_t)qb * 32 + lane];
+    const int qi = __float_as_int(q.w);  // original query index, -1 = padding lane
+    const float4 qlo = boxesQ[qb * 2], qhi = boxesQ[qb * 2 + 1];
+    int cnt = 0;            // hits stored by this warp for this lane (<= nsample)
+    int mxv = -1, mxp = 0;  // once full: largest stored index and its slot
+
+    // level 1 for this warp's groups up front (independent loads); lane j keeps the ballot of its j-th group
+    const int ngroups = (nbc + 31) >> 5;                            // <= 16: nbc <= 512
+    const int mygroups = (ngroups - warp + kSqWarps - 1) / kSqWarps;  // groups warp, warp+4, ...
+    unsigned mymask = 0u;
+#pragma unroll 4
+    for (int j = 0; j < mygroups; ++j) {
+        const int mine = (j * kSqWarps + warp) * 32 + lane;
+        bool near = false;
+        if (mine < nbc) near = box_gap2(qlo, qhi, __ldg(&boxesC[mine * 2]), __ldg(&boxesC[mine * 2 + 1])) < thr2;
+        const unsigned bal = __ballot_sync(0xffffffffu, near);
+        if (lane == j) mymask = bal;
+    }
+    int j = -1;
+    unsigned todo = 0u;
+    // next bucket some lane can reach (level 2), or -1
+    auto next = [&]() -> int {
+        for (;;) {
+            while (!todo) {
+                if (++j >= mygroups) return -1;
+                todo = __shfl_sync(0xffffffffu, mymask, j);
+            }
+            const int cb = (j * kSqWarps + warp) * 32 + __ffs(todo) - 1;
+            todo &= todo - 1;
+            const float4 clo = __ldg(&boxesC[cb * 2]), chi = __ldg(&boxesC[cb * 2 + 1]);
+            // a lane whose row is full only cares about buckets holding an index below its largest kept one
+            const bool want = cnt < nsample || __float_as_int(clo.w) < mxv;
+            if (__any_sync(0xffffffffu, qi >= 0 && want && point_gap2(q, clo, chi) < thr2)) return cb;
+        }
+    };
+    int cur = next();
+    float4 vcur = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (cur >= 0) vcur = __ldg(&sortedC[(size_t)cur * 32 + lane]);
+    while (cur >= 0) {
+        const int nxt = next();  // its candidates are in flight while the current bucket is tested
+        float4 vnxt = vcur;
+        if (nxt >= 0) vnxt = __ldg(&sortedC[(size_t)nxt * 32 + lane]);
+        __syncwarp();
+        tile[lane] = vcur;
+        __syncwarp();
+#pragma unroll 8
+        for (int c32 = 0; c32 < 32; ++c32) {
+            const float4 c = tile[c32];
+            // tf_grouping_g.cu:19-24 (x2 = query, x1 = dataset point); NaN padding never passes
+            if (sqdist(q.x - c.x, q.y - c.y, q.z - c.z) < thr2) {
+                const int k = __float_as_int(c.w);
+                if (cnt < nsample) {
+                    rows[cnt * 33 + lane] = k;
+                    if (k > mxv) { mxv = k; mxp = cnt; }
+                    ++cnt;
+                } else if (k < mxv) {  // keep the nsample smallest indices
+                    rows[mxp * 33 + lane] = k;
+                    mxv = -1;
+                    for (int s2 = 0; s2 < nsample; ++s2) {
+                        const int v = rows[s2 * 33 + lane];
+                        if (v > mxv) { mxv = v; mxp = s2; }
+                    }
+                }
+            }
+        }
+        cur = nxt;
+        vcur = vnxt;
+    }
+    // ascending index order (insertion sort of this lane's <= nsample hits)
+    for (int a = 1; a < cnt; ++a) {
+        const int v = rows[a * 33 + lane];
+        int p = a - 1;
+        while (p >= 0 && rows[p * 33 + lane] > v) {
+            rows[(p + 1) * 33 + lane] = rows[p * 33 + lane];
+            --p;
+        }
+        rows[(p + 1) * 33 + lane] = v;
+    }
+    cnts[warp][lane] = cnt;
+    __syncthreads();
+    if (warp == 0) {  // merge the 4 sorted rows of this lane: the nsample smallest of their union
+        int p[kSqWarps], c[kSqWarps], head[kSqWarps];
+        int total = 0;
+#pragma unroll
+        for (int w = 0; w < kSqWarps; ++w) {
+            p[w] = 0;
+            c[w] = cnts[w][lane];
+            total += c[w];
+            head[w] = c[w] > 0 ? rows_all[(size_t)w * nsample * 33 + lane] : INT_MAX;
+        }
+        total = min(total, nsample);
+        for (int o = 0; o < total; ++o) {
+            int best = 0;
+#pragma unroll
+            for (int w = 1; w < kSqWarps; ++w)
+                if (head[w] < head[best]) best = w;
+            merged[o * 33 + lane] = head[best];
+#pragma unroll
+            for (int w = 0; w < kSqWarps; ++w)
+                if (w == best) {
+                    ++p[w];
+                    head[w] = p[w] < c[w] ? rows_all[((size_t)w * nsample + p[w]) * 33 + lane] : INT_MAX;
+                }
+        }
+        cnts[kSqWarps][lane] = total;
+        if (qi >= 0) pts_cnt[(size_t)scene * m + qi] = total;
+    }
+    __syncthreads();
+    // write-out: warp w writes rows w*8 .. w*8+7, lanes = slots; unused slots repeat the first hit
+    // (:26-29), a row without a hit is written as 0
+    for (int r = warp * 8; r < warp * 8 + 8; ++r) {
+        const int rq = __shfl_sync(0xffffffffu, qi, r);
+        const int rc = cnts[kSqWarps][r];
+        if (rq < 0) continue;
+        int *dst = idx + ((size_t)scene * m + rq) * nsample;
+        const int first = rc > 0 ? merged[r] : 0;
+        for (int s2 = lane; s2 < nsample; s2 += 32) dst[s2] = s2 < rc ? merged[s2 * 33 + r] : first;
+    }
+}
+
+// ---- three_nn: warp = 32 curve-consecutive unknown points; lane = one of them ----------
+__global__ void __launch_bounds__(kSqWarps * 32)
+    three_nn_indexed_kernel(int n, int nbq, int nbc, const float4 *__restrict__ sortedQ,
+                            const float4 *__restrict__ boxesQ, const float4 *__restrict__ sortedC,
+                            const float4 *__restrict__ boxesC, float *__restrict__ dist2, int *__restrict__ idx) {
+    __shared__ __align__(16) float4 tiles[kSqWarps * 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int scene = blockIdx.y;
+    const int qb = blockIdx.x * kSqWarps + warp;
+    if (qb >= nbq) return;
+    float4 *tile = tiles + warp * 32;
+    sortedQ += (size_t)scene * nbq * 32;
+    boxesQ += (size_t)scene * nbq * 2;
+    sortedC += (size_t)scene * nbc * 32;
+    boxesC += (size_t)scene * nbc * 2;
+
+    const float4 q = sortedQ[(size_t)qb * 32 + lane];
+    const int qi = __float_as_int(q.w);
+    const float4 qlo = boxesQ[qb * 2], qhi = boxesQ[qb * 2 + 1];
+    // tf_interpolate_g.cu:36-38: best = 1e40 (+inf once stored as float), besti = 0
+    float b1 = INFINITY, b2 = INFINITY, b3 = INFINITY;
+    int i1 = 0, i2 = 0, i3 = 0;
+
+    auto visit = [&](int cb) {
+        stage_bucket(tile, sortedC, cb, lane);
+#pragma unroll 8
+        for (int j = 0; j < 32; ++j) {
+            const float4 c = tile[j];
+            const float d = sqdist(q.x - c.x, q.y - c.y, q.z - c.z);  // :43-49 (unknown - known)
+            const int k = __float_as_int(c.w);
+            // strict '<' insertion of an ascending scan == rank by (d, k); NaN padding never passes
+            if (d <= b3 && (d < b3 || k < i3)) {  // one compare rejects almost every candidate
+                if (d < b1 || (d == b1 && k < i1)) {
+                    b3 = b2; i3 = i2; b2 = b1; i2 = i1; b1 = d; i1 = k;
+                } else if (d < b2 || (d == b2 && k < i2)) {
+                    b3 = b2; i3 = i2; b2 = d; i2 = k;
+                } else {
+                    b3 = d; i3 = k;
+                }
+            }
+        }
+    };
+    // worst third-best distance of the warp's real lanes, as ordered bits (distances are >= 0)
+    auto threshold = [&]() { return __reduce_max_sync(0xffffffffu, qi >= 0 ? __float_as_uint(b3) : 0u); };
+
+    // pass A: the candidate bucket nearest to this warp's box seeds the bests (and warms L1 with the boxes)
+    const int ngroups = (nbc + 31) >> 5;
+    float lmin = INFINITY;
+    int lwhere = 0;
+#pragma unroll 4
+    for (int g = 0; g < ngroups; ++g) {
+        const int mine = g * 32 + lane;
+        float lb = INFINITY;
+        if (mine < nbc) lb = box_gap2(qlo, qhi, __ldg(&boxesC[mine * 2]), __ldg(&boxesC[mine * 2 + 1]));
+        if (lb < lmin) { lmin = lb; lwhere = mine; }
+    }
+    const uint32_t gmin = __reduce_min_sync(0xffffffffu, __float_as_uint(lmin));
+    const unsigned who = __ballot_sync(0xffffffffu, __float_as_uint(lmin) == gmin);
+    const int seed = __shfl_sync(0xffffffffu, lwhere, __ffs(who) - 1);
+    visit(seed);
+    uint32_t thr = threshold();
+    // pass B: level 1 (bucket box vs warp box, against the warp's threshold), then level 2 (bucket box vs
+    // each lane's point, against that lane's own third best).  '<=': equal distances can still win on index.
+    for (int g = 0; g < ngroups; ++g) {
+        const int mine = g * 32 + lane;
+        float lb = INFINITY;
+        if (mine < nbc && mine != seed) lb = box_gap2(qlo, qhi, __ldg(&boxesC[mine * 2]), __ldg(&boxesC[mine * 2 + 1]));
+        unsigned todo = __ballot_sync(0xffffffffu, mine < nbc && mine != seed && __float_as_uint(lb) <= thr);
+        while (todo) {
+            const int l = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t bound = __float_as_uint(__shfl_sync(0xffffffffu, lb, l));
+            if (bound > thr) continue;  // the threshold has tightened since the ballot
+            const int cb = g * 32 + l;
+            const float4 clo = __ldg(&boxesC[cb * 2]), chi = __ldg(&boxesC[cb * 2 + 1]);
+            if (!__any_sync(0xffffffffu, qi >= 0 && point_gap2(q, clo, chi) <= b3)) continue;
+            visit(cb);
+            thr = threshold();
+        }
+    }
+    if (qi >= 0) {
+        float *dd = dist2 + ((size_t)scene * n + qi) * 3;
+        int *ii = idx + ((size_t)scene * n + qi) * 3;
+        dd[0] = b1; dd[1] = b2; dd[2] = b3;
+        ii[0] = i1; ii[1] = i2; ii[2] = i3;
+    }
+}
+
+int g_spatial_mode = 0;  // 0 = auto, 1 = never (every-pair kernels), 2 = whenever a shape exists
+
+inline int round32(int v) { return (v + 31) & ~31; }
+inline size_t cloud_bytes(int b, int n) { return (size_t)b * round32(n) * 17; }  // 16 B/point + 32 B/bucket
+
+// Is the pruned path used for a call whose query cloud has nq points and candidate cloud nc?
+bool spatial_applies(int nq, int nc) {
+    if (g_spatial_mode == 1) return false;
+    if (nq < 1 || nc < 1 || nq > kMaxIndexed || nc > kMaxIndexed) return false;
+    if (g_spatial_mode == 2) return true;
+    return nq >= 64 && nc >= 64 && (long long)nq * nc >= (1ll << 24);  // measured: tools/spatial_bench.py
+}
+
+struct IndexedPair {
+    CloudDesc q, c;
+};
+
+// Sort both clouds of a call into the workspace (one launch).
+int build_indices(int b, int nq, const float *xyzq, int nc, const float *xyzc, void *workspace, IndexedPair *out,
+                  cudaStream_t s) {
+    unsigned char *w = static_cast<unsigned char *>(workspace);
+    auto carve = [&](int n, const float *xyz) {
+        CloudDesc d;
+        d.xyz = xyz;
+        d.n = n;
+        d.npad = round32(n);
+        d.per_thread = (n + kIdxThreads - 1) / kIdxThreads;
+        d.sorted = reinterpret_cast<float4 *>(w);
+        w += (size_t)b * d.npad * 16;
+        d.boxes = reinterpret_cast<float4 *>(w);
+        w += (size_t)b * (d.npad / 32) * 32;
+        return d;
+    };
+    out->q = carve(nq, xyzq);
+    out->c = carve(nc, xyzc);
+    HF_CUDA_OK(cudaFuncSetAttribute(cloud_index_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIdxSmem));
+    cloud_index_kernel<<<dim3(b, 2), kIdxThreads, kIdxSmem, s>>>(out->q, out->c);
+    HF_LAUNCH_OK("cloud_index_kernel");
+    return HF_OK;
+}
+
+}  // namespace
+}  // namespace hf
+
+extern "C" void hf_spatial_set_mode(int mode) { hf::g_spatial_mode = mode; }
+
+extern "C" size_t hf_spatial_workspace_bytes(int b, int n, int m) {
+    using namespace hf;
+    if (b <= 0 || n <= 0 || m <= 0 || n > kMaxIndexed || m > kMaxIndexed) return 0;
+    return cloud_bytes(b, n) + cloud_bytes(b, m);
+}
+
+extern "C" int hf_query_ball_point_ws(int b, int n, int m, float radius, int nsample, const float *xyz1,
+                                      const float *xyz2, int *idx, int *pts_cnt, void *workspace,
+                                      size_t workspace_bytes, hf_stream_t stream) {
+    using namespace hf;
+    const size_t rowbytes = (size_t)kSqWarps * 32 * sizeof(float4) + (size_t)(kSqWarps + 1) * (nsample > 0 ? nsample : 0) * 33 * sizeof(int);
+    if (!workspace || b <= 0 || m <= 0 || n <= 0 || b > 65535 || !(radius > 0) || nsample <= 0 || nsample > 128 ||
+        !spatial_applies(m, n) || workspace_bytes < hf_spatial_workspace_bytes(b, n, m) ||
+        (reinterpret_cast<uintptr_t>(workspace) & 15) != 0)
+        return hf_query_ball_point(b, n, m, radius, nsample, xyz1, xyz2, idx, pts_cnt, stream);
+    HF_REQUIRE(xyz1 && xyz2 && idx && pts_cnt, "QueryBallPoint: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    IndexedPair ip;
+    int rc = build_indices(b, m, xyz2, n, xyz1, workspace, &ip, s);
+    if (rc != HF_OK) return rc;
+    const int nbq = ip.q.npad / 32, nbc = ip.c.npad / 32;
+    if (rowbytes > 48 * 1024)
+        HF_CUDA_OK(cudaFuncSetAttribute(ball_query_indexed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rowbytes));
+    ball_query_indexed_kernel<<<dim3(nbq, b), kSqWarps * 32, rowbytes, s>>>(
+        m, nsample, ball_threshold(radius), nbq, nbc, ip.q.sorted, ip.q.boxes, ip.c.sorted, ip.c.boxes, idx, pts_cnt);
+    HF_LAUNCH_OK("ball_query_indexed_kernel");
+    return HF_OK;
+}
+
+extern "C" int hf_three_nn_ws(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                              void *workspace, size_t workspace_bytes, hf_stream_t stream) {
+    using namespace hf;
+    if (!workspace || b <= 0 || n <= 0 || m <= 0 || b > 65535 || !spatial_applies(n, m) ||
+        workspace_bytes < hf_spatial_workspace_bytes(b, n, m) || (reinterpret_cast<uintptr_t>(workspace) & 15) != 0)
+        return hf_three_nn(b, n, m, unknown, known, dist2, idx, stream);
+    HF_REQUIRE(unknown && known && dist2 && idx, "ThreeNN: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    IndexedPair ip;
+    int rc = build_indices(b, n, unknown, m, known, workspace, &ip, s);
+    if (rc != HF_OK) return rc;
+    const int nbq = ip.q.npad / 32, nbc = ip.c.npad / 32;
+    const dim3 grid((nbq + kSqWarps - 1) / kSqWarps, b);
+    three_nn_indexed_kernel<<<grid, kSqWarps * 32, 0, s>>>(n, nbq, nbc, ip.q.sorted, ip.q.boxes, ip.c.sorted, ip.c.boxes,
+                                                           dist2, idx);
+    HF_LAUNCH_OK("three_nn_indexed_kernel");
+    return HF_OK;
+}

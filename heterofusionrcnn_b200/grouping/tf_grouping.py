@@ -32,10 +32,14 @@ def query_ball_point(radius, nsample, xyz1, xyz2):
     b, n, m = xyz1.shape[0], xyz1.shape[1], xyz2.shape[1]
     idx = torch.empty((b, m, int(nsample)), dtype=torch.int32, device=xyz1.device)
     pts_cnt = torch.empty((b, m), dtype=torch.int32, device=xyz1.device)
+    lib = _lib.load()
+    # scratch for the spatially pruned kernels (csrc/spatial.cu); 0 bytes = every-pair kernel
+    ws_bytes = int(lib.hf_spatial_workspace_bytes(b, n, m))
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
     with torch.cuda.device(xyz1.device):
-        rc = _lib.load().hf_query_ball_point(
+        rc = lib.hf_query_ball_point_ws(
             b, n, m, float(radius), int(nsample), xyz1.data_ptr(), xyz2.data_ptr(), idx.data_ptr(),
-            pts_cnt.data_ptr(), stream_ptr(xyz1.device))
+            pts_cnt.data_ptr(), ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
     _lib.check(rc, "query_ball_point")
     return idx, pts_cnt
 

@@ -28,9 +28,13 @@ def three_nn(xyz1, xyz2):
     b, n, m = xyz1.shape[0], xyz1.shape[1], xyz2.shape[1]
     dist = torch.empty((b, n, 3), dtype=torch.float32, device=xyz1.device)
     idx = torch.empty((b, n, 3), dtype=torch.int32, device=xyz1.device)
+    lib = _lib.load()
+    # scratch for the spatially pruned kernel (csrc/spatial.cu); 0 bytes = every-pair kernel
+    ws_bytes = int(lib.hf_spatial_workspace_bytes(b, n, m))
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
     with torch.cuda.device(xyz1.device):
-        rc = _lib.load().hf_three_nn(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
-                                     stream_ptr(xyz1.device))
+        rc = lib.hf_three_nn_ws(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
+                                ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
     _lib.check(rc, "three_nn")
     return dist, idx
 

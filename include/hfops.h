@@ -77,6 +77,21 @@ int hf_gather_point(int b, int n, int m, const float *inp, const int *idx, float
 int hf_query_ball_point(int b, int n, int m, float radius, int nsample, const float *xyz1,
                         const float *xyz2, int *idx, int *pts_cnt, hf_stream_t stream);
 
+/* Spatially pruned forms of hf_query_ball_point / hf_three_nn (csrc/spatial.cu): identical
+ * results, but both clouds are first Morton-sorted into `workspace` (caller-provided,
+ * 16-byte aligned, >= hf_spatial_workspace_bytes(b, n, m) bytes, no hidden allocation) and
+ * a warp of 32 neighbouring queries only visits the candidate buckets whose bounding box
+ * is within reach.  With a null / short workspace, clouds beyond 16384 points, or calls too
+ * small to pay for the sort they run the every-pair kernels above.
+ * hf_spatial_set_mode: 0 = auto, 1 = never pruned, 2 = pruned whenever a shape exists (tests). */
+size_t hf_spatial_workspace_bytes(int b, int n, int m);
+void hf_spatial_set_mode(int mode);
+int hf_query_ball_point_ws(int b, int n, int m, float radius, int nsample, const float *xyz1,
+                           const float *xyz2, int *idx, int *pts_cnt, void *workspace,
+                           size_t workspace_bytes, hf_stream_t stream);
+int hf_three_nn_ws(int b, int n, int m, const float *unknown, const float *known, float *dist2,
+                   int *idx, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+
 /* Replaces groupPointLauncher(b,n,c,m,nsample,points,idx,out), grouping/tf_grouping_g.cu:133.
  * points (b,n,c), idx (b,m,nsample) -> out (b,m,nsample,c). */
 int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,

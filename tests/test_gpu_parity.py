@@ -233,6 +233,70 @@ def test_query_ball_point_matches_reference_kernel(cuda):
         assert torch.equal(gidx[hit], ridx[hit])
 
 
+# ---------------------------------------------------------------- spatially pruned ball query / three_nn
+@pytest.fixture
+def pruned(cuda):
+    """Force the pruned kernels of csrc/spatial.cu on every shape they have (default: large calls only)."""
+    from heterofusionrcnn_b200 import _lib
+
+    _lib.load().hf_spatial_set_mode(2)
+    yield
+    _lib.load().hf_spatial_set_mode(0)
+
+
+@pytest.mark.parametrize("b,n,m,r,ns,dup", [(2, 4096, 1024, 0.2, 32, 0), (2, 5000, 777, 0.4, 16, 600), (1, 16384, 300, 0.1, 32, 0),
+                                            (2, 3000, 3000, 2.0, 32, 0), (1, 2048, 512, 50.0, 32, 500), (2, 100, 33, 1.0, 8, 0),
+                                            (1, 31, 1, 0.5, 4, 0), (1, 1, 5, 0.5, 3, 0), (2, 1500, 200, 4.0, 64, 0),
+                                            (1, 6000, 128, 8.0, 128, 1000), (1, 700, 64, 1e-6, 32, 0)])
+def test_query_ball_point_pruned_matches_oracle(cuda, oracle, pruned, b, n, m, r, ns, dup):
+    """Ragged sizes, duplicate points, rows with no hit, rows with far more hits than nsample
+    (the nsample smallest indices must survive), every query inside every ball (r = 50)."""
+    xyz, _ = synthetic.make_scans(n + m + 3, b, n, duplicate_pad=dup)
+    q = (xyz[:, ::-1][:, :m] if m <= n else np.resize(xyz, (b, m, 3))).copy()
+    widx, wcnt = oracle.query_ball_point(r, ns, xyz, q)
+    gidx, gcnt = query_ball_point(r, ns, T(xyz, cuda), T(q, cuda))
+    assert np.array_equal(N(gcnt), wcnt)
+    assert np.array_equal(N(gidx), widx)
+
+
+@pytest.mark.parametrize("b,n,m,dup", [(2, 4096, 1024, 0), (2, 5000, 777, 600), (1, 16384, 300, 2000), (2, 3000, 3000, 0),
+                                       (2, 100, 33, 10), (1, 31, 1, 0), (1, 5, 2, 0), (1, 1, 700, 0), (2, 1500, 3, 0),
+                                       (1, 16384, 16384, 4000)])
+def test_three_nn_pruned_matches_oracle(cuda, oracle, pruned, b, n, m, dup):
+    """Incl. exact distance ties (duplicate points: the lower index must win) and m < 3 (+inf, index 0)."""
+    xyz, _ = synthetic.make_scans(n * 3 + m + 1, b, max(n, m), duplicate_pad=min(dup, max(n, m) - 1))
+    unknown = np.ascontiguousarray(xyz[:, :n])
+    known = xyz[:, ::-1][:, :m].copy()
+    wd, wi = oracle.three_nn(unknown, known)
+    gd, gi = three_nn(T(unknown, cuda), T(known, cuda))
+    assert np.array_equal(N(gi), wi)
+    assert np.array_equal(N(gd), wd)
+
+
+def test_pruned_kernels_equal_every_pair_kernels_on_the_chain_shapes(cuda):
+    """BASELINE config 2 shapes, both radius sets: pruned == every-pair, bit for bit."""
+    from heterofusionrcnn_b200 import _lib
+
+    lib = _lib.load()
+    xyz, _ = synthetic.make_scans(91, 3, 16384, duplicate_pad=1500)
+    x0 = T(xyz, cuda)
+    x1 = gather_point(x0, farthest_point_sample(4096, x0))
+    x2 = gather_point(x1, farthest_point_sample(1024, x1))
+    try:
+        for (a, q, radii) in [(x0, x1, (0.1, 0.5, 4.0)), (x1, x2, (0.2, 1.0))]:
+            lib.hf_spatial_set_mode(1)
+            want_nn = three_nn(a, q)
+            want_bq = [query_ball_point(r, 32, a, q) for r in radii]
+            lib.hf_spatial_set_mode(2)
+            got_nn = three_nn(a, q)
+            got_bq = [query_ball_point(r, 32, a, q) for r in radii]
+            assert torch.equal(got_nn[0], want_nn[0]) and torch.equal(got_nn[1], want_nn[1])
+            for g, w in zip(got_bq, want_bq):
+                assert torch.equal(g[0], w[0]) and torch.equal(g[1], w[1])
+    finally:
+        lib.hf_spatial_set_mode(0)
+
+
 @pytest.mark.parametrize("c", [1, 3, 4, 96, 130, 256])
 def test_group_point(cuda, oracle, c):
     rng = np.random.default_rng(c)
