@@ -59,6 +59,8 @@ def parse_args():
     ap.add_argument("--resident-inflight", type=int, default=1,
                     help="resident leg: batches kept in flight (measured: 2 is slower than 1 - the second batch's FPS "
                          "clusters cannot be gang-scheduled while the first batch's bulk kernels fill every SM)")
+    ap.add_argument("--profile-range", action="store_true",
+                    help="bracket the timed region with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     ap.add_argument("--serial", action="store_true",
                     help="issue the whole chain on one stream in program order (default: independent branches overlap on streams)")
     return ap.parse_args()
@@ -374,11 +376,17 @@ def run_b200(args):
     clocks = ClockSampler(local).start() if rank == 0 else None
     l0 = hf.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if args.profile_range:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     ev0.record()
     for _ in range(args.steps):
         pipe.submit(resident, probe)
     pipe.drain()
     ev1.record()
+    if args.profile_range:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     barrier()
     launches = hf.launch_count() - l0
     ms = max_over_ranks(ev0.elapsed_time(ev1))

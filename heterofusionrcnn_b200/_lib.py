@@ -36,6 +36,12 @@ SIGNATURES = {
     "hf_query_ball_point_ws": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t,
                                         _ptr]),
     "hf_three_nn_ws": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_cloud_index_bytes": (_size_t, [_c_int, _c_int]),
+    "hf_spatial_applies": (_c_int, [_c_int, _c_int]),
+    "hf_cloud_index_build": (_c_int, [_c_int, _c_int, _ptr, _ptr, _size_t, _ptr]),
+    "hf_query_ball_point_indexed": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
+                                             _ptr]),
+    "hf_three_nn_indexed": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_group_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_nn": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_interpolate": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),

@@ -18,7 +18,7 @@ from typing import List
 import numpy as np
 import torch
 
-from . import synthetic
+from . import spatial, synthetic
 from .bev_iou.bev_iou import oriented_nms_batch
 from .cropping.tf_cropping import pc_crop_and_sample
 from .grouping.tf_grouping import group_point, query_ball_point
@@ -137,7 +137,7 @@ class _Lanes:
     intermediate results or on nothing at all.  Issuing those on side streams lets their CTAs
     fill the SM resources the sampling CTAs leave idle:
         crit   fps / gather_point of every level                      (high priority)
-        group  query_ball_point + group_point x2 of level l           (after gather_l)
+        group  [cloud index of level l+1] query_ball_point + group_point x2 of level l  (after gather_l)
         fp     three_nn of every level as soon as its two clouds exist, then the
                three_interpolate calls coarse -> fine (the order the real network needs)
         crop   pc_crop_and_sample                                      (independent)
@@ -231,6 +231,15 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                                              dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
     # ---- set abstraction ----
     nn = [None] * 4
+    # spatial index of each level's cloud, built once and shared by ball query and three_nn of the
+    # two levels that search it (only where the calls are large enough to take the pruned kernels)
+    n_lv = [cfg.points] + list(cfg.npoint)
+    use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
+    index, index_ready = [None] * 5, [None] * 5
+    if use_ix[0]:
+        with on(s_group), probe("cloud_index", level=0, b=b, n=n_lv[0]):
+            index[0] = spatial.build_cloud_index(xyz[0])  # needs only the input: overlaps FPS level 1
+        index_ready[0] = mark(s_group)
     for l in range(4):
         n, m, ns = xyz[l].shape[1], cfg.npoint[l], cfg.nsample
         with on(crit):
@@ -241,17 +250,25 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
         have_xyz = mark(crit)
         after(s_group, have_xyz)
         with on(s_group):
+            if use_ix[l] or (l + 1 < 4 and use_ix[l + 1]):
+                with probe("cloud_index", level=l + 1, b=b, n=m):
+                    index[l + 1] = spatial.build_cloud_index(new_xyz)
+                index_ready[l + 1] = mark(s_group)
+            ix = (index[l], index[l + 1]) if use_ix[l] else (None, None)
             with probe("query_ball_point", level=l + 1, b=b, n=n, m=m, ns=ns):
-                gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz)
+                gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz, index1=ix[0], index2=ix[1])
             with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
                 gxyz = group_point(xyz[l], gidx)
             with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
                 gfeat = group_point(feats[l], gidx)
         # three_nn of FP level l+1 (unknown = level l cloud, known = level l+1 cloud) is geometry only
         after(s_fp, have_xyz)
+        if use_ix[l]:
+            after(s_fp, index_ready[l])
+            after(s_fp, index_ready[l + 1])
         with on(s_fp):
             with probe("three_nn", level=l + 1, b=b, n=n, m=m):
-                dist, nidx = three_nn(xyz[l], new_xyz)
+                dist, nidx = three_nn(xyz[l], new_xyz, index1=ix[0], index2=ix[1])
             with probe("fp_weights_torch", level=l + 1, b=b, n=n):
                 dist, w = _fp_weights(dist)
         nn[l] = (dist, nidx, w)
@@ -316,4 +333,7 @@ class ChainPipeline:
 
 def chain_launches(cfg):
     """Kernels of libhfops launched by one run_chain call."""
-    return 4 * 5 + 4 * 2 + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)
+    n_lv = [cfg.points] + list(cfg.npoint)
+    use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
+    indexed = [use_ix[l] or (l > 0 and use_ix[l - 1]) for l in range(4)] + [use_ix[3]]
+    return 4 * 5 + 4 * 2 + sum(indexed) + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)

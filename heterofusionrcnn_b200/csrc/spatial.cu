@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc c
     // so the pass is in place.
     const int E = cd.per_thread;  // elements per thread, <= kIdxMaxE
     const int np = E * kIdxThreads;
+#pragma unroll 4
     for (int i = t; i < np; i += kIdxThreads) {
         uint32_t c = 0x00FFFFFFu;  // padding sorts last
         if (i < n) {
@@ -549,83 +550,129 @@ bool spatial_applies(int nq, int nc) {
     return nq >= 64 && nc >= 64 && (long long)nq * nc >= (1ll << 24);  // measured: tools/spatial_bench.py
 }
 
-struct IndexedPair {
-    CloudDesc q, c;
-};
+// A cloud index in caller memory: [sorted: b x npad float4][boxes: b x npad/32 x 2 float4].
+CloudDesc carve_index(int b, int n, const float *xyz, void *mem) {
+    unsigned char *w = static_cast<unsigned char *>(mem);
+    CloudDesc d;
+    d.xyz = xyz;
+    d.n = n;
+    d.npad = round32(n);
+    d.per_thread = (n + kIdxThreads - 1) / kIdxThreads;
+    d.sorted = reinterpret_cast<float4 *>(w);
+    d.boxes = reinterpret_cast<float4 *>(w + (size_t)b * d.npad * 16);
+    return d;
+}
 
-// Sort both clouds of a call into the workspace (one launch).
-int build_indices(int b, int nq, const float *xyzq, int nc, const float *xyzc, void *workspace, IndexedPair *out,
-                  cudaStream_t s) {
-    unsigned char *w = static_cast<unsigned char *>(workspace);
-    auto carve = [&](int n, const float *xyz) {
-        CloudDesc d;
-        d.xyz = xyz;
-        d.n = n;
-        d.npad = round32(n);
-        d.per_thread = (n + kIdxThreads - 1) / kIdxThreads;
-        d.sorted = reinterpret_cast<float4 *>(w);
-        w += (size_t)b * d.npad * 16;
-        d.boxes = reinterpret_cast<float4 *>(w);
-        w += (size_t)b * (d.npad / 32) * 32;
-        return d;
-    };
-    out->q = carve(nq, xyzq);
-    out->c = carve(nc, xyzc);
+// Sort one cloud (or the two clouds of a call, in one launch) into their index memory.
+int launch_index(int b, const CloudDesc &a, const CloudDesc *second, cudaStream_t s) {
     HF_CUDA_OK(cudaFuncSetAttribute(cloud_index_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIdxSmem));
-    cloud_index_kernel<<<dim3(b, 2), kIdxThreads, kIdxSmem, s>>>(out->q, out->c);
+    cloud_index_kernel<<<dim3(b, second ? 2 : 1), kIdxThreads, kIdxSmem, s>>>(a, second ? *second : a);
     HF_LAUNCH_OK("cloud_index_kernel");
     return HF_OK;
 }
+
+int launch_ball_query(int b, int m, float radius, int nsample, const CloudDesc &q, const CloudDesc &c, int *idx,
+                      int *pts_cnt, cudaStream_t s) {
+    const size_t rowbytes = (size_t)kSqWarps * 32 * sizeof(float4) + (size_t)(kSqWarps + 1) * nsample * 33 * sizeof(int);
+    const int nbq = q.npad / 32, nbc = c.npad / 32;
+    if (rowbytes > 48 * 1024)
+        HF_CUDA_OK(cudaFuncSetAttribute(ball_query_indexed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rowbytes));
+    ball_query_indexed_kernel<<<dim3(nbq, b), kSqWarps * 32, rowbytes, s>>>(m, nsample, ball_threshold(radius), nbq, nbc,
+                                                                           q.sorted, q.boxes, c.sorted, c.boxes, idx, pts_cnt);
+    HF_LAUNCH_OK("ball_query_indexed_kernel");
+    return HF_OK;
+}
+
+int launch_three_nn(int b, int n, const CloudDesc &q, const CloudDesc &c, float *dist2, int *idx, cudaStream_t s) {
+    const int nbq = q.npad / 32, nbc = c.npad / 32;
+    three_nn_indexed_kernel<<<dim3((nbq + kSqWarps - 1) / kSqWarps, b), kSqWarps * 32, 0, s>>>(
+        n, nbq, nbc, q.sorted, q.boxes, c.sorted, c.boxes, dist2, idx);
+    HF_LAUNCH_OK("three_nn_indexed_kernel");
+    return HF_OK;
+}
+
+inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 }  // namespace
 }  // namespace hf
 
 extern "C" void hf_spatial_set_mode(int mode) { hf::g_spatial_mode = mode; }
+extern "C" int hf_spatial_applies(int nq, int nc) { return hf::spatial_applies(nq, nc) ? 1 : 0; }
+
+extern "C" size_t hf_cloud_index_bytes(int b, int n) {
+    using namespace hf;
+    if (b <= 0 || n <= 0 || n > kMaxIndexed) return 0;
+    return cloud_bytes(b, n);
+}
 
 extern "C" size_t hf_spatial_workspace_bytes(int b, int n, int m) {
+    const size_t a = hf_cloud_index_bytes(b, n), c = hf_cloud_index_bytes(b, m);
+    return (a && c) ? a + c : 0;
+}
+
+extern "C" int hf_cloud_index_build(int b, int n, const float *xyz, void *index, size_t index_bytes, hf_stream_t stream) {
     using namespace hf;
-    if (b <= 0 || n <= 0 || m <= 0 || n > kMaxIndexed || m > kMaxIndexed) return 0;
-    return cloud_bytes(b, n) + cloud_bytes(b, m);
+    HF_REQUIRE(b >= 0 && n >= 1 && n <= kMaxIndexed, "CloudIndex: 1 <= num_points <= %d", kMaxIndexed);
+    HF_REQUIRE(b <= 65535, "CloudIndex: batch_size > 65535 not supported");
+    HF_REQUIRE(xyz && index && aligned16(index), "CloudIndex: null or unaligned pointer");
+    if (index_bytes < hf_cloud_index_bytes(b, n)) {
+        set_error("CloudIndex: index memory too small (%zu < %zu bytes)", index_bytes, hf_cloud_index_bytes(b, n));
+        return HF_ERR_WORKSPACE;
+    }
+    if (b == 0) return HF_OK;
+    return launch_index(b, carve_index(b, n, xyz, index), nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int hf_query_ball_point_indexed(int b, int n, int m, float radius, int nsample, const float *xyz1,
+                                           const float *xyz2, int *idx, int *pts_cnt, const void *index1,
+                                           const void *index2, hf_stream_t stream) {
+    using namespace hf;
+    if (!index1 || !index2 || b <= 0 || m <= 0 || n <= 0 || b > 65535 || !(radius > 0) || nsample <= 0 || nsample > 128 ||
+        !spatial_applies(m, n) || !aligned16(index1) || !aligned16(index2))
+        return hf_query_ball_point(b, n, m, radius, nsample, xyz1, xyz2, idx, pts_cnt, stream);
+    HF_REQUIRE(xyz1 && xyz2 && idx && pts_cnt, "QueryBallPoint: null pointer");
+    return launch_ball_query(b, m, radius, nsample, carve_index(b, m, xyz2, const_cast<void *>(index2)),
+                             carve_index(b, n, xyz1, const_cast<void *>(index1)), idx, pts_cnt, (cudaStream_t)stream);
+}
+
+extern "C" int hf_three_nn_indexed(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                                   const void *index_unknown, const void *index_known, hf_stream_t stream) {
+    using namespace hf;
+    if (!index_unknown || !index_known || b <= 0 || n <= 0 || m <= 0 || b > 65535 || !spatial_applies(n, m) ||
+        !aligned16(index_unknown) || !aligned16(index_known))
+        return hf_three_nn(b, n, m, unknown, known, dist2, idx, stream);
+    HF_REQUIRE(unknown && known && dist2 && idx, "ThreeNN: null pointer");
+    return launch_three_nn(b, n, carve_index(b, n, unknown, const_cast<void *>(index_unknown)),
+                           carve_index(b, m, known, const_cast<void *>(index_known)), dist2, idx, (cudaStream_t)stream);
 }
 
 extern "C" int hf_query_ball_point_ws(int b, int n, int m, float radius, int nsample, const float *xyz1,
                                       const float *xyz2, int *idx, int *pts_cnt, void *workspace,
                                       size_t workspace_bytes, hf_stream_t stream) {
     using namespace hf;
-    const size_t rowbytes = (size_t)kSqWarps * 32 * sizeof(float4) + (size_t)(kSqWarps + 1) * (nsample > 0 ? nsample : 0) * 33 * sizeof(int);
     if (!workspace || b <= 0 || m <= 0 || n <= 0 || b > 65535 || !(radius > 0) || nsample <= 0 || nsample > 128 ||
-        !spatial_applies(m, n) || workspace_bytes < hf_spatial_workspace_bytes(b, n, m) ||
-        (reinterpret_cast<uintptr_t>(workspace) & 15) != 0)
+        !spatial_applies(m, n) || workspace_bytes < hf_spatial_workspace_bytes(b, n, m) || !aligned16(workspace))
         return hf_query_ball_point(b, n, m, radius, nsample, xyz1, xyz2, idx, pts_cnt, stream);
     HF_REQUIRE(xyz1 && xyz2 && idx && pts_cnt, "QueryBallPoint: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
-    IndexedPair ip;
-    int rc = build_indices(b, m, xyz2, n, xyz1, workspace, &ip, s);
+    const CloudDesc c = carve_index(b, n, xyz1, workspace);
+    const CloudDesc q = carve_index(b, m, xyz2, static_cast<unsigned char *>(workspace) + cloud_bytes(b, n));
+    int rc = launch_index(b, c, &q, s);
     if (rc != HF_OK) return rc;
-    const int nbq = ip.q.npad / 32, nbc = ip.c.npad / 32;
-    if (rowbytes > 48 * 1024)
-        HF_CUDA_OK(cudaFuncSetAttribute(ball_query_indexed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rowbytes));
-    ball_query_indexed_kernel<<<dim3(nbq, b), kSqWarps * 32, rowbytes, s>>>(
-        m, nsample, ball_threshold(radius), nbq, nbc, ip.q.sorted, ip.q.boxes, ip.c.sorted, ip.c.boxes, idx, pts_cnt);
-    HF_LAUNCH_OK("ball_query_indexed_kernel");
-    return HF_OK;
+    return launch_ball_query(b, m, radius, nsample, q, c, idx, pts_cnt, s);
 }
 
 extern "C" int hf_three_nn_ws(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
                               void *workspace, size_t workspace_bytes, hf_stream_t stream) {
     using namespace hf;
     if (!workspace || b <= 0 || n <= 0 || m <= 0 || b > 65535 || !spatial_applies(n, m) ||
-        workspace_bytes < hf_spatial_workspace_bytes(b, n, m) || (reinterpret_cast<uintptr_t>(workspace) & 15) != 0)
+        workspace_bytes < hf_spatial_workspace_bytes(b, n, m) || !aligned16(workspace))
         return hf_three_nn(b, n, m, unknown, known, dist2, idx, stream);
     HF_REQUIRE(unknown && known && dist2 && idx, "ThreeNN: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
-    IndexedPair ip;
-    int rc = build_indices(b, n, unknown, m, known, workspace, &ip, s);
+    const CloudDesc q = carve_index(b, n, unknown, workspace);
+    const CloudDesc c = carve_index(b, m, known, static_cast<unsigned char *>(workspace) + cloud_bytes(b, n));
+    int rc = launch_index(b, q, &c, s);
     if (rc != HF_OK) return rc;
-    const int nbq = ip.q.npad / 32, nbc = ip.c.npad / 32;
-    const dim3 grid((nbq + kSqWarps - 1) / kSqWarps, b);
-    three_nn_indexed_kernel<<<grid, kSqWarps * 32, 0, s>>>(n, nbq, nbc, ip.q.sorted, ip.q.boxes, ip.c.sorted, ip.c.boxes,
-                                                           dist2, idx);
-    HF_LAUNCH_OK("three_nn_indexed_kernel");
-    return HF_OK;
+    return launch_three_nn(b, n, q, c, dist2, idx, s);
 }

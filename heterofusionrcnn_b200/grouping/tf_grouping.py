@@ -8,7 +8,7 @@ from .. import _lib
 from .._tensors import dev_tensor, require, stream_ptr
 
 
-def query_ball_point(radius, nsample, xyz1, xyz2):
+def query_ball_point(radius, nsample, xyz1, xyz2, index1=None, index2=None):
     """
     Input:
         radius: float32, ball search radius
@@ -21,6 +21,8 @@ def query_ball_point(radius, nsample, xyz1, xyz2):
 
     Reference: grouping/tf_grouping.py:11-23, op checks grouping/tf_grouping.cpp:67-106.
     Rows with no point in the ball are returned as 0 (uninitialised in the reference).
+    index1 / index2 (optional, not in the reference): spatial.CloudIndex of xyz1 / xyz2, to share
+    one sort between several ops on the same clouds; results do not depend on them.
     """
     require(float(radius) > 0, "QueryBallPoint expects positive radius")
     require(int(nsample) > 0, "QueryBallPoint expects positive nsample")
@@ -33,13 +35,20 @@ def query_ball_point(radius, nsample, xyz1, xyz2):
     idx = torch.empty((b, m, int(nsample)), dtype=torch.int32, device=xyz1.device)
     pts_cnt = torch.empty((b, m), dtype=torch.int32, device=xyz1.device)
     lib = _lib.load()
-    # scratch for the spatially pruned kernels (csrc/spatial.cu); 0 bytes = every-pair kernel
-    ws_bytes = int(lib.hf_spatial_workspace_bytes(b, n, m))
-    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
+    p1 = index1.ptr_for(xyz1) if index1 is not None else None
+    p2 = index2.ptr_for(xyz2) if index2 is not None else None
     with torch.cuda.device(xyz1.device):
-        rc = lib.hf_query_ball_point_ws(
-            b, n, m, float(radius), int(nsample), xyz1.data_ptr(), xyz2.data_ptr(), idx.data_ptr(),
-            pts_cnt.data_ptr(), ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
+        if p1 is not None and p2 is not None:
+            rc = lib.hf_query_ball_point_indexed(
+                b, n, m, float(radius), int(nsample), xyz1.data_ptr(), xyz2.data_ptr(), idx.data_ptr(),
+                pts_cnt.data_ptr(), p1, p2, stream_ptr(xyz1.device))
+        else:
+            # scratch for the spatially pruned kernels (csrc/spatial.cu); 0 bytes = every-pair kernel
+            ws_bytes = int(lib.hf_spatial_workspace_bytes(b, n, m)) if lib.hf_spatial_applies(m, n) else 0
+            ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
+            rc = lib.hf_query_ball_point_ws(
+                b, n, m, float(radius), int(nsample), xyz1.data_ptr(), xyz2.data_ptr(), idx.data_ptr(),
+                pts_cnt.data_ptr(), ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
     _lib.check(rc, "query_ball_point")
     return idx, pts_cnt
 

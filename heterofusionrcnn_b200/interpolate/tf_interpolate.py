@@ -8,7 +8,7 @@ from .. import _lib
 from .._tensors import dev_tensor, require, stream_ptr
 
 
-def three_nn(xyz1, xyz2):
+def three_nn(xyz1, xyz2, index1=None, index2=None):
     """
     Input:
         xyz1: (b,n,3) float32 array, unknown points
@@ -19,6 +19,8 @@ def three_nn(xyz1, xyz2):
 
     Reference: interpolate/tf_interpolate.py:11-20, op checks interpolate/tf_interpolate.cpp:63-96.
     As in the reference kernel the "distances" are SQUARED distances, ascending.
+    index1 / index2 (optional, not in the reference): spatial.CloudIndex of xyz1 / xyz2, to share
+    one sort between several ops on the same clouds; results do not depend on them.
     """
     xyz1 = dev_tensor(xyz1, torch.float32, "xyz1")
     xyz2 = dev_tensor(xyz2, torch.float32, "xyz2")
@@ -29,12 +31,18 @@ def three_nn(xyz1, xyz2):
     dist = torch.empty((b, n, 3), dtype=torch.float32, device=xyz1.device)
     idx = torch.empty((b, n, 3), dtype=torch.int32, device=xyz1.device)
     lib = _lib.load()
-    # scratch for the spatially pruned kernel (csrc/spatial.cu); 0 bytes = every-pair kernel
-    ws_bytes = int(lib.hf_spatial_workspace_bytes(b, n, m))
-    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
+    p1 = index1.ptr_for(xyz1) if index1 is not None else None
+    p2 = index2.ptr_for(xyz2) if index2 is not None else None
     with torch.cuda.device(xyz1.device):
-        rc = lib.hf_three_nn_ws(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
-                                ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
+        if p1 is not None and p2 is not None:
+            rc = lib.hf_three_nn_indexed(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
+                                         p1, p2, stream_ptr(xyz1.device))
+        else:
+            # scratch for the spatially pruned kernel (csrc/spatial.cu); 0 bytes = every-pair kernel
+            ws_bytes = int(lib.hf_spatial_workspace_bytes(b, n, m)) if lib.hf_spatial_applies(n, m) else 0
+            ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
+            rc = lib.hf_three_nn_ws(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
+                                    ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
     _lib.check(rc, "three_nn")
     return dist, idx
 

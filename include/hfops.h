@@ -91,6 +91,23 @@ int hf_query_ball_point_ws(int b, int n, int m, float radius, int nsample, const
                            size_t workspace_bytes, hf_stream_t stream);
 int hf_three_nn_ws(int b, int n, int m, const float *unknown, const float *known, float *dist2,
                    int *idx, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* The same kernels with the sort factored out, for callers that run several ops on one cloud
+ * (a PointNet++ level runs ball query and three_nn on the same two clouds): build the index of a
+ * cloud (b,n,3) once into caller memory (16-byte aligned, hf_cloud_index_bytes(b, n) bytes; 0 =
+ * cloud too large to index) and pass it to any number of calls that take that cloud.  index1 /
+ * index_unknown belong to xyz1 / unknown, index2 / index_known to xyz2 / known; a null index
+ * (or a call too small to profit) runs the every-pair kernel. */
+size_t hf_cloud_index_bytes(int b, int n);
+/* 1 if a call with nq query points and nc candidate points would take the pruned kernels. */
+int hf_spatial_applies(int nq, int nc);
+int hf_cloud_index_build(int b, int n, const float *xyz, void *index, size_t index_bytes,
+                         hf_stream_t stream);
+int hf_query_ball_point_indexed(int b, int n, int m, float radius, int nsample, const float *xyz1,
+                                const float *xyz2, int *idx, int *pts_cnt, const void *index1,
+                                const void *index2, hf_stream_t stream);
+int hf_three_nn_indexed(int b, int n, int m, const float *unknown, const float *known,
+                        float *dist2, int *idx, const void *index_unknown,
+                        const void *index_known, hf_stream_t stream);
 
 /* Replaces groupPointLauncher(b,n,c,m,nsample,points,idx,out), grouping/tf_grouping_g.cu:133.
  * points (b,n,c), idx (b,m,nsample) -> out (b,m,nsample,c). */

@@ -9,13 +9,14 @@ tail -3 $OUT/${TAG}_pytest.log
 python __graft_entry__.py smoke > $OUT/${TAG}_smoke.log 2>&1; echo "smoke rc=$?"; tail -1 $OUT/${TAG}_smoke.log
 python bench.py --table > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench_table.txt; echo "bench rc=$?"
 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>$OUT/${TAG}_bench_ref.err; echo "ref rc=$?"
-PROF="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --serial"
+PROF="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --serial --profile-range"
 $PROF > $OUT/${TAG}_plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -s 160 -c 110 --csv --log-file $OUT/${TAG}_launches.csv $PROF > $OUT/${TAG}_ncu1.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 200 --csv --log-file $OUT/${TAG}_launches.csv $PROF > $OUT/${TAG}_ncu1.log 2>&1
 echo "launch list rc=$?"
 $PROF > $OUT/${TAG}_plain2.log 2>&1 &&
 ncu --set full --clock-control none --import-source on \
-    -k 'regex:crop_kernel|group_point_vec4|three_interpolate_nlc_vec4|fps_cluster|fps_multi|nms_filter|nms_clip|nms_sweep|three_nn_kernel|query_ball' \
-    -s 69 -c 23 -o $OUT/${TAG}_full $PROF > $OUT/${TAG}_ncu2.log 2>&1
+    --profile-from-start off \
+    -k 'regex:crop_kernel|group_point_vec4|three_interpolate_nlc_vec4|fps_cluster|fps_multi|nms_filter|nms_clip|nms_sweep|three_nn|query_ball|ball_query|cloud_index' \
+    -c 40 -o $OUT/${TAG}_full $PROF > $OUT/${TAG}_ncu2.log 2>&1
 echo "full capture rc=$?"
 ls -la $OUT
