@@ -316,7 +316,21 @@ int launch_fps_multi(int b, int n, int m, const float *inp, int *out, cudaStream
 }
 
 template <int C>
-int dispatch_multi(int per, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {
+int dispatch_multi(int per, int warps, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {
+    // warps per CTA: 4 by default (one per scheduler: the shortest latency chain); 8 / 16 put the same
+    // number of groups on half / a quarter of the SMs (hf_fps_set_variant(3, warps, 0)).
+    if constexpr (C <= 4) {
+      if (warps == 8 && per <= 4096) {
+        if (per <= 2048) return launch_fps_multi<C, 8, 8>(b, n, m, inp, out, s);
+        return launch_fps_multi<C, 8, 16>(b, n, m, inp, out, s);
+      }
+    }
+    if constexpr (C <= 2) {
+      if (warps == 16 && per <= 8192) {
+        if (per <= 4096) return launch_fps_multi<C, 16, 8>(b, n, m, inp, out, s);
+        return launch_fps_multi<C, 16, 16>(b, n, m, inp, out, s);
+      }
+    }
     if (per <= 512) return launch_fps_multi<C, 4, 4>(b, n, m, inp, out, s);
     if (per <= 1024) return launch_fps_multi<C, 4, 8>(b, n, m, inp, out, s);
     if (per <= 2048) return launch_fps_multi<C, 4, 16>(b, n, m, inp, out, s);
@@ -331,7 +345,7 @@ int dispatch_multi(int per, int b, int n, int m, const float *inp, int *out, cud
 // 1 CTA up to 512 points, 2 up to 2048, 4 up to 4096, else 8; halved while the batch would not
 // fit the GPU in one wave and a CTA still holds <= 4096 points.  Returns HF_ERR_UNSUPPORTED
 // for clouds beyond 8 x 8192 points.
-int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req) {
+int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req, int warps_req) {
     int cluster = 1;
     if (cluster_req == 1 || cluster_req == 2 || cluster_req == 4 || cluster_req == 8) {
         cluster = cluster_req;
@@ -339,14 +353,23 @@ int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStre
         cluster = n <= 512 ? 1 : n <= 2048 ? 2 : n <= 4096 ? 4 : 8;
         const int sms = num_sms();
         while (cluster > 1 && (long long)b * cluster > sms && (n + cluster / 2 - 1) / (cluster / 2) <= 4096) cluster >>= 1;
+        // A B200 co-schedules 15 clusters of 8 CTAs, not 18 (a cluster must sit inside one GPC:
+        // profiles/r1_fps_wave_probe.txt): from the 16th scene on, clusters share SMs and every
+        // scene runs at two warps per scheduler anyway (0.83 -> 1.18 ms for 16384 -> 4096).  Then
+        // 4 CTAs of 8 warps hold the same 32 groups on half the SMs for 5% more time alone, and
+        // leave the other half of the GPU to concurrent kernels (chain: 2.76 -> 2.56 ms/step).
+        if (cluster == 8 && warps_req == 0 && b > 15 && (n + 3) / 4 <= 4096) {
+            cluster = 4;
+            warps_req = 8;
+        }
     }
     while (cluster < 8 && (n + cluster - 1) / cluster > 8192) cluster <<= 1;
     const int per = (n + cluster - 1) / cluster;
     switch (cluster) {
-        case 1: return dispatch_multi<1>(per, b, n, m, inp, out, s);
-        case 2: return dispatch_multi<2>(per, b, n, m, inp, out, s);
-        case 4: return dispatch_multi<4>(per, b, n, m, inp, out, s);
-        default: return dispatch_multi<8>(per, b, n, m, inp, out, s);
+        case 1: return dispatch_multi<1>(per, warps_req, b, n, m, inp, out, s);
+        case 2: return dispatch_multi<2>(per, warps_req, b, n, m, inp, out, s);
+        case 4: return dispatch_multi<4>(per, warps_req, b, n, m, inp, out, s);
+        default: return dispatch_multi<8>(per, warps_req, b, n, m, inp, out, s);
     }
 }
 

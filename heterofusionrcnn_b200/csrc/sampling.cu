@@ -22,7 +22,7 @@ namespace hf {
 // fps_bucket.cu: the bucket-pruned kernel (default for clouds it covers)
 int fps_bucket_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int w_req, int j_req);
 // fps_multi.cu: the multi-pick kernel (default for clouds of up to 65536 points)
-int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req);
+int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req, int warps_req);
 
 namespace {
 
@@ -363,7 +363,7 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
     // DSMEM exchange.  algo 1 = the one-pick-per-exchange cluster kernel below, which also
     // serves clouds the multi-pick kernel has no shape for.
     if (g_algo == 0 || g_algo == 3) {
-        int rc = fps_multi_dispatch(b, n, m, inp, out, s, g_cluster_override);
+        int rc = fps_multi_dispatch(b, n, m, inp, out, s, g_cluster_override, g_algo == 3 ? g_bucket_w : 0);
         if (rc != HF_ERR_UNSUPPORTED) return rc;
         if (g_algo == 3) {
             set_error("FarthestPointSample: multi-pick kernel has no shape for n=%d", n);
