@@ -42,6 +42,14 @@ SIGNATURES = {
     "hf_query_ball_point_indexed": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                              _ptr]),
     "hf_three_nn_indexed": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "hf_scatter_workspace_bytes": (_size_t, [_c_int, _c_int, _c_int]),
+    "hf_gather_point_grad": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_group_point_grad": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_three_interpolate_grad": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_three_interpolate_grad_nlc": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t,
+                                               _ptr]),
+    "hf_pc_crop_and_sample_grad_fts": (_c_int, [_ptr, _ptr, _ptr, _c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr,
+                                                _size_t, _ptr]),
     "hf_group_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_nn": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_interpolate": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),

@@ -24,3 +24,10 @@ def dev_tensor(t, dtype, name):
 
 def stream_ptr(device):
     return torch.cuda.current_stream(device).cuda_stream
+
+
+def scatter_workspace(lib, scenes, dst_rows, entries, device):
+    """Scratch of the deterministic scatter-add gradients (csrc/backward.cu)."""
+    nbytes = int(lib.hf_scatter_workspace_bytes(int(scenes), int(dst_rows), int(entries)))
+    require(nbytes > 0, "gradient: more than 2^31 destination rows or entries")
+    return torch.empty((nbytes,), dtype=torch.uint8, device=device), nbytes

@@ -5,7 +5,7 @@ Native code: csrc/cropping.cu via include/hfops.h.
 import torch
 
 from .. import _lib
-from .._tensors import dev_tensor, require, stream_ptr
+from .._tensors import dev_tensor, require, scatter_workspace, stream_ptr
 
 
 def pc_crop_and_sample(pts, fts, intensities, mask, boxes, box_ind, resize):
@@ -66,3 +66,36 @@ def pc_crop_and_sample(pts, fts, intensities, mask, boxes, box_ind, resize):
             crop_mask.data_ptr(), crop_ind.data_ptr(), non_empty.data_ptr(), stream_ptr(dev))
     _lib.check(rc, "pc_crop_and_sample")
     return crop_pts, crop_fts, crop_int, crop_mask, crop_ind, non_empty
+
+
+def pc_crop_and_sample_grad_fts(fts, box_ind, crop_ind, grad_crop_fts):
+    """Gradient of pc_crop_and_sample w.r.t. fts (the reference's PcCropAndSampleGradFts op,
+    cropping/tf_cropping.py:36-46, op checks cropping/tf_cropping.cpp:200-235).
+
+    fts (B,P,C) [shape only], box_ind (N) int32, crop_ind (N,R) int32, grad_crop_fts (N,R,C) -> grad_fts (B,P,C).
+    Deterministic: a point's contributions are added in ascending (box, slot) order.
+    """
+    fts = dev_tensor(fts, torch.float32, "fts")
+    box_ind = dev_tensor(box_ind, torch.int32, "box_ind")
+    crop_ind = dev_tensor(crop_ind, torch.int32, "crop_ind")
+    grad_crop_fts = dev_tensor(grad_crop_fts, torch.float32, "grad_crop_fts")
+    require(fts.dim() == 3 and grad_crop_fts.dim() == 3 and fts.shape[2] == grad_crop_fts.shape[2],
+            "PcCropAndSampleGradFts expects fts and grad_crop_fts has same shape(2)")
+    require(box_ind.dim() == 1 and crop_ind.dim() == 2 and box_ind.shape[0] == crop_ind.shape[0] == grad_crop_fts.shape[0],
+            "PcCropAndSampleGradFts expects box_ind, crop_ind and grad_crop_fts has same shape(0)")
+    require(crop_ind.shape[1] == grad_crop_fts.shape[1],
+            "PcCropAndSampleGradFts expects crop_ind and grad_crop_fts has same shape(1)")
+    batch, npts, c = fts.shape
+    nb, r = crop_ind.shape
+    require(npts > 0 and c > 0 and batch > 0, "PcCropAndSampleGradFts expects (B, P, C) fts shape")
+    grad_fts = torch.empty((batch, npts, c), dtype=torch.float32, device=fts.device)
+    if nb == 0 or r == 0:
+        return grad_fts.zero_()
+    lib = _lib.load()
+    ws, ws_bytes = scatter_workspace(lib, 1, batch * npts, nb * r, fts.device)
+    with torch.cuda.device(fts.device):
+        rc = lib.hf_pc_crop_and_sample_grad_fts(box_ind.data_ptr(), crop_ind.data_ptr(), grad_crop_fts.data_ptr(), nb, batch,
+                                                npts, r, c, grad_fts.data_ptr(), ws.data_ptr(), ws_bytes,
+                                                stream_ptr(fts.device))
+    _lib.check(rc, "pc_crop_and_sample_grad_fts")
+    return grad_fts

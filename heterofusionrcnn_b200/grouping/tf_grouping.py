@@ -5,7 +5,7 @@ Native code: csrc/grouping.cu via include/hfops.h.
 import torch
 
 from .. import _lib
-from .._tensors import dev_tensor, require, stream_ptr
+from .._tensors import dev_tensor, require, scatter_workspace, stream_ptr
 
 
 def query_ball_point(radius, nsample, xyz1, xyz2, index1=None, index2=None):
@@ -75,3 +75,29 @@ def group_point(points, idx):
                                         stream_ptr(points.device))
     _lib.check(rc, "group_point")
     return out
+
+
+def group_point_grad(points, idx, grad_out):
+    """Gradient of group_point w.r.t. points (the reference's GroupPointGrad op,
+    grouping/tf_grouping.py:55-59, op checks grouping/tf_grouping.cpp:173-208).
+
+    points (b,n,c) [shape only], idx (b,m,nsample) int32, grad_out (b,m,nsample,c) -> grad_points (b,n,c).
+    Deterministic: a point's contributions are added in ascending (row, sample) order.
+    """
+    points = dev_tensor(points, torch.float32, "points")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    grad_out = dev_tensor(grad_out, torch.float32, "grad_out")
+    require(points.dim() == 3, "GroupPointGrad expects (batch_size, num_points, channel) points shape")
+    b, n, c = points.shape
+    require(idx.dim() == 3 and idx.shape[0] == b, "GroupPointGrad expects (batch_size, npoints, nsample) idx shape")
+    m, nsample = idx.shape[1], idx.shape[2]
+    require(grad_out.dim() == 4 and tuple(grad_out.shape) == (b, m, nsample, c),
+            "GroupPointGrad expects (batch_size, npoints, nsample, channel) grad_out shape")
+    grad_points = torch.empty((b, n, c), dtype=torch.float32, device=points.device)
+    lib = _lib.load()
+    ws, ws_bytes = scatter_workspace(lib, b, n, m * nsample, points.device)
+    with torch.cuda.device(points.device):
+        rc = lib.hf_group_point_grad(b, n, c, m, nsample, grad_out.data_ptr(), idx.data_ptr(), grad_points.data_ptr(),
+                                     ws.data_ptr(), ws_bytes, stream_ptr(points.device))
+    _lib.check(rc, "group_point_grad")
+    return grad_points

@@ -5,7 +5,7 @@ Native code: csrc/interpolate.cu via include/hfops.h.
 import torch
 
 from .. import _lib
-from .._tensors import dev_tensor, require, stream_ptr
+from .._tensors import dev_tensor, require, scatter_workspace, stream_ptr
 
 
 def three_nn(xyz1, xyz2, index1=None, index2=None):
@@ -93,3 +93,52 @@ def three_interpolate_channel_first(points, idx, weight):
                                               out.data_ptr(), stream_ptr(points.device))
     _lib.check(rc, "three_interpolate")
     return out
+
+
+def _interp_grad_args(points, idx, weight, grad_out, channel_first):
+    points = dev_tensor(points, torch.float32, "points")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    weight = dev_tensor(weight, torch.float32, "weight")
+    grad_out = dev_tensor(grad_out, torch.float32, "grad_out")
+    lay = "(b,c,m)" if channel_first else "(b,m,c)"
+    require(points.dim() == 3, "ThreeInterpolateGrad expects %s points shape" % lay)
+    b = points.shape[0]
+    c, m = (points.shape[1], points.shape[2]) if channel_first else (points.shape[2], points.shape[1])
+    require(idx.dim() == 3 and idx.shape[0] == b and idx.shape[2] == 3, "ThreeInterpolateGrad expects (b,n,3) idx shape")
+    n = idx.shape[1]
+    require(weight.dim() == 3 and tuple(weight.shape) == (b, n, 3), "ThreeInterpolateGrad expects (b,n,3) weight shape")
+    want = (b, c, n) if channel_first else (b, n, c)
+    require(tuple(grad_out.shape) == want,
+            "ThreeInterpolateGrad expects %s grad_out shape" % ("(b,c,n)" if channel_first else "(b,n,c)"))
+    return points, idx, weight, grad_out, b, c, m, n
+
+
+def three_interpolate_grad(points, idx, weight, grad_out):
+    """Gradient of three_interpolate w.r.t. points in the Python API's layout
+    (interpolate/tf_interpolate.py:40-49 with the transposes of :35-37 folded in):
+    points (b,m,c) [shape only], idx / weight (b,n,3), grad_out (b,n,c) -> grad_points (b,m,c).
+    Deterministic: contributions are added in ascending (point, neighbour) order.
+    """
+    points, idx, weight, grad_out, b, c, m, n = _interp_grad_args(points, idx, weight, grad_out, False)
+    grad_points = torch.empty((b, m, c), dtype=torch.float32, device=points.device)
+    lib = _lib.load()
+    ws, ws_bytes = scatter_workspace(lib, b, m, 3 * n, points.device)
+    with torch.cuda.device(points.device):
+        rc = lib.hf_three_interpolate_grad_nlc(b, n, c, m, grad_out.data_ptr(), idx.data_ptr(), weight.data_ptr(),
+                                               grad_points.data_ptr(), ws.data_ptr(), ws_bytes, stream_ptr(points.device))
+    _lib.check(rc, "three_interpolate_grad")
+    return grad_points
+
+
+def three_interpolate_grad_channel_first(points, idx, weight, grad_out):
+    """The native ThreeInterpolateGrad op's own layout (interpolate/tf_interpolate.cpp:141-185):
+    points (b,c,m), grad_out (b,c,n) -> grad_points (b,c,m)."""
+    points, idx, weight, grad_out, b, c, m, n = _interp_grad_args(points, idx, weight, grad_out, True)
+    grad_points = torch.empty((b, c, m), dtype=torch.float32, device=points.device)
+    lib = _lib.load()
+    ws, ws_bytes = scatter_workspace(lib, b, m, 3 * n, points.device)
+    with torch.cuda.device(points.device):
+        rc = lib.hf_three_interpolate_grad(b, c, n, m, grad_out.data_ptr(), idx.data_ptr(), weight.data_ptr(),
+                                           grad_points.data_ptr(), ws.data_ptr(), ws_bytes, stream_ptr(points.device))
+    _lib.check(rc, "three_interpolate_grad")
+    return grad_points

@@ -6,7 +6,7 @@ buffers) instead of lazy TF graph nodes.  Native code: csrc/sampling.cu via incl
 import torch
 
 from .. import _lib
-from .._tensors import dev_tensor, require, stream_ptr
+from .._tensors import dev_tensor, require, scatter_workspace, stream_ptr
 
 # FPS keeps clouds of up to this many points entirely on chip; beyond it the kernel needs
 # the reference's (32, n) float scratch (sampling/tf_sampling.cpp:115).
@@ -62,3 +62,29 @@ returns:
             stream_ptr(inp.device))
     _lib.check(rc, "farthest_point_sample")
     return out
+
+
+def gather_point_grad(inp, idx, out_g):
+    """Gradient of gather_point w.r.t. inp (the reference's GatherPointGrad op,
+    sampling/tf_sampling.py:54-58, op checks sampling/tf_sampling.cpp:150-179).
+
+    inp (b,n,3) [shape only], idx (b,m) int32, out_g (b,m,3) -> inp_g (b,n,3).
+    Deterministic: contributions of a repeated index are added in ascending position.
+    """
+    inp = dev_tensor(inp, torch.float32, "inp")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    out_g = dev_tensor(out_g, torch.float32, "out_g")
+    require(inp.dim() == 3 and inp.shape[2] == 3, "GatherPointGradGpuOp expects (batch_size,num_points,3) inp")
+    b, n = inp.shape[0], inp.shape[1]
+    require(idx.dim() == 2 and idx.shape[0] == b, "GatherPointGradGpuOp expects (batch_size,num_result) idx shape")
+    m = idx.shape[1]
+    require(out_g.dim() == 3 and tuple(out_g.shape) == (b, m, 3),
+            "GatherPointGradGpuOp expects (batch_size,num_result,3) out_g shape")
+    inp_g = torch.empty((b, n, 3), dtype=torch.float32, device=inp.device)
+    lib = _lib.load()
+    ws, ws_bytes = scatter_workspace(lib, b, n, m, inp.device)
+    with torch.cuda.device(inp.device):
+        rc = lib.hf_gather_point_grad(b, n, m, out_g.data_ptr(), idx.data_ptr(), inp_g.data_ptr(), ws.data_ptr(), ws_bytes,
+                                      stream_ptr(inp.device))
+    _lib.check(rc, "gather_point_grad")
+    return inp_g

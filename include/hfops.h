@@ -184,6 +184,44 @@ void hf_nms_set_spatial_sort(int on);
 long long hf_oriented_nms_last_pair_count(int scenes, int boxes_num, const void *workspace,
                                           hf_stream_t stream);
 
+/* ---- gradients ------------------------------ */
+/* The four scatter-add gradients, deterministic: each output row is the sum of its
+ * contributions in ascending entry order (= the reference's loops run serially), written
+ * exactly once — no float atomics, no memset of the output (the reference wrappers issue one:
+ * tf_sampling.cpp:174, tf_interpolate.cpp:178).  Entries whose index is out of range are
+ * skipped.  All take caller workspace of hf_scatter_workspace_bytes(scenes, dst_rows, entries)
+ * bytes, 16-byte aligned:
+ *   gather_point_grad          (b, n, m)                    group_point_grad (b, n, m*nsample)
+ *   three_interpolate_grad*    (b, m, 3*n)                  crop grad_fts    (1, batch*npts, num_boxes*resize) */
+size_t hf_scatter_workspace_bytes(int scenes, int dst_rows, int entries);
+/* Replaces scatteraddpointLauncher(b,n,m,out_g,idx,inp_g), sampling/tf_sampling_g.cu:209.
+ * out_g (b,m,3), idx (b,m) -> inp_g (b,n,3). */
+int hf_gather_point_grad(int b, int n, int m, const float *out_g, const int *idx, float *inp_g,
+                         void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* Replaces groupPointGradLauncher(b,n,c,m,nsample,grad_out,idx,grad_points),
+ * grouping/tf_grouping_g.cu:137.  grad_out (b,m,nsample,c), idx (b,m,nsample) -> grad_points (b,n,c). */
+int hf_group_point_grad(int b, int n, int c, int m, int nsample, const float *grad_out,
+                        const int *idx, float *grad_points, void *workspace,
+                        size_t workspace_bytes, hf_stream_t stream);
+/* Replaces three_interpolate_grad_gpu(b,c,n,m,grad_out,idx,weight,grad_points),
+ * interpolate/tf_interpolate_g.cu:157 (channel-first): grad_out (b,c,n), idx / weight (b,n,3)
+ * -> grad_points (b,c,m).  _nlc is the channel-last form that matches the Python API's
+ * tensors: grad_out (b,n,c) -> grad_points (b,m,c). */
+int hf_three_interpolate_grad(int b, int c, int n, int m, const float *grad_out, const int *idx,
+                              const float *weight, float *grad_points, void *workspace,
+                              size_t workspace_bytes, hf_stream_t stream);
+int hf_three_interpolate_grad_nlc(int b, int n, int c, int m, const float *grad_out,
+                                  const int *idx, const float *weight, float *grad_points,
+                                  void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* Replaces pccropandsamplegradfts_gpu(box_ind,crop_ind,grad_crop_fts,num_boxes,npts,resize,
+ * channel,grad_fts), cropping/tf_cropping_g.cu:161 (+ `batch`, which the reference takes from
+ * the fts tensor, tf_cropping.cpp:225).  box_ind (N), crop_ind (N,R), grad_crop_fts (N,R,C)
+ * -> grad_fts (batch,npts,C). */
+int hf_pc_crop_and_sample_grad_fts(const int *box_ind, const int *crop_ind,
+                                   const float *grad_crop_fts, int num_boxes, int batch, int npts,
+                                   int resize, int channel, float *grad_fts, void *workspace,
+                                   size_t workspace_bytes, hf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

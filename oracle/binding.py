@@ -175,6 +175,53 @@ def oriented_nms(boxes, thresh, return_info=False):
 
 
 # ---- oracle/_ref: the reference's own sources, compiled where they lie --------------
+
+# ---- gradients (serial = ascending entry order) ----------------------------------------
+def gather_point_grad(inp, idx, out_g):
+    idx, out_g = _c(idx, np.int32), _c(out_g, np.float32)
+    b, n, _ = inp.shape
+    m = idx.shape[1]
+    inp_g = np.zeros((b, n, 3), np.float32)
+    lib().hf_oracle_gather_point_grad(_i(b), _i(n), _i(m), _ptr(out_g), _ptr(idx), _ptr(inp_g))
+    return inp_g
+
+
+def group_point_grad(points, idx, grad_out):
+    idx, grad_out = _c(idx, np.int32), _c(grad_out, np.float32)
+    b, n, c = points.shape
+    m, ns = idx.shape[1], idx.shape[2]
+    g = np.zeros((b, n, c), np.float32)
+    lib().hf_oracle_group_point_grad(_i(b), _i(n), _i(c), _i(m), _i(ns), _ptr(grad_out), _ptr(idx), _ptr(g))
+    return g
+
+
+def three_interpolate_grad_channel_first(points, idx, weight, grad_out):
+    """points (b,c,m), idx / weight (b,n,3), grad_out (b,c,n) -> (b,c,m): the reference op's layout."""
+    idx, weight, grad_out = _c(idx, np.int32), _c(weight, np.float32), _c(grad_out, np.float32)
+    b, c, m = points.shape
+    n = idx.shape[1]
+    g = np.zeros((b, c, m), np.float32)
+    lib().hf_oracle_three_interpolate_grad(_i(b), _i(c), _i(n), _i(m), _ptr(grad_out), _ptr(idx), _ptr(weight), _ptr(g))
+    return g
+
+
+def three_interpolate_grad(points, idx, weight, grad_out):
+    """Channel-last form of the Python API: points (b,m,c), grad_out (b,n,c) -> (b,m,c)."""
+    g = three_interpolate_grad_channel_first(np.transpose(points, (0, 2, 1)), idx, weight,
+                                             np.transpose(grad_out, (0, 2, 1)))
+    return np.ascontiguousarray(np.transpose(g, (0, 2, 1)))
+
+
+def pc_crop_and_sample_grad_fts(fts, box_ind, crop_ind, grad_crop_fts):
+    box_ind, crop_ind, grad_crop_fts = _c(box_ind, np.int32), _c(crop_ind, np.int32), _c(grad_crop_fts, np.float32)
+    batch, npts, c = fts.shape
+    nb, r = crop_ind.shape
+    g = np.zeros((batch, npts, c), np.float32)
+    lib().hf_oracle_pc_crop_and_sample_grad_fts(_ptr(box_ind), _ptr(crop_ind), _ptr(grad_crop_fts), _i(nb), _i(batch),
+                                                _i(npts), _i(r), _i(c), _ptr(g))
+    return g
+
+
 def _mangled(so, name):
     out = subprocess.run(["nm", "-D", "--defined-only", so], check=True, stdout=subprocess.PIPE, text=True).stdout
     for line in out.splitlines():

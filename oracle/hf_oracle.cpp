@@ -615,4 +615,69 @@ int hf_oracle_oriented_nms(const float *boxes, int boxes_num, float thresh, int 
     return hf_oracle_nms_sweep(mask.data(), boxes_num, keep);
 }
 
+// ---------------------------------------------------------------------------
+// Gradients.  The reference kernels scatter with float
+// atomicAdd, so their summation order is whatever the hardware schedules; the oracle
+// runs the same loops SERIALLY (ascending entry order), which is also the order the
+// CUDA path guarantees.  The outputs are zeroed first, as the TF wrappers do
+// (tf_sampling.cpp:174, tf_interpolate.cpp:178).  Out-of-range indices are skipped.
+// ---------------------------------------------------------------------------
+// sampling/tf_sampling_g.cu:183-192  scatteraddpointKernel
+void hf_oracle_gather_point_grad(int b, int n, int m, const float *out_g, const int *idx, float *inp_g) {
+    std::memset(inp_g, 0, sizeof(float) * (size_t)b * n * 3);
+    for (int64_t i = 0; i < b; ++i)
+        for (int64_t j = 0; j < m; ++j) {
+            int a = idx[i * m + j];
+            if (a < 0 || a >= n) continue;
+            for (int l = 0; l < 3; ++l) inp_g[(i * n + a) * 3 + l] += out_g[(i * m + j) * 3 + l];
+        }
+}
+
+// grouping/tf_grouping_g.cu:61-78  group_point_grad_gpu
+void hf_oracle_group_point_grad(int b, int n, int c, int m, int nsample, const float *grad_out, const int *idx,
+                                float *grad_points) {
+    std::memset(grad_points, 0, sizeof(float) * (size_t)b * n * c);
+    for (int64_t i = 0; i < b; ++i)
+        for (int64_t j = 0; j < m; ++j)
+            for (int k = 0; k < nsample; ++k) {
+                int ii = idx[(i * m + j) * nsample + k];
+                if (ii < 0 || ii >= n) continue;
+                for (int l = 0; l < c; ++l)
+                    grad_points[(i * n + ii) * c + l] += grad_out[((i * m + j) * nsample + k) * c + l];
+            }
+}
+
+// interpolate/tf_interpolate_g.cu:133-155  three_interpolate_grad_kernel_fast, channel-first:
+// grad_out (b,c,n), idx / weight (b,n,3) -> grad_points (b,c,m); the product is rounded, then added.
+void hf_oracle_three_interpolate_grad(int b, int c, int n, int m, const float *grad_out, const int *idx,
+                                      const float *weight, float *grad_points) {
+    std::memset(grad_points, 0, sizeof(float) * (size_t)b * c * m);
+    for (int64_t i = 0; i < b; ++i)
+        for (int64_t ch = 0; ch < c; ++ch)
+            for (int64_t p = 0; p < n; ++p)
+                for (int k = 0; k < 3; ++k) {
+                    int d = idx[(i * n + p) * 3 + k];
+                    if (d < 0 || d >= m) continue;
+                    volatile float prod = grad_out[(i * c + ch) * n + p] * weight[(i * n + p) * 3 + k];
+                    grad_points[(i * c + ch) * m + d] += prod;
+                }
+}
+
+// cropping/tf_cropping_g.cu:134-150  pccropandsamplegradftsKernel
+void hf_oracle_pc_crop_and_sample_grad_fts(const int *box_ind, const int *crop_ind, const float *grad_crop_fts,
+                                           int num_boxes, int batch, int npts, int resize, int channel,
+                                           float *grad_fts) {
+    std::memset(grad_fts, 0, sizeof(float) * (size_t)batch * npts * channel);
+    for (int64_t bx = 0; bx < num_boxes; ++bx) {
+        int bch = box_ind[bx];
+        if (bch < 0 || bch >= batch) continue;
+        for (int64_t p = 0; p < resize; ++p) {
+            int id = crop_ind[bx * resize + p];
+            if (id < 0 || id >= npts) continue;
+            for (int ch = 0; ch < channel; ++ch)
+                grad_fts[((int64_t)bch * npts + id) * channel + ch] += grad_crop_fts[(bx * resize + p) * channel + ch];
+        }
+    }
+}
+
 }  // extern "C"

@@ -139,3 +139,44 @@ def nms_mask(boxes, thresh):
     _fn("oriented_nms_gpu")(_d(boxes), _d(mask), _i(n), _f(thresh))
     torch.cuda.synchronize()
     return mask
+
+
+# ---- gradients: the wrappers memset the output first (tf_sampling.cpp:174, tf_interpolate.cpp:178) ----
+def gather_point_grad(inp, idx, out_g):
+    b, n, _ = inp.shape
+    m = idx.shape[1]
+    inp_g = torch.zeros((b, n, 3), dtype=torch.float32, device=inp.device)
+    torch.cuda.synchronize()
+    _fn("scatteraddpointLauncher")(_i(b), _i(n), _i(m), _d(out_g), _d(idx), _d(inp_g))
+    torch.cuda.synchronize()
+    return inp_g
+
+
+def group_point_grad(points, idx, grad_out):
+    b, n, c = points.shape
+    m, ns = idx.shape[1], idx.shape[2]
+    g = torch.zeros((b, n, c), dtype=torch.float32, device=points.device)
+    torch.cuda.synchronize()
+    _fn("groupPointGradLauncher")(_i(b), _i(n), _i(c), _i(m), _i(ns), _d(grad_out), _d(idx), _d(g))
+    torch.cuda.synchronize()
+    return g
+
+
+def three_interpolate_grad_channel_first(points, idx, weight, grad_out):
+    b, c, m = points.shape
+    n = idx.shape[1]
+    g = torch.zeros((b, c, m), dtype=torch.float32, device=points.device)
+    torch.cuda.synchronize()
+    _fn("three_interpolate_grad_gpu")(_i(b), _i(c), _i(n), _i(m), _d(grad_out), _d(idx), _d(weight), _d(g))
+    torch.cuda.synchronize()
+    return g
+
+
+def pc_crop_and_sample_grad_fts(fts, box_ind, crop_ind, grad_crop_fts):
+    B, P, C = fts.shape
+    N, R = crop_ind.shape
+    g = torch.zeros((B, P, C), dtype=torch.float32, device=fts.device)
+    torch.cuda.synchronize()
+    _fn("pccropandsamplegradfts_gpu")(_d(box_ind), _d(crop_ind), _d(grad_crop_fts), _i(N), _i(P), _i(R), _i(C), _d(g))
+    torch.cuda.synchronize()
+    return g

@@ -45,6 +45,13 @@ def test_status_codes_without_a_gpu():
     assert lib.hf_oriented_nms(1, 1, 100, 0.5, 1, None, None, 0, None) == _lib.HF_ERR_WORKSPACE
     assert lib.hf_oriented_nms_workspace_bytes(16, 9000) >= 16 * 9000 * 141 * 8  # mask + box records + pair list
     assert lib.hf_farthest_point_sample(0, 8, 4, 1, None, 1, None) == _lib.HF_OK  # empty batch: no launch
+    # gradients: workspace is the caller's, sized by the query; a missing one is an error, not an allocation
+    assert lib.hf_scatter_workspace_bytes(16, 4096, 4096 * 32) >= 4 * (16 * 4096 * 32 + 2 * 16 * 4096)
+    assert lib.hf_group_point_grad(1, 8, 4, 2, 2, 1, 1, 1, None, 0, None) == _lib.HF_ERR_INVALID_ARG
+    assert b"workspace" in lib.hf_last_error()
+    assert lib.hf_group_point_grad(1, 8, 4, 2, 2, 1, 1, 1, 16, 16, None) == _lib.HF_ERR_WORKSPACE
+    assert lib.hf_three_interpolate_grad_nlc(1, 8, 0, 4, 1, 1, 1, 1, 16, 16, None) == _lib.HF_ERR_INVALID_ARG
+    assert lib.hf_gather_point_grad(0, 8, 4, 1, 1, 1, None, 0, None) == _lib.HF_OK
 
 
 def test_python_mirror_rejects_bad_arguments_and_cpu_tensors():

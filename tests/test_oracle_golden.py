@@ -183,3 +183,47 @@ def test_corner_order_matches_box_8c_encoder_fixture():
     assert c[2].tolist() == [5.5, 0.5, 0.5, 5.5, 5.5, 0.5, 0.5, 5.5]
     bev = synthetic.boxes3d_to_bev(np.array([[1, 2, 3, 4, 5, 6, 0.3]], np.float32))[0]
     assert np.allclose(bev, [-1, 0.5, 3, 5.5, 0.3])
+
+
+# ---------------------------------------------------------------- gradients
+def test_oracle_gradients_are_the_adjoints_of_the_forward_ops(oracle):
+    """<forward(x), g> == <x, grad(g)> in float64, and the serial sums match numpy's add.at."""
+    rng = np.random.default_rng(21)
+    b, n, c, m, ns = 2, 60, 5, 20, 4
+    pts = rng.standard_normal((b, n, c)).astype(np.float32)
+    idx = rng.integers(0, n, (b, m, ns)).astype(np.int32)
+    g = rng.standard_normal((b, m, ns, c)).astype(np.float32)
+    gp = oracle.group_point_grad(pts, idx, g)
+    assert np.isclose(np.vdot(oracle.group_point(pts, idx).astype(np.float64), g), np.vdot(pts.astype(np.float64), gp), rtol=1e-5)
+    ref = np.zeros((b, n, c))
+    for i in range(b):
+        np.add.at(ref[i], idx[i].reshape(-1), g[i].reshape(-1, c).astype(np.float64))
+    assert np.allclose(gp, ref, rtol=1e-5, atol=1e-5)
+
+    xyz = rng.standard_normal((b, n, 3)).astype(np.float32)
+    gi = rng.integers(0, n, (b, m)).astype(np.int32)
+    og = rng.standard_normal((b, m, 3)).astype(np.float32)
+    assert np.isclose(np.vdot(oracle.gather_point(xyz, gi).astype(np.float64), og),
+                      np.vdot(xyz.astype(np.float64), oracle.gather_point_grad(xyz, gi, og)), rtol=1e-5)
+
+    known = rng.standard_normal((b, m, c)).astype(np.float32)
+    i3 = rng.integers(0, m, (b, n, 3)).astype(np.int32)
+    w = rng.random((b, n, 3)).astype(np.float32)
+    go = rng.standard_normal((b, n, c)).astype(np.float32)
+    gk = oracle.three_interpolate_grad(known, i3, w, go)
+    assert np.isclose(np.vdot(oracle.three_interpolate(known, i3, w).astype(np.float64), go),
+                      np.vdot(known.astype(np.float64), gk), rtol=1e-4)
+
+    B, P, C, nb, R = 2, 40, 3, 5, 8
+    fts = rng.standard_normal((B, P, C)).astype(np.float32)
+    box_ind = rng.integers(0, B, nb).astype(np.int32)
+    crop_ind = rng.integers(0, P, (nb, R)).astype(np.int32)
+    gc = rng.standard_normal((nb, R, C)).astype(np.float32)
+    gf = oracle.pc_crop_and_sample_grad_fts(fts, box_ind, crop_ind, gc)
+    ref = np.zeros((B, P, C))
+    for k in range(nb):
+        np.add.at(ref[box_ind[k]], crop_ind[k], gc[k].astype(np.float64))
+    assert np.allclose(gf, ref, rtol=1e-5, atol=1e-5)
+    # out-of-range indices are skipped, not written
+    idx[0, 0, 0], idx[1, 3, 2] = -1, n
+    assert np.isfinite(oracle.group_point_grad(pts, idx, g)).all()
