@@ -31,6 +31,8 @@ import sys
 import threading
 import time
 
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")  # before the CUDA context exists (see heterofusionrcnn_b200/__init__.py)
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -59,6 +61,11 @@ def parse_args():
     ap.add_argument("--resident-inflight", type=int, default=1,
                     help="resident leg: batches kept in flight (measured: 2 is slower than 1 - the second batch's FPS "
                          "clusters cannot be gang-scheduled while the first batch's bulk kernels fill every SM)")
+    ap.add_argument("--graph", action="store_true",
+                    help="resident leg: replay one captured CUDA graph per step instead of issuing every launch from Python "
+                         "(measured equal within noise: the step is GPU bound, not launch bound)")
+    ap.add_argument("--timeline", action="store_true",
+                    help="print (stderr) when every op of the last timed step started and ended, relative to the step's start")
     ap.add_argument("--profile-range", action="store_true",
                     help="bracket the timed region with cudaProfilerStart/Stop (ncu --profile-from-start off)")
     ap.add_argument("--serial", action="store_true",
@@ -99,7 +106,8 @@ def config_dict(args, cfg, n_gpus):
         "points_per_scan": cfg.points,
         "sharding": "batch slices, one per GPU, no collective" if n_gpus > 1 else "single GPU",
         "issue": "one stream, program order" if args.serial else
-                 "independent branches of the chain on 5 CUDA streams, %d batch(es) in flight (e2e leg: %d)" % (
+                 "independent branches of the chain on 13 CUDA streams%s, %d batch(es) in flight (e2e leg: eager, %d)" % (
+                     ", one step = one replay of the captured CUDA graph" if (args.graph and not args.timeline) else "",
                      max(1, args.resident_inflight), max(1, args.inflight)),
         "l2": "no explicit flush: one step reads 0.45 GB and writes 5.6 GB per GPU, far beyond the 126 MB L2",
     }
@@ -364,6 +372,7 @@ def run_b200(args):
 
     # ---- resident-input throughput (value) + per-launch events (roofline) ----
     overlap = not args.serial
+    use_graph = overlap and args.graph and not args.timeline
     depth = max(1, args.resident_inflight) if overlap else 1
     probe = EventProbe(torch)
     probe.enabled = False
@@ -371,7 +380,12 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         pipe.submit(resident, probe)
     pipe.drain()
-    probe.enabled = True
+    torch.cuda.synchronize()
+    graph = chain.ChainGraph(resident, cfg) if use_graph else None
+    if graph is not None:
+        for _ in range(max(args.warmup, 3)):
+            graph.replay()
+        torch.cuda.synchronize()
     barrier()
     clocks = ClockSampler(local).start() if rank == 0 else None
     l0 = hf.launch_count()
@@ -380,19 +394,38 @@ def run_b200(args):
         torch.cuda.synchronize()
         torch.cuda.profiler.start()
     ev0.record()
-    for _ in range(args.steps):
-        pipe.submit(resident, probe)
-    pipe.drain()
+    if graph is not None:
+        for _ in range(args.steps):
+            graph.replay()  # one cudaGraphLaunch = the whole step: every lane, every libhfops kernel
+    else:
+        probe.enabled = True
+        for _ in range(args.steps):
+            pipe.submit(resident, probe)
+        pipe.drain()
     ev1.record()
     if args.profile_range:
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
     barrier()
-    launches = hf.launch_count() - l0
+    launches = (graph.launches * args.steps) if graph is not None else hf.launch_count() - l0
     ms = max_over_ranks(ev0.elapsed_time(ev1))
     launches = int(sum_over_ranks(launches))
+    if graph is not None:
+        # per-launch durations inside an overlapped step cannot be read out of a graph replay: measure them on
+        # eagerly issued steps (same streams, same kernels) right after the timed region
+        probe.enabled = True
+        for _ in range(args.steps):
+            pipe.submit(resident, probe)
+        pipe.drain()
+        torch.cuda.synchronize()
     ops = probe.summarise(args.steps)
     probe.enabled = False
+    if args.timeline and rank == 0:
+        per = len(probe.records) // max(args.steps, 1)
+        last = probe.records[-per:]
+        t0 = min(ev0.elapsed_time(r[3]) for r in last)
+        for key, _, _, s_, e_ in sorted(last, key=lambda r: ev0.elapsed_time(r[3])):
+            sys.stderr.write("timeline %-34s %8.3f -> %8.3f ms\n" % (key, ev0.elapsed_time(s_) - t0, ev0.elapsed_time(e_) - t0))
     # each launch timed ALONE (one stream, program order) — outside the timed region, for the per-kernel table
     alone = EventProbe(torch)
     for _ in range(2):  # untimed: the caching allocator has no blocks on this stream yet

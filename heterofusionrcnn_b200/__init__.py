@@ -10,6 +10,13 @@ tensors, calling hand-written CUDA through the C-ABI of include/hfops.h:
     from heterofusionrcnn_b200.cropping.tf_cropping import pc_crop_and_sample
     from heterofusionrcnn_b200.bev_iou.bev_iou import compute_bev_iou, oriented_nms
 """
+import os as _os
+
+# The chain spreads one pass over 13 CUDA streams; with the default 8 hardware queues several of
+# them alias and pick up false dependencies (a three_nn queued behind the NMS sweep).  Must be set
+# before the CUDA context exists, so it is done at import; an explicit setting wins.
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 from ._lib import HfOpsError, InvalidArgumentError, launch_count, load  # noqa: F401
 
 __version__ = "0.1.0"

@@ -22,7 +22,7 @@ from . import spatial, synthetic
 from .bev_iou.bev_iou import oriented_nms_batch
 from .cropping.tf_cropping import pc_crop_and_sample
 from .grouping.tf_grouping import group_point, query_ball_point
-from .interpolate.tf_interpolate import three_interpolate, three_nn
+from .interpolate.tf_interpolate import three_interpolate, three_nn_weights
 from .sampling.tf_sampling import farthest_point_sample, gather_point
 
 
@@ -136,23 +136,30 @@ class _Lanes:
     and latency bound (one cluster per scan); everything else only depends on one of its
     intermediate results or on nothing at all.  Issuing those on side streams lets their CTAs
     fill the SM resources the sampling CTAs leave idle:
-        crit   fps / gather_point of every level                      (high priority)
-        group  [cloud index of level l+1] query_ball_point + group_point x2 of level l  (after gather_l)
-        fp     three_nn of every level as soon as its two clouds exist, then the
-               three_interpolate calls coarse -> fine (the order the real network needs)
-        crop   pc_crop_and_sample                                      (independent)
-        nms    oriented_nms                                            (independent)
+        crit      fps / gather_point of every level                     (highest priority, issued first)
+        group[l]  [cloud index of level l+1] query_ball_point + group_point x2 of level l (after gather_l)
+        nn[l]     three_nn (+ interpolation weights) of level l as soon as its two clouds exist
+        fp        the three_interpolate calls coarse -> fine (the order the real network needs)
+        crop      pc_crop_and_sample                                      (independent)
+        nms       oriented_nms                                            (independent)
+    One stream per level: level l+1's ball query must not queue behind level l's group_point.
+    Priorities (measured, profiles/r1_chain_schedule.md): sampling > grouping / three_nn /
+    interpolation > NMS > crop — the crop's 8192 CTAs would otherwise starve the small kernels
+    behind the sampling chain; HF_CHAIN_PRIORITIES="crit,group,nn,crop,nms" overrides.
     """
 
     _cache = {}
 
     def __init__(self, device):
-        lo, hi = -1, 0
-        self.crit = torch.cuda.Stream(device=device, priority=lo)
-        self.group = torch.cuda.Stream(device=device, priority=hi)
-        self.fp = torch.cuda.Stream(device=device, priority=hi)
-        self.crop = torch.cuda.Stream(device=device, priority=hi)
-        self.nms = torch.cuda.Stream(device=device, priority=hi)
+        import os
+        pr = [int(v) for v in os.environ.get("HF_CHAIN_PRIORITIES", "-3,-2,-2,0,-1").split(",")]
+        mk = lambda p: torch.cuda.Stream(device=device, priority=p)  # noqa: E731
+        self.crit = mk(pr[0])
+        self.group = [mk(pr[1]) for _ in range(4)]
+        self.nn = [mk(pr[2]) for _ in range(4)]
+        self.fp = mk(pr[2])
+        self.crop = mk(pr[3])
+        self.nms = mk(pr[4])
 
     @classmethod
     def get(cls, device, slot=0):
@@ -162,13 +169,7 @@ class _Lanes:
         return cls._cache[key]
 
     def all(self):
-        return (self.crit, self.group, self.fp, self.crop, self.nms)
-
-
-def _fp_weights(dist):
-    dist = torch.clamp_min(dist, 1e-10)  # pointnet_util.py:304-307
-    inv = 1.0 / dist
-    return dist, inv / inv.sum(dim=2, keepdim=True)
+        return [self.crit] + self.group + self.nn + [self.fp, self.crop, self.nms]
 
 
 def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
@@ -193,17 +194,18 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
     main = torch.cuda.current_stream(device)
     if overlap:
         lanes = _Lanes.get(device, slot)
-        crit, s_group, s_fp, s_crop, s_nms = lanes.all()
+        crit, s_group, s_nn, s_fp, s_crop, s_nms = lanes.crit, lanes.group, lanes.nn, lanes.fp, lanes.crop, lanes.nms
         start = torch.cuda.Event()
         start.record(main)
         for s in lanes.all():
             s.wait_event(start)
     else:
-        crit = s_group = s_fp = s_crop = s_nms = main
+        crit = s_fp = s_crop = s_nms = main
+        s_group = s_nn = [main] * 4
     on = torch.cuda.stream
 
     def after(stream, event):
-        if overlap:
+        if overlap and event is not None:
             stream.wait_event(event)
 
     def mark(stream):
@@ -218,7 +220,35 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
     fps_idx = []
     feats = [dev["intensity"]] + list(dev["sa_feats"][1:])
     b = dev["xyz"].shape[0]
-    # independent branches first, so their CTAs are queued behind the sampling chain from the start
+    n_lv = [cfg.points] + list(cfg.npoint)
+    ns = cfg.nsample
+
+    def sample_level(l):
+        n, m = n_lv[l], n_lv[l + 1]
+        with on(crit):
+            with probe("fps", level=l + 1, b=b, n=n, m=m):
+                idx = farthest_point_sample(m, xyz[l])
+            with probe("gather_point", level=l + 1, b=b, n=n, m=m):
+                new_xyz = gather_point(xyz[l], idx)
+        fps_idx.append(idx)
+        xyz.append(new_xyz)
+        return mark(crit)
+
+    # The sampling chain is the spine of the step: its first (longest) launch goes out before anything else,
+    # so its clusters take their SMs while the GPU is still empty.  In program order (overlap=False) the
+    # independent branches keep the reference's order instead.
+    have_xyz = [None] * 4
+    if overlap:
+        have_xyz[0] = sample_level(0)
+    # spatial index of each level's cloud, built once and shared by ball query and three_nn of the
+    # two levels that search it (only where the calls are large enough to take the pruned kernels).
+    # The input's index needs whole SMs (1024-thread CTAs): it goes out before the crop floods the GPU.
+    use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
+    index, index_ready = [None] * 5, [None] * 5
+    if use_ix[0]:
+        with on(s_group[0]), probe("cloud_index", level=0, b=b, n=n_lv[0]):
+            index[0] = spatial.build_cloud_index(xyz[0])  # needs only the input: overlaps FPS level 1
+        index_ready[0] = mark(s_group[0])
     if cfg.with_nms:
         with on(s_nms), probe("oriented_nms", b=b, nb=cfg.nms_boxes):
             keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
@@ -231,61 +261,52 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                                              dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
     # ---- set abstraction ----
     nn = [None] * 4
-    # spatial index of each level's cloud, built once and shared by ball query and three_nn of the
-    # two levels that search it (only where the calls are large enough to take the pruned kernels)
-    n_lv = [cfg.points] + list(cfg.npoint)
-    use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
-    index, index_ready = [None] * 5, [None] * 5
-    if use_ix[0]:
-        with on(s_group), probe("cloud_index", level=0, b=b, n=n_lv[0]):
-            index[0] = spatial.build_cloud_index(xyz[0])  # needs only the input: overlaps FPS level 1
-        index_ready[0] = mark(s_group)
+    nn_ready = [None] * 4
     for l in range(4):
-        n, m, ns = xyz[l].shape[1], cfg.npoint[l], cfg.nsample
-        with on(crit):
-            with probe("fps", level=l + 1, b=b, n=n, m=m):
-                idx = farthest_point_sample(m, xyz[l])
-            with probe("gather_point", level=l + 1, b=b, n=n, m=m):
-                new_xyz = gather_point(xyz[l], idx)
-        have_xyz = mark(crit)
-        after(s_group, have_xyz)
-        with on(s_group):
+        n, m = n_lv[l], n_lv[l + 1]
+        if have_xyz[l] is None:
+            have_xyz[l] = sample_level(l)
+        new_xyz = xyz[l + 1]
+        sg = s_group[l]
+        after(sg, have_xyz[l])
+        with on(sg):
             if use_ix[l] or (l + 1 < 4 and use_ix[l + 1]):
                 with probe("cloud_index", level=l + 1, b=b, n=m):
                     index[l + 1] = spatial.build_cloud_index(new_xyz)
-                index_ready[l + 1] = mark(s_group)
+                index_ready[l + 1] = mark(sg)
             ix = (index[l], index[l + 1]) if use_ix[l] else (None, None)
+            if use_ix[l]:
+                after(sg, index_ready[l])
             with probe("query_ball_point", level=l + 1, b=b, n=n, m=m, ns=ns):
                 gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz, index1=ix[0], index2=ix[1])
             with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
                 gxyz = group_point(xyz[l], gidx)
             with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
                 gfeat = group_point(feats[l], gidx)
-        # three_nn of FP level l+1 (unknown = level l cloud, known = level l+1 cloud) is geometry only
-        after(s_fp, have_xyz)
+        # three_nn of FP level l+1 (unknown = level l cloud, known = level l+1 cloud) is geometry only;
+        # the interpolation weights (pointnet_util.py:304-307) come out of the same kernel
+        sn = s_nn[l]
+        after(sn, have_xyz[l])
         if use_ix[l]:
-            after(s_fp, index_ready[l])
-            after(s_fp, index_ready[l + 1])
-        with on(s_fp):
+            after(sn, index_ready[l])
+            after(sn, index_ready[l + 1])
+        with on(sn):
             with probe("three_nn", level=l + 1, b=b, n=n, m=m):
-                dist, nidx = three_nn(xyz[l], new_xyz, index1=ix[0], index2=ix[1])
-            with probe("fp_weights_torch", level=l + 1, b=b, n=n):
-                dist, w = _fp_weights(dist)
-        nn[l] = (dist, nidx, w)
-        fps_idx.append(idx)
-        xyz.append(new_xyz)
+                nn[l] = three_nn_weights(xyz[l], new_xyz, index1=ix[0], index2=ix[1])
+        nn_ready[l] = mark(sn)
         res["sa%d" % (l + 1)] = (gidx, cnt, gxyz, gfeat)
     res["fps_idx"] = fps_idx
     res["xyz_levels"] = xyz
+    res["_keep"] = index  # referenced until the pass is over: other streams read them
     # ---- feature propagation, coarse to fine (pointnet_util.py:289-330) ----
-    with on(s_fp):
-        for j in range(4):
-            lvl = 3 - j  # unknown cloud = xyz[lvl], known = xyz[lvl + 1]
-            dist, nidx, w = nn[lvl]
-            n, m, c = xyz[lvl].shape[1], xyz[lvl + 1].shape[1], dev["fp_feats"][j].shape[2]
-            with probe("three_interpolate", level=lvl + 1, b=b, n=n, m=m, c=c):
-                out = three_interpolate(dev["fp_feats"][j], nidx, w)
-            res["fp%d" % (lvl + 1)] = (dist, nidx, out)
+    for j in range(4):
+        lvl = 3 - j  # unknown cloud = xyz[lvl], known = xyz[lvl + 1]
+        dist, nidx, w = nn[lvl]
+        n, m, c = n_lv[lvl], n_lv[lvl + 1], dev["fp_feats"][j].shape[2]
+        after(s_fp, nn_ready[lvl])
+        with on(s_fp), probe("three_interpolate", level=lvl + 1, b=b, n=n, m=m, c=c):
+            out = three_interpolate(dev["fp_feats"][j], nidx, w)
+        res["fp%d" % (lvl + 1)] = (dist, nidx, out)
     if overlap:
         done = [mark(s) for s in lanes.all()]
         if join:
@@ -329,6 +350,40 @@ class ChainPipeline:
             if item is not None:
                 for e in item[1]["_done"]:
                     main.wait_event(e)
+
+
+class ChainGraph:
+    """One chain pass over fixed device buffers, captured into a CUDA graph and replayed.
+
+    The step is ~40 launches of 10-100 us kernels on 13 streams; issued from Python the host needs
+    about as long to enqueue them as the GPU needs to run them, and every dependent launch adds
+    its latency to the tail behind the level-1 FPS.  Captured once (all lanes fork from and join
+    the capture stream), a step is one cudaGraphLaunch.  Inputs are read from `dev` and results
+    are written to the same tensors on every replay: copy new inputs into `dev` (stream ordered)
+    before replay() and consume `res` before the next one.
+    """
+
+    def __init__(self, dev, cfg, slot=0):
+        from . import _lib
+
+        self.dev, self.cfg = dev, cfg
+        device = dev["xyz"].device
+        side = torch.cuda.Stream(device=device)
+        side.wait_stream(torch.cuda.current_stream(device))
+        with torch.cuda.stream(side):  # eager passes first: one-time attribute calls, allocator pools
+            for _ in range(2):
+                run_chain(dev, cfg, slot=slot)
+        torch.cuda.current_stream(device).wait_stream(side)
+        torch.cuda.synchronize(device)
+        self.graph = torch.cuda.CUDAGraph()
+        before = _lib.launch_count()
+        with torch.cuda.graph(self.graph):
+            self.res = run_chain(dev, cfg, slot=slot)
+        self.launches = _lib.launch_count() - before  # libhfops kernels per replay
+
+    def replay(self):
+        self.graph.replay()
+        return self.res
 
 
 def chain_launches(cfg):

@@ -66,6 +66,17 @@ __device__ __forceinline__ float sqdist(float dx, float dy, float dz) {
     return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
 }
 
+// Inverse-distance weights of the three nearest neighbours (hf/core/feature_extractors/
+// pointnet_util.py:304-307): d = max(d, 1e-10); w_k = (1/d_k) / sum_k (1/d_k).
+__device__ __forceinline__ void fp_weights3(float d1, float d2, float d3, float *w) {
+    const float i1 = __fdiv_rn(1.f, fmaxf(d1, 1e-10f)), i2 = __fdiv_rn(1.f, fmaxf(d2, 1e-10f)),
+                i3 = __fdiv_rn(1.f, fmaxf(d3, 1e-10f));
+    const float norm = __fadd_rn(__fadd_rn(i1, i2), i3);
+    w[0] = __fdiv_rn(i1, norm);
+    w[1] = __fdiv_rn(i2, norm);
+    w[2] = __fdiv_rn(i3, norm);
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
     return (uint32_t)__cvta_generic_to_shared(p);
 }

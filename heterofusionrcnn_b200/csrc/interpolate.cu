@@ -24,7 +24,7 @@ constexpr int kNnTile = 1024;
 
 __global__ void __launch_bounds__(kNnThreads)
     three_nn_kernel(int n, int m, const float *__restrict__ unknown, const float *__restrict__ known,
-                    float *__restrict__ dist2, int *__restrict__ idx) {
+                    float *__restrict__ dist2, int *__restrict__ idx, float *__restrict__ weight) {
     __shared__ __align__(16) float stage0[kNnTile * 3];
     __shared__ __align__(16) float stage1[kNnTile * 3];
     __shared__ __align__(8) uint64_t bars[2];
@@ -84,6 +84,7 @@ __global__ void __launch_bounds__(kNnThreads)
         int *ii = idx + ((size_t)scene * n + j) * 3;
         dd[0] = best1; dd[1] = best2; dd[2] = best3;
         ii[0] = besti1; ii[1] = besti2; ii[2] = besti3;
+        if (weight) fp_weights3(best1, best2, best3, weight + ((size_t)scene * n + j) * 3);
     }
 }
 
@@ -180,18 +181,24 @@ __global__ void __launch_bounds__(256)
 }  // namespace
 }  // namespace hf
 
-extern "C" int hf_three_nn(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
-                           hf_stream_t stream) {
-    using namespace hf;
+namespace hf {
+int three_nn_every_pair(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                        float *weight, cudaStream_t s) {
     HF_REQUIRE(b >= 0 && n >= 0, "ThreeNN expects (b,n,3) xyz1 shape.");
     HF_REQUIRE(m >= 0, "ThreeNN expects (b,m,3) xyz2 shape.");
     HF_REQUIRE(unknown && known && dist2 && idx, "ThreeNN: null pointer");
     HF_REQUIRE(b <= 65535, "ThreeNN: batch_size > 65535 not supported");
     if (b == 0 || n == 0) return HF_OK;
     dim3 grid((n + kNnThreads - 1) / kNnThreads, b);
-    three_nn_kernel<<<grid, kNnThreads, 0, (cudaStream_t)stream>>>(n, m, unknown, known, dist2, idx);
+    three_nn_kernel<<<grid, kNnThreads, 0, s>>>(n, m, unknown, known, dist2, idx, weight);
     HF_LAUNCH_OK("three_nn_kernel");
     return HF_OK;
+}
+}  // namespace hf
+
+extern "C" int hf_three_nn(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                           hf_stream_t stream) {
+    return hf::three_nn_every_pair(b, n, m, unknown, known, dist2, idx, nullptr, (cudaStream_t)stream);
 }
 
 extern "C" int hf_three_interpolate_nlc(int b, int m, int c, int n, const float *points, const int *idx,

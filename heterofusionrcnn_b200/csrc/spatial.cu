@@ -30,6 +30,8 @@
 
 namespace hf {
 float ball_threshold(float radius);  // grouping.cu
+int three_nn_every_pair(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                        float *weight, cudaStream_t s);  // interpolate.cu
 
 namespace {
 
@@ -453,7 +455,8 @@ __global__ void __launch_bounds__(kSqWarps * 32)
 __global__ void __launch_bounds__(kSqWarps * 32)
     three_nn_indexed_kernel(int n, int nbq, int nbc, const float4 *__restrict__ sortedQ,
                             const float4 *__restrict__ boxesQ, const float4 *__restrict__ sortedC,
-                            const float4 *__restrict__ boxesC, float *__restrict__ dist2, int *__restrict__ idx) {
+                            const float4 *__restrict__ boxesC, float *__restrict__ dist2, int *__restrict__ idx,
+                            float *__restrict__ weight) {
     __shared__ __align__(16) float4 tiles[kSqWarps * 32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int scene = blockIdx.y;
@@ -534,6 +537,7 @@ __global__ void __launch_bounds__(kSqWarps * 32)
         int *ii = idx + ((size_t)scene * n + qi) * 3;
         dd[0] = b1; dd[1] = b2; dd[2] = b3;
         ii[0] = i1; ii[1] = i2; ii[2] = i3;
+        if (weight) fp_weights3(b1, b2, b3, weight + ((size_t)scene * n + qi) * 3);
     }
 }
 
@@ -583,10 +587,11 @@ int launch_ball_query(int b, int m, float radius, int nsample, const CloudDesc &
     return HF_OK;
 }
 
-int launch_three_nn(int b, int n, const CloudDesc &q, const CloudDesc &c, float *dist2, int *idx, cudaStream_t s) {
+int launch_three_nn(int b, int n, const CloudDesc &q, const CloudDesc &c, float *dist2, int *idx, float *weight,
+                    cudaStream_t s) {
     const int nbq = q.npad / 32, nbc = c.npad / 32;
     three_nn_indexed_kernel<<<dim3((nbq + kSqWarps - 1) / kSqWarps, b), kSqWarps * 32, 0, s>>>(
-        n, nbq, nbc, q.sorted, q.boxes, c.sorted, c.boxes, dist2, idx);
+        n, nbq, nbc, q.sorted, q.boxes, c.sorted, c.boxes, dist2, idx, weight);
     HF_LAUNCH_OK("three_nn_indexed_kernel");
     return HF_OK;
 }
@@ -643,7 +648,8 @@ extern "C" int hf_three_nn_indexed(int b, int n, int m, const float *unknown, co
         return hf_three_nn(b, n, m, unknown, known, dist2, idx, stream);
     HF_REQUIRE(unknown && known && dist2 && idx, "ThreeNN: null pointer");
     return launch_three_nn(b, n, carve_index(b, n, unknown, const_cast<void *>(index_unknown)),
-                           carve_index(b, m, known, const_cast<void *>(index_known)), dist2, idx, (cudaStream_t)stream);
+                           carve_index(b, m, known, const_cast<void *>(index_known)), dist2, idx, nullptr,
+                           (cudaStream_t)stream);
 }
 
 extern "C" int hf_query_ball_point_ws(int b, int n, int m, float radius, int nsample, const float *xyz1,
@@ -674,5 +680,19 @@ extern "C" int hf_three_nn_ws(int b, int n, int m, const float *unknown, const f
     const CloudDesc c = carve_index(b, m, known, static_cast<unsigned char *>(workspace) + cloud_bytes(b, n));
     int rc = launch_index(b, q, &c, s);
     if (rc != HF_OK) return rc;
-    return launch_three_nn(b, n, q, c, dist2, idx, s);
+    return launch_three_nn(b, n, q, c, dist2, idx, nullptr, s);
+}
+
+extern "C" int hf_three_nn_weights(int b, int n, int m, const float *unknown, const float *known, float *dist2, int *idx,
+                                   float *weight, const void *index_unknown, const void *index_known,
+                                   hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(weight, "ThreeNN: null weight pointer");
+    if (!index_unknown || !index_known || b <= 0 || n <= 0 || m <= 0 || b > 65535 || !spatial_applies(n, m) ||
+        !aligned16(index_unknown) || !aligned16(index_known))
+        return three_nn_every_pair(b, n, m, unknown, known, dist2, idx, weight, (cudaStream_t)stream);
+    HF_REQUIRE(unknown && known && dist2 && idx, "ThreeNN: null pointer");
+    return launch_three_nn(b, n, carve_index(b, n, unknown, const_cast<void *>(index_unknown)),
+                           carve_index(b, m, known, const_cast<void *>(index_known)), dist2, idx, weight,
+                           (cudaStream_t)stream);
 }

@@ -47,6 +47,32 @@ def three_nn(xyz1, xyz2, index1=None, index2=None):
     return dist, idx
 
 
+def three_nn_weights(xyz1, xyz2, index1=None, index2=None):
+    """three_nn fused with the interpolation weights its caller computes from it
+    (hf/core/feature_extractors/pointnet_util.py:303-308):
+
+        dist, idx = three_nn(xyz1, xyz2); dist = max(dist, 1e-10)
+        weight = (1/dist) / sum(1/dist, axis=2)
+
+    Returns (dist (b,n,3) raw squared distances, idx (b,n,3) int32, weight (b,n,3)).
+    """
+    xyz1 = dev_tensor(xyz1, torch.float32, "xyz1")
+    xyz2 = dev_tensor(xyz2, torch.float32, "xyz2")
+    require(xyz1.dim() == 3 and xyz1.shape[2] == 3, "ThreeNN expects (b,n,3) xyz1 shape.")
+    require(xyz2.dim() == 3 and xyz2.shape[2] == 3 and xyz2.shape[0] == xyz1.shape[0], "ThreeNN expects (b,m,3) xyz2 shape.")
+    b, n = xyz1.shape[0], xyz1.shape[1]
+    m = xyz2.shape[1]
+    out = torch.empty((3, b, n, 3), dtype=torch.float32, device=xyz1.device)  # dist | idx bits | weight: one allocation
+    dist, idx, weight = out[0], out[1].view(torch.int32), out[2]
+    p1 = index1.ptr_for(xyz1) if index1 is not None else None
+    p2 = index2.ptr_for(xyz2) if index2 is not None else None
+    with torch.cuda.device(xyz1.device):
+        rc = _lib.load().hf_three_nn_weights(b, n, m, xyz1.data_ptr(), xyz2.data_ptr(), dist.data_ptr(), idx.data_ptr(),
+                                             weight.data_ptr(), p1, p2, stream_ptr(xyz1.device))
+    _lib.check(rc, "three_nn")
+    return dist, idx, weight
+
+
 def three_interpolate(points, idx, weight):
     """
     Input:

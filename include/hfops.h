@@ -108,6 +108,13 @@ int hf_query_ball_point_indexed(int b, int n, int m, float radius, int nsample, 
 int hf_three_nn_indexed(int b, int n, int m, const float *unknown, const float *known,
                         float *dist2, int *idx, const void *index_unknown,
                         const void *index_known, hf_stream_t stream);
+/* three_nn fused with the inverse-distance weights its only caller computes next
+ * (hf/core/feature_extractors/pointnet_util.py:303-308: d = max(d, 1e-10), w = (1/d) / sum(1/d)):
+ * also writes weight (b,n,3).  dist2 is the raw squared distance as in hf_three_nn.  Both indices
+ * may be NULL (every-pair kernel). */
+int hf_three_nn_weights(int b, int n, int m, const float *unknown, const float *known,
+                        float *dist2, int *idx, float *weight, const void *index_unknown,
+                        const void *index_known, hf_stream_t stream);
 
 /* Replaces groupPointLauncher(b,n,c,m,nsample,points,idx,out), grouping/tf_grouping_g.cu:133.
  * points (b,n,c), idx (b,m,nsample) -> out (b,m,nsample,c). */

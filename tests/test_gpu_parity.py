@@ -521,3 +521,25 @@ def test_chain_on_streams_equals_chain_in_program_order(cuda):
         assert len(a) == len(b)
         for (ka, ta), (kb, tb) in zip(a, b):
             assert ka == kb and torch.equal(ta, tb), ka
+
+
+# ---------------------------------------------------------------- three_nn fused with the FP weights
+@pytest.mark.parametrize("b,n,m,indexed", [(2, 16384, 4096, True), (2, 16384, 4096, False), (3, 1024, 256, False),
+                                           (2, 300, 2, False), (1, 64, 3, False)])
+def test_three_nn_weights_matches_three_nn_plus_reference_formula(cuda, oracle, b, n, m, indexed):
+    """Same dist / idx as three_nn (bit-exact); weights = pointnet_util.py:304-307 within 1e-5 relative."""
+    from heterofusionrcnn_b200 import spatial
+    from heterofusionrcnn_b200.interpolate.tf_interpolate import three_nn_weights
+
+    xyz1, _ = synthetic.make_scans(31 + n, b, n, duplicate_pad=n // 8)  # duplicates: zero distances hit the 1e-10 clamp
+    x1 = T(xyz1, cuda)
+    x2 = gather_point(x1, farthest_point_sample(m, x1))
+    ix = (spatial.build_cloud_index(x1), spatial.build_cloud_index(x2)) if indexed else (None, None)
+    d0, i0 = three_nn(x1, x2)
+    d, i, w = three_nn_weights(x1, x2, index1=ix[0], index2=ix[1])
+    assert torch.equal(d, d0) and torch.equal(i, i0)
+    wd, wi = oracle.three_nn(xyz1, N(x2))
+    assert np.array_equal(N(i), wi) and np.array_equal(N(d), wd)
+    want = synthetic.fp_weights(wd)
+    assert close(N(w), want)
+    assert np.allclose(N(w).sum(axis=2), 1.0, atol=1e-6)
