@@ -101,3 +101,65 @@ def group_point_grad(points, idx, grad_out):
                                      ws.data_ptr(), ws_bytes, stream_ptr(points.device))
     _lib.check(rc, "group_point_grad")
     return grad_points
+
+
+def select_top_k(k, dist):
+    """
+    Input:
+        k: int32, number of k SMALLEST elements selected
+        dist: (b,m,n) float32 array, distance matrix, m query points, n dataset points
+    Output:
+        idx: (b,m,n) int32 array, first k in n are indices to the top k
+        dist_out: (b,m,n) float32 array, first k in n are the top k
+
+    Reference: grouping/tf_grouping.py:29-39 (SelectionSort op, grouping/tf_grouping.cpp:108-141);
+    the whole output, tail included, equals the reference kernel's (tf_grouping_g.cu:83-123).
+    """
+    require(isinstance(k, int) and k > 0, "SelectionSort expects positive k")
+    dist = dev_tensor(dist, torch.float32, "dist")
+    require(dist.dim() == 3, "SelectionSort expects (b,m,n) dist shape.")
+    b, m, n = dist.shape
+    require(n >= 1, "SelectionSort expects (b,m,n) dist shape.")
+    idx = torch.empty((b, m, n), dtype=torch.int32, device=dist.device)
+    dist_out = torch.empty((b, m, n), dtype=torch.float32, device=dist.device)
+    with torch.cuda.device(dist.device):
+        rc = _lib.load().hf_select_top_k(b, n, m, k, dist.data_ptr(), idx.data_ptr(), dist_out.data_ptr(),
+                                         stream_ptr(dist.device))
+    _lib.check(rc, "select_top_k")
+    return idx, dist_out
+
+
+def knn_point(k, xyz1, xyz2):
+    """
+    Input:
+        k: int32, number of k in k-nn search
+        xyz1: (batch_size, ndataset, c) float32 array, input points
+        xyz2: (batch_size, npoint, c) float32 array, query points
+    Output:
+        val: (batch_size, npoint, k) float32 array, L2 distances
+        idx: (batch_size, npoint, k) int32 array, indices to input points
+
+    Reference: grouping/tf_grouping.py:62-95.  As there, val holds SQUARED distances, ascending, and
+    equal distances keep the lower index first (tf.nn.top_k).  c must be 3.  The (b,m,n) distance
+    matrix of the reference is never formed, and val is the directly computed squared distance rather
+    than r2 - 2*x2.x1 + r1 (which carries a cancellation error of ~1e-7 * |x|^2).
+    """
+    require(isinstance(k, int) and k > 0, "KnnPoint expects positive k")
+    xyz1 = dev_tensor(xyz1, torch.float32, "xyz1")
+    xyz2 = dev_tensor(xyz2, torch.float32, "xyz2")
+    require(xyz1.dim() == 3 and xyz1.shape[2] == 3, "KnnPoint expects (batch_size, ndataset, 3) xyz1 shape")
+    require(xyz2.dim() == 3 and xyz2.shape[2] == 3 and xyz2.shape[0] == xyz1.shape[0],
+            "KnnPoint expects (batch_size, npoint, 3) xyz2 shape")
+    b, n = xyz1.shape[0], xyz1.shape[1]
+    m = xyz2.shape[1]
+    require(k <= n, "KnnPoint: input must have at least k columns")
+    val = torch.empty((b, m, k), dtype=torch.float32, device=xyz1.device)
+    idx = torch.empty((b, m, k), dtype=torch.int32, device=xyz1.device)
+    lib = _lib.load()
+    ws_bytes = int(lib.hf_knn_workspace_bytes(b, n, m))
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=xyz1.device) if ws_bytes else None
+    with torch.cuda.device(xyz1.device):
+        rc = lib.hf_knn_point(b, n, m, k, xyz1.data_ptr(), xyz2.data_ptr(), val.data_ptr(), idx.data_ptr(),
+                              ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
+    _lib.check(rc, "knn_point")
+    return val, idx

@@ -229,6 +229,25 @@ int hf_pc_crop_and_sample_grad_fts(const int *box_ind, const int *crop_ind,
                                    int resize, int channel, float *grad_fts, void *workspace,
                                    size_t workspace_bytes, hf_stream_t stream);
 
+/* ---- KNN grouping --------------------------- */
+/* knn_point (grouping/tf_grouping.py:62-95): the k nearest points of xyz1 (b,n,3) for every query
+ * of xyz2 (b,m,3) -> val (b,m,k) squared distances ascending, idx (b,m,k); ties go to the lower
+ * index (tf.nn.top_k's rule).  The reference builds the whole (b,m,n) matrix as r2 - 2*x2.x1^T + r1
+ * with a TF matmul and runs top_k on the CPU; here distance and selection are fused and the matrix
+ * never exists.  val is the directly computed squared distance (the expanded form's cancellation
+ * error, ~1e-7 * |x|^2, is not reproduced).  Requires 1 <= k <= min(n, 128).  workspace =
+ * hf_knn_workspace_bytes(b, n, m) bytes (0 = the call is too small to profit from sorting) or NULL
+ * (then every pair is tested). */
+size_t hf_knn_workspace_bytes(int b, int n, int m);
+int hf_knn_point(int b, int n, int m, int k, const float *xyz1, const float *xyz2, float *val,
+                 int *idx, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* Replaces selectionSortLauncher(b,n,m,k,dist,outi,out), grouping/tf_grouping_g.cu:129: k steps of
+ * selection sort on every row of dist (b,m,n) -> outi (b,m,n) int32, out (b,m,n); the first k
+ * entries are the k smallest in order, the tail is the permutation the swaps leave (bit-exact,
+ * tail included).  Rows of up to 25600 elements. */
+int hf_select_top_k(int b, int n, int m, int k, const float *dist, int *outi, float *out,
+                    hf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -222,6 +222,27 @@ def pc_crop_and_sample_grad_fts(fts, box_ind, crop_ind, grad_crop_fts):
     return g
 
 
+
+# ---- KNN grouping -------------------------------------------------------------------------
+def select_top_k(k, dist):
+    dist = _c(dist, np.float32)
+    b, m, n = dist.shape
+    outi = np.zeros((b, m, n), np.int32)
+    out = np.zeros((b, m, n), np.float32)
+    lib().hf_oracle_select_top_k(_i(b), _i(n), _i(m), _i(int(k)), _ptr(dist), _ptr(outi), _ptr(out))
+    return outi, out
+
+
+def knn_point(k, xyz1, xyz2):
+    xyz1, xyz2 = _c(xyz1, np.float32), _c(xyz2, np.float32)
+    b, n, _ = xyz1.shape
+    m = xyz2.shape[1]
+    val = np.zeros((b, m, k), np.float32)
+    idx = np.zeros((b, m, k), np.int32)
+    lib().hf_oracle_knn_point(_i(b), _i(n), _i(m), _i(int(k)), _ptr(xyz1), _ptr(xyz2), _ptr(val), _ptr(idx))
+    return val, idx
+
+
 def _mangled(so, name):
     out = subprocess.run(["nm", "-D", "--defined-only", so], check=True, stdout=subprocess.PIPE, text=True).stdout
     for line in out.splitlines():
@@ -278,6 +299,20 @@ def ref_group_point_cpu(points, idx):
     out = np.zeros((b, m, ns, c), np.float32)
     fn(_i(b), _i(n), _i(c), _i(m), _i(ns), _ptr(points), _ptr(idx), _ptr(out))
     return out
+
+
+
+def ref_selection_sort_cpu(k, dist):
+    """grouping/test/selection_sort.cpp:19-63 (the reference's own CPU prototype; it prints every row
+    it sorts, so keep the inputs small)."""
+    so = os.path.join(REF_DIR, "libref_selection_sort_cpu.so")
+    fn = getattr(_ref("libref_selection_sort_cpu.so"), _mangled(so, "selection_sort_cpu"))
+    dist = _c(dist, np.float32)
+    b, m, n = dist.shape
+    idx = np.zeros((b, m, n), np.int32)
+    val = np.zeros((b, m, n), np.float32)
+    fn(_i(b), _i(n), _i(m), _i(int(k)), _ptr(dist), _ptr(idx), _ptr(val))
+    return idx, val
 
 
 def ref_bev_host(boxes_a, boxes_b):

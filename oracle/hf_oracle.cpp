@@ -680,4 +680,50 @@ void hf_oracle_pc_crop_and_sample_grad_fts(const int *box_ind, const int *crop_i
     }
 }
 
+// ---------------------------------------------------------------------------
+// KNN grouping
+// ---------------------------------------------------------------------------
+// grouping/tf_grouping_g.cu:83-123  selection_sort_gpu, one row at a time
+void hf_oracle_select_top_k(int b, int n, int m, int k, const float *dist, int *outi, float *out) {
+    parallel_for((int64_t)b * m, [&](int64_t lo, int64_t hi) {
+        for (int64_t r = lo; r < hi; ++r) {
+            float *p = out + r * n;
+            int *pi = outi + r * n;
+            for (int s = 0; s < n; ++s) {
+                p[s] = dist[r * n + s];
+                pi[s] = s;
+            }
+            for (int s = 0; s < k && s < n; ++s) {
+                int mn = s;
+                for (int t = s + 1; t < n; ++t)
+                    if (p[t] < p[mn]) mn = t;
+                if (mn != s) {
+                    std::swap(p[mn], p[s]);
+                    std::swap(pi[mn], pi[s]);
+                }
+            }
+        }
+    });
+}
+
+// grouping/tf_grouping.py:62-95  knn_point: squared distances, k smallest ascending, ties to the lower
+// index (tf.nn.top_k).  Distances in the direct form every other op of the path uses (sqdist), not the
+// reference's r2 - 2*x2.x1 + r1 expansion, whose rounding depends on TensorFlow's matmul (absent here).
+void hf_oracle_knn_point(int b, int n, int m, int k, const float *xyz1, const float *xyz2, float *val, int *idx) {
+    parallel_for((int64_t)b * m, [&](int64_t lo, int64_t hi) {
+        std::vector<std::pair<float, int>> d(n);
+        for (int64_t q = lo; q < hi; ++q) {
+            int64_t i = q / m;
+            const float *c = xyz1 + i * (int64_t)n * 3;
+            const float *p = xyz2 + q * 3;
+            for (int j = 0; j < n; ++j) d[j] = {sqdist(p[0] - c[3 * j], p[1] - c[3 * j + 1], p[2] - c[3 * j + 2]), j};
+            std::partial_sort(d.begin(), d.begin() + k, d.end());
+            for (int s = 0; s < k; ++s) {
+                val[q * k + s] = d[s].first;
+                idx[q * k + s] = d[s].second;
+            }
+        }
+    });
+}
+
 }  // extern "C"

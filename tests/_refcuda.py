@@ -180,3 +180,13 @@ def pc_crop_and_sample_grad_fts(fts, box_ind, crop_ind, grad_crop_fts):
     _fn("pccropandsamplegradfts_gpu")(_d(box_ind), _d(crop_ind), _d(grad_crop_fts), _i(N), _i(P), _i(R), _i(C), _d(g))
     torch.cuda.synchronize()
     return g
+
+
+def select_top_k(k, dist):
+    b, m, n = dist.shape
+    outi = torch.zeros((b, m, n), dtype=torch.int32, device=dist.device)
+    out = torch.zeros((b, m, n), dtype=torch.float32, device=dist.device)
+    torch.cuda.synchronize()
+    _fn("selectionSortLauncher")(_i(b), _i(n), _i(m), _i(int(k)), _d(dist), _d(outi), _d(out))
+    torch.cuda.synchronize()
+    return outi, out

@@ -1,0 +1,84 @@
+"""GPU: knn_point and select_top_k (csrc/spatial.cu knn_kernel, csrc/topk.cu) through the Python mirror ->
+ctypes -> C-ABI against the CPU oracle and the unmodified reference SelectionSort kernel on the same B200.
+Bar: bit-exact (indices, values, and for select_top_k the whole output including the unsorted tail)."""
+import numpy as np
+import pytest
+import torch
+
+from heterofusionrcnn_b200 import _lib, synthetic
+from heterofusionrcnn_b200.grouping.tf_grouping import knn_point, select_top_k
+from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample, gather_point
+
+import _refcuda
+
+pytestmark = pytest.mark.gpu
+needs_ref = pytest.mark.skipif(not _refcuda.available(), reason="oracle/_ref/libref_cuda.so not built")
+
+
+def T(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def N(t):
+    return t.detach().cpu().numpy()
+
+
+@pytest.mark.parametrize("b,n,m,k,dup,mode", [(2, 16384, 4096, 16, 0, 0), (2, 16384, 4096, 32, 2000, 0),
+                                              (2, 16384, 4096, 16, 0, 1), (2, 4096, 1024, 32, 500, 2),
+                                              (2, 4096, 1024, 32, 500, 1), (1, 1000, 77, 64, 0, 0), (2, 300, 300, 1, 0, 0),
+                                              (1, 40, 5, 40, 10, 0), (2, 2000, 130, 128, 0, 2), (1, 5000, 33, 8, 0, 2)])
+def test_knn_point_matches_oracle(cuda, oracle, b, n, m, k, dup, mode):
+    """mode 0 = auto, 1 = every-pair kernel forced, 2 = pruned kernel forced."""
+    xyz, _ = synthetic.make_scans(41 + n + k, b, n, duplicate_pad=dup)
+    x1 = T(xyz, cuda)
+    x2 = gather_point(x1, farthest_point_sample(m, x1)) if m <= n else x1
+    want_v, want_i = oracle.knn_point(k, xyz, N(x2))
+    _lib.load().hf_spatial_set_mode(mode)
+    try:
+        val, idx = knn_point(k, x1, x2)
+    finally:
+        _lib.load().hf_spatial_set_mode(0)
+    assert val.shape == (b, m, k) and idx.dtype == torch.int32
+    assert np.array_equal(N(idx), want_i)
+    assert np.array_equal(N(val), want_v)
+
+
+def test_knn_point_rejects_bad_arguments(cuda):
+    x = torch.zeros((1, 8, 3), device=cuda)
+    with pytest.raises(_lib.InvalidArgumentError):
+        knn_point(0, x, x)
+    with pytest.raises(_lib.InvalidArgumentError):
+        knn_point(9, x, x)
+    with pytest.raises(_lib.InvalidArgumentError):
+        knn_point(2, torch.zeros((1, 8, 4), device=cuda), x)
+
+
+@pytest.mark.parametrize("b,m,n,k,ties", [(2, 64, 1024, 32, False), (1, 33, 4096, 16, True), (2, 5, 17, 17, True),
+                                          (1, 3, 25600, 8, False), (1, 4, 7, 20, True)])
+def test_select_top_k_matches_oracle(cuda, oracle, b, m, n, k, ties):
+    rng = np.random.default_rng(n + k)
+    d = rng.integers(0, 50, (b, m, n)).astype(np.float32) if ties else rng.random((b, m, n)).astype(np.float32)
+    wi, wv = oracle.select_top_k(k, d)
+    gi, gv = select_top_k(k, T(d, cuda))
+    assert np.array_equal(N(gi), wi) and np.array_equal(N(gv), wv)
+
+
+@needs_ref
+def test_select_top_k_matches_reference_kernel(cuda):
+    rng = np.random.default_rng(12)
+    d = T(rng.integers(0, 30, (2, 40, 300)).astype(np.float32), cuda)
+    ri, rv = _refcuda.select_top_k(12, d)
+    gi, gv = select_top_k(12, d)
+    assert torch.equal(gi, ri) and torch.equal(gv, rv)
+
+
+def test_select_top_k_of_the_distance_matrix_agrees_with_knn_point(cuda):
+    """The two halves of the reference's knn_point_old path (tf_grouping.py:98-120): distance matrix +
+    SelectionSort gives the same neighbours as the fused kernel when there are no ties."""
+    xyz, _ = synthetic.make_scans(77, 1, 2048)
+    x1 = T(xyz, cuda)
+    x2 = x1[:, :128].contiguous()
+    d = ((x2[:, :, None, :] - x1[:, None, :, :]) ** 2).sum(-1)
+    oi, _ = select_top_k(8, d)
+    _, ki = knn_point(8, x1, x2)
+    assert (oi[:, :, :8] == ki).float().mean().item() > 0.999  # the torch matrix rounds differently from sqdist

@@ -227,3 +227,41 @@ def test_oracle_gradients_are_the_adjoints_of_the_forward_ops(oracle):
     # out-of-range indices are skipped, not written
     idx[0, 0, 0], idx[1, 3, 2] = -1, n
     assert np.isfinite(oracle.group_point_grad(pts, idx, g)).all()
+
+
+# ---------------------------------------------------------------- KNN grouping
+def test_oracle_select_top_k_matches_reference_cpu_prototype_and_its_toy(oracle, capfd):
+    """grouping/test/selection_sort.cpp: the toy of its main() (dist[i] = 10 - i, b=2, n=4, m=2, k=3) and
+    seeded rows with ties, against the reference's own selection_sort_cpu compiled where it lies."""
+    toy = (10.0 - np.arange(16, dtype=np.float32)).reshape(2, 2, 4)
+    oi, ov = oracle.select_top_k(3, toy)
+    assert np.array_equal(oi[0, 0], [3, 2, 1, 0]) and np.array_equal(ov[0, 0], [7, 8, 9, 10])
+    rng = np.random.default_rng(5)
+    d = rng.integers(0, 6, (2, 3, 17)).astype(np.float32)  # many ties: the swap chain decides the order
+    oi, ov = oracle.select_top_k(5, d)
+    assert np.array_equal(np.sort(oi, axis=2), np.broadcast_to(np.arange(17), oi.shape))
+    assert np.array_equal(np.take_along_axis(d, oi.astype(np.int64), axis=2), ov)
+    assert np.array_equal(ov[:, :, :5], np.sort(d, axis=2)[:, :, :5])
+    if not oracle.ref_available("libref_selection_sort_cpu.so"):
+        pytest.skip("oracle/_ref not built")
+    for k in (1, 5, 17):
+        ri, rv = oracle.ref_selection_sort_cpu(k, d)
+        capfd.readouterr()  # the prototype prints every row
+        oi, ov = oracle.select_top_k(k, d)
+        assert np.array_equal(oi, ri) and np.array_equal(ov, rv)
+
+
+def test_oracle_knn_point_is_a_stable_top_k_of_the_squared_distances(oracle):
+    rng = np.random.default_rng(6)
+    x1 = rng.standard_normal((2, 50, 3)).astype(np.float32)
+    x1[:, 10:14] = x1[:, 3:4]  # duplicates: ties go to the lower index
+    x2 = np.concatenate([x1[:, :5], rng.standard_normal((2, 7, 3)).astype(np.float32)], axis=1)
+    val, idx = oracle.knn_point(8, x1, x2)
+    d = ((x2[:, :, None, :].astype(np.float64) - x1[:, None, :, :]) ** 2).sum(-1)
+    order = np.argsort(d, axis=2, kind="stable")[:, :, :8]
+    assert np.allclose(val, np.take_along_axis(d, order, axis=2), rtol=1e-5, atol=1e-6)
+    assert np.array_equal(idx[:, 3, :5], np.broadcast_to([3, 10, 11, 12, 13], (2, 5)))
+    assert (np.diff(val, axis=2) >= 0).all()
+    # the reference's expanded form r2 - 2*x2.x1 + r1 agrees up to its cancellation error
+    exp = (x2 ** 2).sum(-1)[:, :, None] - 2 * np.einsum("bmc,bnc->bmn", x2, x1) + (x1 ** 2).sum(-1)[:, None, :]
+    assert np.allclose(np.sort(exp, axis=2)[:, :, :8], val, atol=1e-4)
