@@ -97,47 +97,73 @@ __device__ __forceinline__ float tap3(float w0, float p0, float w1, float p1, fl
 constexpr int kTiThreads = 256;
 
 // channel-last, c % 4 == 0: points (b,m,c4) float4 -> out (b,n,c4).  grid = (blocks, b)
+// A warp takes U consecutive rows per step: their 3U indices and weights are one coalesced load by
+// lanes 0..3U-1, issued one step AHEAD (the gathers depend on them: without the prefetch every step is
+// two dependent memory round trips and the kernel is latency bound at ~0.5 of the HBM peak), and the
+// 3U gathered 128-bit loads of a channel chunk are all in flight before the first FMA.
+// The grid is one-dimensional and exactly as large as the GPU holds at once (rows of all scenes are one
+// list): these launches last 15-50 us, a partial last wave is a visible fraction of that.
+constexpr int kTiRows = 4;
 __global__ void __launch_bounds__(kTiThreads)
-    three_interpolate_nlc_vec4_kernel(int m, int c4, int n, const float4 *__restrict__ points,
+    three_interpolate_nlc_vec4_kernel(int m, int c4, int n, long long rows_all, const float4 *__restrict__ points,
                                       const int *__restrict__ idx, const float *__restrict__ weight,
                                       float4 *__restrict__ out) {
-    const int scene = blockIdx.y;
+    constexpr int U = kTiRows;
     const int lane = threadIdx.x & 31;
-    const int warp = (blockIdx.x * kTiThreads + threadIdx.x) >> 5;
-    const int nwarps = (gridDim.x * kTiThreads) >> 5;
-    const float4 *pts = points + (size_t)scene * m * c4;
-    const int *ind = idx + (size_t)scene * n * 3;
-    const float *wgt = weight + (size_t)scene * n * 3;
-    float4 *o = out + (size_t)scene * n * c4;
-    for (int r0 = warp * 2; r0 < n; r0 += nwarps * 2) {
-        int i0[2], i1[2], i2[2];
-        float w0[2], w1[2], w2[2];
+    const long long warp = ((long long)blockIdx.x * kTiThreads + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * kTiThreads) >> 5;
+    const long long e_all = rows_all * 3;
+    // lane < 3U: source row (in the batch-flattened points array) and weight of tap lane % 3 of row r0 + lane / 3
+    auto fetch = [&](long long r0, long long &src, float &ww) {
+        const long long e = r0 * 3 + lane;
+        const bool ok = lane < 3 * U && e < e_all;
+        src = 0;
+        ww = 0.f;
+        if (ok) {
+            const long long scene = (e / 3) / n;
+            src = scene * m + __ldg(&idx[e]);
+            ww = __ldg(&weight[e]);
+        }
+    };
+    long long r0 = warp * U;
+    long long cur_i, nxt_i = 0;
+    float cur_w, nxt_w = 0.f;
+    fetch(r0, cur_i, cur_w);
+    for (; r0 < rows_all; r0 += nwarps * U) {
+        fetch(r0 + nwarps * U, nxt_i, nxt_w);
+        const float4 *p0[U], *p1[U], *p2[U];
+        float w0[U], w1[U], w2[U];
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-            int r = r0 + u < n ? r0 + u : r0;
-            i0[u] = ind[r * 3]; i1[u] = ind[r * 3 + 1]; i2[u] = ind[r * 3 + 2];
-            w0[u] = wgt[r * 3]; w1[u] = wgt[r * 3 + 1]; w2[u] = wgt[r * 3 + 2];
+        for (int u = 0; u < U; ++u) {
+            p0[u] = points + __shfl_sync(0xffffffffu, cur_i, 3 * u) * c4;
+            p1[u] = points + __shfl_sync(0xffffffffu, cur_i, 3 * u + 1) * c4;
+            p2[u] = points + __shfl_sync(0xffffffffu, cur_i, 3 * u + 2) * c4;
+            w0[u] = __shfl_sync(0xffffffffu, cur_w, 3 * u);
+            w1[u] = __shfl_sync(0xffffffffu, cur_w, 3 * u + 1);
+            w2[u] = __shfl_sync(0xffffffffu, cur_w, 3 * u + 2);
         }
         for (int v = lane; v < c4; v += 32) {
-            float4 a[2], b[2], c[2];
+            float4 a[U], b[U], c[U];
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-                a[u] = __ldg(&pts[(size_t)i0[u] * c4 + v]);
-                b[u] = __ldg(&pts[(size_t)i1[u] * c4 + v]);
-                c[u] = __ldg(&pts[(size_t)i2[u] * c4 + v]);
+            for (int u = 0; u < U; ++u) {  // rows past the end carry source row 0: valid memory, never stored
+                a[u] = __ldg(p0[u] + v);
+                b[u] = __ldg(p1[u] + v);
+                c[u] = __ldg(p2[u] + v);
             }
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-                if (r0 + u < n) {
+            for (int u = 0; u < U; ++u) {
+                if (r0 + u < rows_all) {
                     float4 r;
                     r.x = tap3(w0[u], a[u].x, w1[u], b[u].x, w2[u], c[u].x);
                     r.y = tap3(w0[u], a[u].y, w1[u], b[u].y, w2[u], c[u].y);
                     r.z = tap3(w0[u], a[u].z, w1[u], b[u].z, w2[u], c[u].z);
                     r.w = tap3(w0[u], a[u].w, w1[u], b[u].w, w2[u], c[u].w);
-                    stg_cs_f4(&o[(size_t)(r0 + u) * c4 + v], r);
+                    stg_cs_f4(&out[(size_t)(r0 + u) * c4 + v], r);
                 }
             }
         }
+        cur_i = nxt_i;
+        cur_w = nxt_w;
     }
 }
 
@@ -214,13 +240,16 @@ extern "C" int hf_three_interpolate_nlc(int b, int m, int c, int n, const float 
     bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(points) & 15) == 0) &&
                ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
     if (vec) {
-        int warps_needed = (n + 1) / 2;
-        int blocks = (warps_needed + (kTiThreads / 32) - 1) / (kTiThreads / 32);
-        int cap = (sms * 8 + b - 1) / b;
-        if (blocks > cap) blocks = cap;
-        if (blocks < 1) blocks = 1;
-        three_interpolate_nlc_vec4_kernel<<<dim3(blocks, b), kTiThreads, 0, s>>>(
-            m, c / 4, n, reinterpret_cast<const float4 *>(points), idx, weight, reinterpret_cast<float4 *>(out));
+        const long long rows_all = (long long)b * n;
+        static int per_sm = 0;
+        if (per_sm == 0) {
+            HF_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, three_interpolate_nlc_vec4_kernel, kTiThreads, 0));
+            if (per_sm < 1) per_sm = 1;
+        }
+        long long blocks = (rows_all + (long long)kTiRows * (kTiThreads / 32) - 1) / ((long long)kTiRows * (kTiThreads / 32));
+        if (blocks > (long long)sms * per_sm) blocks = (long long)sms * per_sm;
+        three_interpolate_nlc_vec4_kernel<<<(unsigned)blocks, kTiThreads, 0, s>>>(
+            m, c / 4, n, rows_all, reinterpret_cast<const float4 *>(points), idx, weight, reinterpret_cast<float4 *>(out));
         HF_LAUNCH_OK("three_interpolate_nlc_vec4_kernel");
     } else {
         long long total = (long long)n * c;
