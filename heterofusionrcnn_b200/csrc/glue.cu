@@ -1,0 +1,187 @@
+// glue.cu — the callers' glue around BEV IoU / NMS (hf/core/compute_iou.py), on the device, for sm_100a.
+//
+//   boxes3d_to_bev_tf   compute_iou.py:7-20    [x,y,z,l,w,h,ry] -> [x-l/2, z-w/2, x+l/2, z+w/2, ry]
+//   box3d_iou_tf        compute_iou.py:23-64   BEV overlap x height overlap -> 3-D IoU (+ the 2-D IoU)
+//   oriented_nms_tf     compute_iou.py:67-80   BEV boxes, tf.nn.top_k over ALL scores (a full descending
+//                                               sort, equal scores keep the lower index first), oriented_nms,
+//                                               keep list mapped back to the caller's box order
+// The reference runs these as a dozen small TF ops (tile / reshape / gather) around the two custom ops, and
+// per scene inside a tf.map_fn (rpn_model.py:683).  Here they are batched over scenes and stay on the device.
+#include <float.h>
+#include <stdint.h>
+
+#include "common.cuh"
+
+namespace hf {
+namespace {
+
+__global__ void boxes3d_to_bev_kernel(long long total, const float *__restrict__ b3, const int *__restrict__ order,
+                                      int per_scene, float *__restrict__ bev) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        long long src = i;
+        if (order) src = (i / per_scene) * per_scene + order[i];  // row i of the sorted list
+        const float *p = b3 + src * 7;
+        const float hl = p[3] / 2, hw = p[4] / 2;
+        float *o = bev + i * 5;
+        o[0] = p[0] - hl;
+        o[1] = p[2] - hw;
+        o[2] = p[0] + hl;
+        o[3] = p[2] + hw;
+        o[4] = p[6];
+    }
+}
+
+// iou3d holds the BEV overlap on entry (compute_iou.py:38-62).
+__global__ void box3d_iou_kernel(int na, int nb, const float *__restrict__ a, const float *__restrict__ b,
+                                 float *__restrict__ iou3d) {
+    const long long total = (long long)na * nb;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const float *pa = a + (i / nb) * 7, *pb = b + (i % nb) * 7;
+        const float amin = __fsub_rn(pa[1], pa[5]), amax = pa[1], bmin = __fsub_rn(pb[1], pb[5]), bmax = pb[1];
+        const float oh = fminf(fmaxf(__fsub_rn(fminf(amax, bmax), fmaxf(amin, bmin)), 0.f), FLT_MAX);
+        const float o3 = __fmul_rn(iou3d[i], oh);
+        const float va = __fmul_rn(__fmul_rn(pa[3], pa[4]), pa[5]), vb = __fmul_rn(__fmul_rn(pb[3], pb[4]), pb[5]);
+        const float den = fminf(fmaxf(__fsub_rn(__fadd_rn(va, vb), o3), 1e-7f), FLT_MAX);
+        iou3d[i] = __fdiv_rn(o3, den);
+    }
+}
+
+// Descending stable order of one scene's scores: 64-bit keys {~ordered(score), index}, bitonic sort in shared memory.
+constexpr int kSortThreads = 1024;
+__global__ void __launch_bounds__(kSortThreads) score_order_kernel(int n, int P, const float *__restrict__ scores,
+                                                                   int *__restrict__ order) {
+    extern __shared__ __align__(16) unsigned long long keys[];
+    const int t = threadIdx.x;
+    const float *sc = scores + (size_t)blockIdx.x * n;
+    for (int i = t; i < P; i += kSortThreads) {
+        unsigned long long k = ~0ull;
+        if (i < n) {
+            float f = sc[i];
+            if (f == 0.f) f = 0.f;  // -0 and +0 are one score
+            unsigned u = __float_as_uint(f);
+            u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // ascending order of the float as unsigned
+            if (f != f) u = 0u;                              // NaN scores sort last
+            k = ((unsigned long long)(~u) << 32) | (unsigned)i;
+        }
+        keys[i] = k;
+    }
+    __syncthreads();
+    for (int k2 = 2; k2 <= P; k2 <<= 1) {
+        for (int j = k2 >> 1; j > 0; j >>= 1) {
+            for (int i = t; i < P; i += kSortThreads) {
+                const int p = i ^ j;
+                if (p > i) {
+                    const unsigned long long x = keys[i], y = keys[p];
+                    if ((x > y) == ((i & k2) == 0)) {
+                        keys[i] = y;
+                        keys[p] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    int *o = order + (size_t)blockIdx.x * n;
+    for (int i = t; i < n; i += kSortThreads) o[i] = (int)(unsigned)keys[i];
+}
+
+__global__ void map_keep_kernel(long long total, int per_scene, const int *__restrict__ order,
+                                const int *__restrict__ keep_sorted, int *__restrict__ keep) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long base = (i / per_scene) * per_scene;
+        keep[i] = order[base + keep_sorted[i]];
+    }
+}
+
+inline size_t a16(size_t v) { return (v + 15) & ~(size_t)15; }
+inline int grid_for(long long total) {
+    long long g = (total + 255) / 256;
+    const long long cap = (long long)num_sms() * 8;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_boxes3d_to_bev(long long num, const float *boxes3d, float *boxes_bev, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(num >= 0, "boxes3d_to_bev expects (N,7) boxes3d");
+    HF_REQUIRE(num == 0 || (boxes3d && boxes_bev), "boxes3d_to_bev: null pointer");
+    if (num == 0) return HF_OK;
+    boxes3d_to_bev_kernel<<<grid_for(num), 256, 0, (cudaStream_t)stream>>>(num, boxes3d, nullptr, 1, boxes_bev);
+    HF_LAUNCH_OK("boxes3d_to_bev_kernel");
+    return HF_OK;
+}
+
+extern "C" size_t hf_box3d_iou_workspace_bytes(int num_a, int num_b) {
+    if (num_a < 0 || num_b < 0) return 0;
+    return hf::a16((size_t)num_a * 20) + hf::a16((size_t)num_b * 20) + 16;
+}
+
+extern "C" int hf_box3d_iou(int num_a, const float *boxes_a, int num_b, const float *boxes_b, float *iou_3d, float *iou_2d,
+                            void *workspace, size_t workspace_bytes, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(num_a >= 0 && num_b >= 0, "box3d_iou expects (N,7) and (M,7) boxes");
+    if (num_a == 0 || num_b == 0) return HF_OK;
+    HF_REQUIRE(boxes_a && boxes_b && iou_3d && iou_2d, "box3d_iou: null pointer");
+    HF_REQUIRE(workspace && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "box3d_iou: null or unaligned workspace");
+    if (workspace_bytes < hf_box3d_iou_workspace_bytes(num_a, num_b)) {
+        set_error("box3d_iou: workspace too small");
+        return HF_ERR_WORKSPACE;
+    }
+    float *bev_a = static_cast<float *>(workspace);
+    float *bev_b = reinterpret_cast<float *>(static_cast<unsigned char *>(workspace) + a16((size_t)num_a * 20));
+    int rc = hf_boxes3d_to_bev(num_a, boxes_a, bev_a, stream);
+    if (rc == HF_OK) rc = hf_boxes3d_to_bev(num_b, boxes_b, bev_b, stream);
+    if (rc == HF_OK) rc = hf_compute_bev_iou(num_a, bev_a, num_b, bev_b, iou_3d, iou_2d, stream);  // iou_3d <- overlap
+    if (rc != HF_OK) return rc;
+    box3d_iou_kernel<<<grid_for((long long)num_a * num_b), 256, 0, (cudaStream_t)stream>>>(num_a, num_b, boxes_a, boxes_b, iou_3d);
+    HF_LAUNCH_OK("box3d_iou_kernel");
+    return HF_OK;
+}
+
+extern "C" size_t hf_oriented_nms_scored_workspace_bytes(int scenes, int boxes_num) {
+    if (scenes <= 0 || boxes_num <= 0) return 16;
+    const size_t sn = (size_t)scenes * boxes_num;
+    return hf::a16(sn * 4) + hf::a16(sn * 20) + hf::a16(sn * 4) + hf_oriented_nms_workspace_bytes(scenes, boxes_num);
+}
+
+extern "C" int hf_oriented_nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_num, float thresh,
+                                      int *keep, int *num_kept, void *workspace, size_t workspace_bytes,
+                                      hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(thresh >= 0, "Need nms_threshold >= 0, got %f", (double)thresh);
+    HF_REQUIRE(scenes >= 0 && boxes_num >= 0, "oriented_nms expects (S,N,7) boxes and (S,N) scores");
+    if (scenes == 0 || boxes_num == 0) return HF_OK;
+    HF_REQUIRE(boxes3d && scores && keep, "oriented_nms: null pointer");
+    HF_REQUIRE(workspace && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "oriented_nms: null or unaligned workspace");
+    if (workspace_bytes < hf_oriented_nms_scored_workspace_bytes(scenes, boxes_num)) {
+        set_error("oriented_nms: workspace too small");
+        return HF_ERR_WORKSPACE;
+    }
+    int P = 32;
+    while (P < boxes_num) P <<= 1;
+    if ((size_t)P * 8 > 200 * 1024) {
+        set_error("oriented_nms: more than %d boxes per scene are not supported by the score sort", 200 * 1024 / 8);
+        return HF_ERR_UNSUPPORTED;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t sn = (size_t)scenes * boxes_num;
+    unsigned char *w = static_cast<unsigned char *>(workspace);
+    int *order = reinterpret_cast<int *>(w);
+    float *bev = reinterpret_cast<float *>(w + a16(sn * 4));
+    int *keep_sorted = reinterpret_cast<int *>(w + a16(sn * 4) + a16(sn * 20));
+    void *nms_ws = w + a16(sn * 4) + a16(sn * 20) + a16(sn * 4);
+    const size_t smem = (size_t)P * 8;
+    if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(score_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    score_order_kernel<<<scenes, kSortThreads, smem, s>>>(boxes_num, P, scores, order);
+    HF_LAUNCH_OK("score_order_kernel");
+    boxes3d_to_bev_kernel<<<grid_for((long long)sn), 256, 0, s>>>((long long)sn, boxes3d, order, boxes_num, bev);
+    HF_LAUNCH_OK("boxes3d_to_bev_kernel");
+    int rc = hf_oriented_nms(bev, scenes, boxes_num, thresh, keep_sorted, num_kept, nms_ws,
+                             hf_oriented_nms_workspace_bytes(scenes, boxes_num), stream);
+    if (rc != HF_OK) return rc;
+    map_keep_kernel<<<grid_for((long long)sn), 256, 0, s>>>((long long)sn, boxes_num, order, keep_sorted, keep);
+    HF_LAUNCH_OK("map_keep_kernel");
+    return HF_OK;
+}

@@ -248,6 +248,24 @@ int hf_knn_point(int b, int n, int m, int k, const float *xyz1, const float *xyz
 int hf_select_top_k(int b, int n, int m, int k, const float *dist, int *outi, float *out,
                     hf_stream_t stream);
 
+/* ---- glue of hf/core/compute_iou.py --------- */
+/* boxes3d_to_bev_tf, compute_iou.py:7-20: (N,7) [x,y,z,l,w,h,ry] -> (N,5) [x-l/2, z-w/2, x+l/2, z+w/2, ry]. */
+int hf_boxes3d_to_bev(long long num, const float *boxes3d, float *boxes_bev, hf_stream_t stream);
+/* box3d_iou_tf, compute_iou.py:23-64: boxes_a (N,7), boxes_b (M,7) -> iou_3d (N,M), iou_2d (N,M)
+ * (BEV overlap x height overlap over the union of the volumes, clipped at 1e-7). */
+size_t hf_box3d_iou_workspace_bytes(int num_a, int num_b);
+int hf_box3d_iou(int num_a, const float *boxes_a, int num_b, const float *boxes_b, float *iou_3d,
+                 float *iou_2d, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* oriented_nms_tf, compute_iou.py:67-80, batched over scenes (the reference maps scenes with
+ * tf.map_fn, rpn_model.py:683): boxes3d (S,N,7), scores (S,N) in any order -> keep (S,N) indices
+ * into the caller's box order (descending score, suppressed boxes removed, tail padded with
+ * keep[0] like bev_iou.cpp:104-112), num_kept (S) (may be NULL).  Equal scores keep the lower
+ * index first (tf.nn.top_k).  At most 25600 boxes per scene. */
+size_t hf_oriented_nms_scored_workspace_bytes(int scenes, int boxes_num);
+int hf_oriented_nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_num,
+                           float nms_overlap_thresh, int *keep, int *num_kept, void *workspace,
+                           size_t workspace_bytes, hf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -329,3 +329,31 @@ def ref_bev_host(boxes_a, boxes_b):
             overlap[i, j] = L.ref_host_box_overlap(pa, pb)
             iou[i, j] = L.ref_host_iou_bev(pa, pb)
     return overlap, iou
+
+
+# ---- glue of hf/core/compute_iou.py (numpy restatement, float32 throughout) ----------------
+def boxes3d_to_bev(boxes3d):
+    """compute_iou.py:7-20."""
+    b = np.asarray(boxes3d, np.float32)
+    hl, hw = b[:, 3] / np.float32(2), b[:, 4] / np.float32(2)
+    return np.stack([b[:, 0] - hl, b[:, 2] - hw, b[:, 0] + hl, b[:, 2] + hw, b[:, 6]], axis=1).astype(np.float32)
+
+
+def box3d_iou(boxes_a, boxes_b):
+    """compute_iou.py:23-64."""
+    a, b = np.asarray(boxes_a, np.float32), np.asarray(boxes_b, np.float32)
+    overlap, iou2d = compute_bev_iou(boxes3d_to_bev(a), boxes3d_to_bev(b))
+    amin, amax = (a[:, 1] - a[:, 5])[:, None], a[:, 1][:, None]
+    bmin, bmax = (b[:, 1] - b[:, 5])[None, :], b[:, 1][None, :]
+    oh = np.clip(np.minimum(amax, bmax) - np.maximum(amin, bmin), 0, np.finfo(np.float32).max).astype(np.float32)
+    o3 = overlap * oh
+    va, vb = (a[:, 3] * a[:, 4] * a[:, 5])[:, None], (b[:, 3] * b[:, 4] * b[:, 5])[None, :]
+    iou3d = o3 / np.clip(va + vb - o3, np.float32(1e-7), np.finfo(np.float32).max)
+    return iou3d.astype(np.float32), iou2d
+
+
+def oriented_nms_scored(boxes3d, scores, thresh):
+    """compute_iou.py:67-80: tf.nn.top_k over all scores = stable descending sort."""
+    order = np.argsort(-np.asarray(scores, np.float32), kind="stable").astype(np.int32)
+    keep_sorted = oriented_nms(boxes3d_to_bev(np.asarray(boxes3d, np.float32)[order]), thresh)
+    return order[keep_sorted]

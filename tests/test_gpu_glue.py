@@ -1,0 +1,59 @@
+"""GPU: the compute_iou.py glue (csrc/glue.cu) through the Python mirror -> ctypes -> C-ABI against the oracle.
+Bar: keep lists bit-exact; BEV boxes bit-exact; IoU values within 1e-5 relative (sinf/cosf differ by ulps
+between CUDA and glibc, as for compute_bev_iou)."""
+import numpy as np
+import pytest
+import torch
+
+from heterofusionrcnn_b200 import synthetic
+from heterofusionrcnn_b200.compute_iou import box3d_iou_tf, boxes3d_to_bev_tf, oriented_nms_tf
+
+pytestmark = pytest.mark.gpu
+
+
+def T(a, dev):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+
+def N(t):
+    return t.detach().cpu().numpy()
+
+
+def clustered_boxes3d(seed, num, clusters=25):
+    rng = np.random.default_rng(seed)
+    xyz, _ = synthetic.make_scan(seed, 4096)
+    base = synthetic.make_boxes3d(seed, xyz, clusters)
+    b = base[rng.integers(0, clusters, num)].copy()
+    b[:, [0, 2]] += rng.normal(0, 0.3, (num, 2)).astype(np.float32)
+    b[:, 6] += rng.normal(0, 0.1, num).astype(np.float32)
+    return b.astype(np.float32)
+
+
+def test_boxes3d_to_bev_and_box3d_iou(cuda, oracle):
+    a, b = clustered_boxes3d(1, 300), clustered_boxes3d(2, 40)
+    b[:5] = a[:5]  # identical boxes: IoU 1
+    assert np.array_equal(N(boxes3d_to_bev_tf(T(a, cuda))), oracle.boxes3d_to_bev(a))
+    want3, want2 = oracle.box3d_iou(a, b)
+    got3, got2 = box3d_iou_tf(T(a, cuda), T(b, cuda))
+    assert np.allclose(N(got2), want2, rtol=1e-5, atol=1e-6)
+    assert np.allclose(N(got3), want3, rtol=1e-5, atol=1e-6)
+    assert np.allclose(np.diag(N(got3)[:5, :5]), 1.0, atol=1e-4) and (N(got3) > 0).sum() > 100
+
+
+@pytest.mark.parametrize("s,n,thresh,ties", [(1, 700, 0.5, False), (3, 2000, 0.8, False), (2, 9000, 0.85, False),
+                                             (2, 1500, 0.01, True), (1, 33, 0.3, True)])
+def test_oriented_nms_tf_matches_oracle(cuda, oracle, s, n, thresh, ties):
+    rng = np.random.default_rng(n)
+    boxes = np.stack([clustered_boxes3d(10 + i, n) for i in range(s)])
+    scores = rng.random((s, n)).astype(np.float32)
+    if ties:
+        scores = np.round(scores * 20) / np.float32(20)  # many equal scores: the lower index goes first
+        scores[:, ::17] = -0.0
+    keep, num = oriented_nms_tf(T(boxes, cuda), T(scores, cuda), thresh, return_num_kept=True)
+    for i in range(s):
+        want = oracle.oriented_nms_scored(boxes[i], scores[i], thresh)
+        assert np.array_equal(N(keep[i]), want), i
+    k0, n0 = N(keep[0]), int(N(num)[0])
+    assert len(set(k0[:n0].tolist())) == n0 and (np.diff(scores[0][k0[:n0]]) <= 0).all()
+    single = oriented_nms_tf(T(boxes[0], cuda), T(scores[0], cuda), thresh)
+    assert torch.equal(single, keep[0])
