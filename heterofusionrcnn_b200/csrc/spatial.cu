@@ -37,7 +37,10 @@ namespace {
 
 constexpr int kIdxThreads = 1024;
 constexpr int kIdxMaxE = 16;                        // sort elements per thread
-constexpr int kMaxIndexed = kIdxMaxE * kIdxThreads;  // 16384 points per cloud fit the shared-memory sort
+constexpr int kMaxIndexed = kIdxMaxE * kIdxThreads;  // 16384 points fit the shared-memory sort of one CTA
+// Larger clouds are indexed in PARTS of <= 16384 consecutive points, each sorted by its own CTA: the query
+// kernels only need buckets of 32 nearby points with a box, not one curve through the whole cloud.
+constexpr int kMaxCloud = 4 * kMaxIndexed;
 constexpr int kHistPitch = 257;                     // hist[warp][digit], padded: conflict free by digit and by warp
 constexpr int kHistWords = 32 * kHistPitch;
 constexpr size_t kIdxSmem = (size_t)kMaxIndexed * 4 + (size_t)kHistWords * 4 + (size_t)kMaxIndexed * 2;  // 128 KB
@@ -79,11 +82,12 @@ struct CloudDesc {
     const float *xyz;  // (b, n, 3)
     float4 *sorted;    // (b, npad) {x, y, z, original index as int bits}; padding = {NaN, NaN, NaN, -1}
     float4 *boxes;     // (b, npad/32, 2) {lo.xyz, smallest original index in the bucket}, {hi.xyz, -}
-    int n, npad, per_thread;  // points, rounded up to 32, sort elements per thread = ceil(n / 1024)
+    int n, npad, per_thread;  // points, rounded up to 32, sort elements per thread = ceil(part_n / 1024)
+    int parts, part_n;        // the cloud is sorted in `parts` runs of part_n (a multiple of 32) consecutive points
 };
 
 // grid = (b, 2): blockIdx.y selects the cloud.  dynamic smem = kIdxSmem.
-__global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc ca, CloudDesc cb) {
+__global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc ca, CloudDesc cb, int gparts) {
     extern __shared__ __align__(16) unsigned char idx_smem[];
     uint32_t *code = reinterpret_cast<uint32_t *>(idx_smem);               // [np] Hilbert position
     uint32_t *hist = code + kIdxMaxE * kIdxThreads;                         // [32 warps][257]
@@ -100,9 +104,12 @@ __global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc c
 #define TICK() do {} while (0)
 #endif
     TICK();
-    const int scene = blockIdx.x;
-    const int n = cd.n;
-    const float *data = cd.xyz + (size_t)scene * n * 3;
+    const int scene = blockIdx.x / gparts, part = blockIdx.x % gparts;
+    if (part >= cd.parts) return;
+    const int base = part * cd.part_n;
+    const int n = min(cd.part_n, cd.n - base);  // points of this part
+    if (n <= 0) return;
+    const float *data = cd.xyz + ((size_t)scene * cd.n + base) * 3;
     if (t < 192) hlut[t] = kHilbertLut[t];  // read after the barriers of the bounding box pass
 
     // ---- bounding box -> cubic quantisation ----
@@ -233,10 +240,11 @@ __global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc c
     }
 
     // ---- sorted copy + bucket boxes (a warp writes one bucket per step) ----
-    float4 *sorted = cd.sorted + (size_t)scene * cd.npad;
-    float4 *boxes = cd.boxes + (size_t)scene * (cd.npad / 32) * 2;
+    float4 *sorted = cd.sorted + (size_t)scene * cd.npad + base;
+    float4 *boxes = cd.boxes + ((size_t)scene * (cd.npad / 32) + base / 32) * 2;
+    const int npad = (n + 31) & ~31;
     const float qnan = __int_as_float(0x7FC00000);
-    for (int i0 = t; i0 < cd.npad; i0 += 4 * kIdxThreads) {
+    for (int i0 = t; i0 < npad; i0 += 4 * kIdxThreads) {
         float4 v[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {  // the 12 gathers of a step are in flight together
@@ -247,13 +255,13 @@ __global__ void __launch_bounds__(kIdxThreads, 1) cloud_index_kernel(CloudDesc c
                 v[u].x = __ldg(&data[(size_t)src * 3]);
                 v[u].y = __ldg(&data[(size_t)src * 3 + 1]);
                 v[u].z = __ldg(&data[(size_t)src * 3 + 2]);
-                v[u].w = __int_as_float(src);
+                v[u].w = __int_as_float(src + base);
             }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int i = i0 + u * kIdxThreads;
-            if (i >= cd.npad) break;  // warp uniform: npad is a multiple of 32
+            if (i >= npad) break;  // warp uniform: npad is a multiple of 32
             const bool real = i < n;
             sorted[i] = v[u];
             // bucket box + smallest original index: 7 redux.sync on order-preserving integer images
@@ -707,7 +715,7 @@ inline size_t cloud_bytes(int b, int n) { return (size_t)b * round32(n) * 17; } 
 // Is the pruned path used for a call whose query cloud has nq points and candidate cloud nc?
 bool spatial_applies(int nq, int nc) {
     if (g_spatial_mode == 1) return false;
-    if (nq < 1 || nc < 1 || nq > kMaxIndexed || nc > kMaxIndexed) return false;
+    if (nq < 1 || nc < 1 || nq > kMaxCloud || nc > kMaxCloud) return false;
     if (g_spatial_mode == 2) return true;
     return nq >= 64 && nc >= 64 && (long long)nq * nc >= (1ll << 24);  // measured: tools/spatial_bench.py
 }
@@ -727,7 +735,9 @@ CloudDesc carve_index(int b, int n, const float *xyz, void *mem) {
     d.xyz = xyz;
     d.n = n;
     d.npad = round32(n);
-    d.per_thread = (n + kIdxThreads - 1) / kIdxThreads;
+    d.parts = (n + kMaxIndexed - 1) / kMaxIndexed;
+    d.part_n = round32((n + d.parts - 1) / d.parts);
+    d.per_thread = (d.part_n + kIdxThreads - 1) / kIdxThreads;
     d.sorted = reinterpret_cast<float4 *>(w);
     d.boxes = reinterpret_cast<float4 *>(w + (size_t)b * d.npad * 16);
     return d;
@@ -736,7 +746,8 @@ CloudDesc carve_index(int b, int n, const float *xyz, void *mem) {
 // Sort one cloud (or the two clouds of a call, in one launch) into their index memory.
 int launch_index(int b, const CloudDesc &a, const CloudDesc *second, cudaStream_t s) {
     HF_CUDA_OK(cudaFuncSetAttribute(cloud_index_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kIdxSmem));
-    cloud_index_kernel<<<dim3(b, second ? 2 : 1), kIdxThreads, kIdxSmem, s>>>(a, second ? *second : a);
+    const int gparts = second && second->parts > a.parts ? second->parts : a.parts;
+    cloud_index_kernel<<<dim3(b * gparts, second ? 2 : 1), kIdxThreads, kIdxSmem, s>>>(a, second ? *second : a, gparts);
     HF_LAUNCH_OK("cloud_index_kernel");
     return HF_OK;
 }
@@ -772,7 +783,7 @@ extern "C" int hf_spatial_applies(int nq, int nc) { return hf::spatial_applies(n
 
 extern "C" size_t hf_cloud_index_bytes(int b, int n) {
     using namespace hf;
-    if (b <= 0 || n <= 0 || n > kMaxIndexed) return 0;
+    if (b <= 0 || n <= 0 || n > kMaxCloud) return 0;
     return cloud_bytes(b, n);
 }
 
@@ -783,7 +794,7 @@ extern "C" size_t hf_spatial_workspace_bytes(int b, int n, int m) {
 
 extern "C" int hf_cloud_index_build(int b, int n, const float *xyz, void *index, size_t index_bytes, hf_stream_t stream) {
     using namespace hf;
-    HF_REQUIRE(b >= 0 && n >= 1 && n <= kMaxIndexed, "CloudIndex: 1 <= num_points <= %d", kMaxIndexed);
+    HF_REQUIRE(b >= 0 && n >= 1 && n <= kMaxCloud, "CloudIndex: 1 <= num_points <= %d", kMaxCloud);
     HF_REQUIRE(b <= 65535, "CloudIndex: batch_size > 65535 not supported");
     HF_REQUIRE(xyz && index && aligned16(index), "CloudIndex: null or unaligned pointer");
     if (index_bytes < hf_cloud_index_bytes(b, n)) {

@@ -247,7 +247,9 @@ def pruned(cuda):
 @pytest.mark.parametrize("b,n,m,r,ns,dup", [(2, 4096, 1024, 0.2, 32, 0), (2, 5000, 777, 0.4, 16, 600), (1, 16384, 300, 0.1, 32, 0),
                                             (2, 3000, 3000, 2.0, 32, 0), (1, 2048, 512, 50.0, 32, 500), (2, 100, 33, 1.0, 8, 0),
                                             (1, 31, 1, 0.5, 4, 0), (1, 1, 5, 0.5, 3, 0), (2, 1500, 200, 4.0, 64, 0),
-                                            (1, 6000, 128, 8.0, 128, 1000), (1, 700, 64, 1e-6, 32, 0)])
+                                            (1, 6000, 128, 8.0, 128, 1000), (1, 700, 64, 1e-6, 32, 0),
+                                            (1, 20000, 900, 0.5, 32, 3000), (1, 65536, 4096, 0.4, 32, 0),
+                                            (1, 40000, 20000, 1.0, 16, 0)])
 def test_query_ball_point_pruned_matches_oracle(cuda, oracle, pruned, b, n, m, r, ns, dup):
     """Ragged sizes, duplicate points, rows with no hit, rows with far more hits than nsample
     (the nsample smallest indices must survive), every query inside every ball (r = 50)."""
@@ -261,7 +263,8 @@ def test_query_ball_point_pruned_matches_oracle(cuda, oracle, pruned, b, n, m, r
 
 @pytest.mark.parametrize("b,n,m,dup", [(2, 4096, 1024, 0), (2, 5000, 777, 600), (1, 16384, 300, 2000), (2, 3000, 3000, 0),
                                        (2, 100, 33, 10), (1, 31, 1, 0), (1, 5, 2, 0), (1, 1, 700, 0), (2, 1500, 3, 0),
-                                       (1, 16384, 16384, 4000)])
+                                       (1, 16384, 16384, 4000), (1, 20000, 900, 3000), (1, 65536, 4096, 0),
+                                       (1, 33000, 40000, 5000)])
 def test_three_nn_pruned_matches_oracle(cuda, oracle, pruned, b, n, m, dup):
     """Incl. exact distance ties (duplicate points: the lower index must win) and m < 3 (+inf, index 0)."""
     xyz, _ = synthetic.make_scans(n * 3 + m + 1, b, max(n, m), duplicate_pad=min(dup, max(n, m) - 1))
@@ -295,6 +298,26 @@ def test_pruned_kernels_equal_every_pair_kernels_on_the_chain_shapes(cuda):
                 assert torch.equal(g[0], w[0]) and torch.equal(g[1], w[1])
     finally:
         lib.hf_spatial_set_mode(0)
+
+
+def test_pruned_kernels_equal_every_pair_kernels_at_config5_level1(cuda):
+    """BASELINE config 5, level 1 (65536 -> 16384): clouds indexed in four parts; pruned == every-pair."""
+    from heterofusionrcnn_b200 import _lib
+
+    lib = _lib.load()
+    xyz, _ = synthetic.make_scans(17, 2, 65536, duplicate_pad=3000)
+    x0 = T(xyz, cuda)
+    x1 = gather_point(x0, farthest_point_sample(16384, x0))
+    try:
+        lib.hf_spatial_set_mode(1)
+        want_nn, want_bq = three_nn(x0, x1), [query_ball_point(r, 32, x0, x1) for r in (0.1, 0.5)]
+        lib.hf_spatial_set_mode(0)  # auto: these shapes take the pruned kernels
+        got_nn, got_bq = three_nn(x0, x1), [query_ball_point(r, 32, x0, x1) for r in (0.1, 0.5)]
+    finally:
+        lib.hf_spatial_set_mode(0)
+    assert torch.equal(got_nn[0], want_nn[0]) and torch.equal(got_nn[1], want_nn[1])
+    for g, w in zip(got_bq, want_bq):
+        assert torch.equal(g[0], w[0]) and torch.equal(g[1], w[1])
 
 
 @pytest.mark.parametrize("c", [1, 3, 4, 96, 130, 256])
