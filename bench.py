@@ -61,9 +61,10 @@ def parse_args():
     ap.add_argument("--resident-inflight", type=int, default=1,
                     help="resident leg: batches kept in flight (measured: 2 is slower than 1 - the second batch's FPS "
                          "clusters cannot be gang-scheduled while the first batch's bulk kernels fill every SM)")
-    ap.add_argument("--graph", action="store_true",
-                    help="resident leg: replay one captured CUDA graph per step instead of issuing every launch from Python "
-                         "(measured equal within noise: the step is GPU bound, not launch bound)")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="resident leg: issue every launch from Python each step instead of replaying the captured CUDA graph "
+                         "(equal within noise on one GPU; with 8 ranks on one host the Python enqueue becomes the bottleneck: "
+                         "2.45 -> 3.63 ms/step eager, profiles/r1_bench_8gpu_eager_v10.json)")
     ap.add_argument("--timeline", action="store_true",
                     help="print (stderr) when every op of the last timed step started and ended, relative to the step's start")
     ap.add_argument("--profile-range", action="store_true",
@@ -107,7 +108,7 @@ def config_dict(args, cfg, n_gpus):
         "sharding": "batch slices, one per GPU, no collective" if n_gpus > 1 else "single GPU",
         "issue": "one stream, program order" if args.serial else
                  "independent branches of the chain on 13 CUDA streams%s, %d batch(es) in flight (e2e leg: eager, %d)" % (
-                     ", one step = one replay of the captured CUDA graph" if (args.graph and not args.timeline) else "",
+                     "" if (args.no_graph or args.timeline) else ", one step = one replay of the captured CUDA graph",
                      max(1, args.resident_inflight), max(1, args.inflight)),
         "l2": "no explicit flush: one step reads 0.45 GB and writes 5.6 GB per GPU, far beyond the 126 MB L2",
     }
@@ -372,7 +373,7 @@ def run_b200(args):
 
     # ---- resident-input throughput (value) + per-launch events (roofline) ----
     overlap = not args.serial
-    use_graph = overlap and args.graph and not args.timeline
+    use_graph = overlap and not args.no_graph and not args.timeline
     depth = max(1, args.resident_inflight) if overlap else 1
     probe = EventProbe(torch)
     probe.enabled = False

@@ -64,6 +64,7 @@ SIGNATURES = {
     "hf_three_interpolate": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_interpolate_nlc": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_pc_crop_and_sample": (_c_int, [_ptr] * 6 + [_c_int] * 6 + [_ptr] * 6 + [_ptr]),
+    "hf_pc_crop_and_sample_indexed": (_c_int, [_ptr] * 6 + [_c_int] * 6 + [_ptr] * 6 + [_ptr, _ptr]),
     "hf_compute_bev_iou": (_c_int, [_c_int, _ptr, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_oriented_nms_mask": (_c_int, [_ptr, _ptr, _c_int, _c_float, _c_int, _ptr]),
     "hf_oriented_nms_workspace_bytes": (_size_t, [_c_int, _c_int]),

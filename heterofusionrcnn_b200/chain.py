@@ -255,10 +255,11 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
         res["nms_keep"] = keep[:, : cfg.post_nms]
         res["nms_num"] = num
     if cfg.with_crop:
+        after(s_crop, index_ready[0])  # the input's index (if built) also prunes the crop's point-in-box scan
         with on(s_crop), probe("pc_crop_and_sample", b=b, p=cfg.points, c=cfg.crop_channels,
                                nb=dev["crop_boxes"].shape[0], r=cfg.crop_resize):
             res["crop"] = pc_crop_and_sample(dev["xyz"], dev["crop_fts"], dev["intensity"], dev["fg_mask"],
-                                             dev["crop_boxes"], dev["box_ind"], cfg.crop_resize)
+                                             dev["crop_boxes"], dev["box_ind"], cfg.crop_resize, index=index[0])
     # ---- set abstraction ----
     nn = [None] * 4
     nn_ready = [None] * 4

@@ -8,7 +8,7 @@ from .. import _lib
 from .._tensors import dev_tensor, require, scatter_workspace, stream_ptr
 
 
-def pc_crop_and_sample(pts, fts, intensities, mask, boxes, box_ind, resize):
+def pc_crop_and_sample(pts, fts, intensities, mask, boxes, box_ind, resize, index=None):
     """
     input:
         pts:    (B, P, 3), [x, y, z],   float32
@@ -59,11 +59,12 @@ def pc_crop_and_sample(pts, fts, intensities, mask, boxes, box_ind, resize):
     crop_mask = torch.empty((N, R), dtype=torch.bool, device=dev)
     crop_ind = torch.empty((N, R), dtype=torch.int32, device=dev)
     non_empty = torch.empty((N,), dtype=torch.bool, device=dev)
+    ix = index.ptr_for(pts) if index is not None else None  # spatial.CloudIndex of pts (optional accelerator)
     with torch.cuda.device(dev):
-        rc = _lib.load().hf_pc_crop_and_sample(
+        rc = _lib.load().hf_pc_crop_and_sample_indexed(
             pts.data_ptr(), fts.data_ptr(), intensities.data_ptr(), mask.data_ptr(), boxes.data_ptr(),
             box_ind.data_ptr(), N, B, P, R, C, IC, crop_pts.data_ptr(), crop_fts.data_ptr(), crop_int.data_ptr(),
-            crop_mask.data_ptr(), crop_ind.data_ptr(), non_empty.data_ptr(), stream_ptr(dev))
+            crop_mask.data_ptr(), crop_ind.data_ptr(), non_empty.data_ptr(), ix, stream_ptr(dev))
     _lib.check(rc, "pc_crop_and_sample")
     return crop_pts, crop_fts, crop_int, crop_mask, crop_ind, non_empty
 

@@ -14,6 +14,8 @@
 //      row and streaming 128-bit stores, four rows in flight per warp.  Every output
 //      element is written exactly once (empty boxes are zero-filled here), so no memset
 //      pass over the 4.8 GB output is needed.
+#include <limits.h>
+
 #include "common.cuh"
 
 namespace hf {
@@ -27,18 +29,26 @@ __device__ __forceinline__ float dot3(float x1, float y1, float z1, float x2, fl
     return __fmaf_rn(z1, z2, __fmaf_rn(y1, y2, __fmul_rn(x1, x2)));
 }
 
-template <bool VEC4>
+// INDEXED: `index` is the cloud index of pts (hf_cloud_index_build: per scan the points sorted along a
+// Hilbert curve as {x, y, z, original index} in buckets of 32 with their bounding boxes, spatial.cu).  Phase 1
+// then tests the 512 bucket boxes of the scan against the RoI's (padded) bounding box and runs the exact
+// predicate only on the points of the few buckets that can touch it, instead of on all 16384 points — the
+// full scan is two thirds of the kernel's instructions.  Hits come out in curve order, so they are sorted
+// by original index (bitonic, shared memory) to give the same canonical slot order as the scan.
+template <bool VEC4, bool INDEXED>
 __global__ void __launch_bounds__(kCropThreads)
     crop_kernel(const float *__restrict__ pts_data, const float *__restrict__ fts_data,
                 const float *__restrict__ int_data, const uint8_t *__restrict__ mask_data,
                 const float *__restrict__ boxes, const int *__restrict__ box_ind, int npts, int resize,
                 int channel, int ichannel, float *__restrict__ crop_pts, float *__restrict__ crop_fts,
                 float *__restrict__ crop_int, uint8_t *__restrict__ crop_mask, int *__restrict__ crop_ind,
-                uint8_t *__restrict__ non_empty) {
+                uint8_t *__restrict__ non_empty, const float4 *__restrict__ ix_sorted, const float4 *__restrict__ ix_boxes,
+                int npad) {
     extern __shared__ int smem_i[];
     int *sel = smem_i;                // [resize] final source index per slot
     int *wlist = smem_i + resize;     // [kCropWarps][resize] per-warp ordered hits
     __shared__ int wcount[kCropWarps];
+    __shared__ int hcount;
 
     const int b = blockIdx.x;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -59,42 +69,118 @@ __global__ void __launch_bounds__(kCropThreads)
     const float *pts = pts_data + (size_t)bch * npts * 3;
 
     // ---- 1. select ----
-    const int per_warp = (npts + kCropWarps - 1) / kCropWarps;
-    const int lo = warp * per_warp;
-    const int hi = min(npts, lo + per_warp);
-    int *mine = wlist + warp * resize;
-    int cnt = 0;
-    for (int p0 = lo; p0 < hi && cnt < resize; p0 += 32) {
-        int p = p0 + lane;
-        bool in = false;
-        if (p < hi) {
-            float px = pts[(size_t)p * 3], py = pts[(size_t)p * 3 + 1], pz = pts[(size_t)p * 3 + 2];
-            float ud = dot3(ux, uy, uz, px, py, pz);
-            float vd = dot3(vx, vy, vz, px, py, pz);
-            float wd = dot3(wx, wy, wz, px, py, pz);
-            in = u_p1 < ud && ud < u_p2 && v_p1 < vd && vd < v_p4 && w_p1 < wd && wd < w_p5;
-        }
-        unsigned bal = __ballot_sync(0xffffffffu, in);
-        int pos = cnt + __popc(bal & ((1u << lane) - 1u));
-        if (in && pos < resize) mine[pos] = p;
-        cnt += __popc(bal);
-    }
-    if (cnt > resize) cnt = resize;
-    if (lane == 0) wcount[warp] = cnt;
-    __syncthreads();
-    int offset = 0, total = 0;
+    int count = -1;  // -1: not selected yet (no index, or more hits than the list holds)
+    if (INDEXED) {
+        int *hits = wlist;  // [kCropWarps * resize] original indices, any order
+        const int hcap = kCropWarps * resize;
+        if (t == 0) hcount = 0;
+        // bounding box of the 8 corners, padded far beyond the rounding of the dot products below
+        float lox = bx[0], hix = bx[0], loy = bx[8], hiy = bx[8], loz = bx[16], hiz = bx[16];
 #pragma unroll
-    for (int w = 0; w < kCropWarps; ++w) {
-        int c = wcount[w];
-        if (w < warp) offset += c;
-        total += c;
+        for (int k = 1; k < 8; ++k) {
+            lox = fminf(lox, bx[k]); hix = fmaxf(hix, bx[k]);
+            loy = fminf(loy, bx[8 + k]); hiy = fmaxf(hiy, bx[8 + k]);
+            loz = fminf(loz, bx[16 + k]); hiz = fmaxf(hiz, bx[16 + k]);
+        }
+        const float padx = 1e-2f + 1e-4f * fmaxf(fabsf(lox), fabsf(hix)), pady = 1e-2f + 1e-4f * fmaxf(fabsf(loy), fabsf(hiy)),
+                    padz = 1e-2f + 1e-4f * fmaxf(fabsf(loz), fabsf(hiz));
+        lox -= padx; hix += padx; loy -= pady; hiy += pady; loz -= padz; hiz += padz;
+        const int nb = npad >> 5;
+        const float4 *srt = ix_sorted + (size_t)bch * npad;
+        const float4 *bxs = ix_boxes + (size_t)bch * nb * 2;
+        __syncthreads();
+        for (int g0 = warp * 32; g0 < nb; g0 += kCropWarps * 32) {
+            const int cb = g0 + lane;
+            bool touch = false;
+            if (cb < nb) {
+                const float4 blo = __ldg(&bxs[cb * 2]), bhi = __ldg(&bxs[cb * 2 + 1]);
+                touch = blo.x <= hix && bhi.x >= lox && blo.y <= hiy && bhi.y >= loy && blo.z <= hiz && bhi.z >= loz;
+            }
+            unsigned todo = __ballot_sync(0xffffffffu, touch);
+            while (todo) {
+                const int l = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const float4 c = __ldg(&srt[(size_t)(g0 + l) * 32 + lane]);
+                const float ud = dot3(ux, uy, uz, c.x, c.y, c.z);
+                const float vd = dot3(vx, vy, vz, c.x, c.y, c.z);
+                const float wd = dot3(wx, wy, wz, c.x, c.y, c.z);
+                const bool in = u_p1 < ud && ud < u_p2 && v_p1 < vd && vd < v_p4 && w_p1 < wd && wd < w_p5;  // NaN padding fails
+                const unsigned bal = __ballot_sync(0xffffffffu, in);
+                if (bal) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(&hcount, __popc(bal));
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    const int pos = base + __popc(bal & ((1u << lane) - 1u));
+                    if (in && pos < hcap) hits[pos] = __float_as_int(c.w);
+                }
+            }
+        }
+        __syncthreads();
+        const int total = hcount;
+        if (total <= hcap) {
+            int P = 32;
+            while (P < total) P <<= 1;
+            for (int i = total + t; i < P; i += kCropThreads) hits[i] = INT_MAX;
+            __syncthreads();
+            for (int k2 = 2; k2 <= P; k2 <<= 1) {
+                for (int j = k2 >> 1; j > 0; j >>= 1) {
+                    for (int i = t; i < P; i += kCropThreads) {
+                        const int q = i ^ j;
+                        if (q > i) {
+                            const int x = hits[i], y = hits[q];
+                            if ((x > y) == ((i & k2) == 0)) {
+                                hits[i] = y;
+                                hits[q] = x;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+            count = min(total, resize);
+            for (int i = t; i < count; i += kCropThreads) sel[i] = hits[i];
+            __syncthreads();
+        }
     }
-    const int count = min(total, resize);
-    for (int i = lane; i < cnt; i += 32) {
-        int pos = offset + i;
-        if (pos < resize) sel[pos] = mine[i];
+    if (count < 0) {  // ordered scan of the whole scan (block uniform)
+        const int per_warp = (npts + kCropWarps - 1) / kCropWarps;
+        const int lo = warp * per_warp;
+        const int hi = min(npts, lo + per_warp);
+        int *mine = wlist + warp * resize;
+        int cnt = 0;
+        for (int p0 = lo; p0 < hi && cnt < resize; p0 += 32) {
+            int p = p0 + lane;
+            bool in = false;
+            if (p < hi) {
+                float px = pts[(size_t)p * 3], py = pts[(size_t)p * 3 + 1], pz = pts[(size_t)p * 3 + 2];
+                float ud = dot3(ux, uy, uz, px, py, pz);
+                float vd = dot3(vx, vy, vz, px, py, pz);
+                float wd = dot3(wx, wy, wz, px, py, pz);
+                in = u_p1 < ud && ud < u_p2 && v_p1 < vd && vd < v_p4 && w_p1 < wd && wd < w_p5;
+            }
+            unsigned bal = __ballot_sync(0xffffffffu, in);
+            int pos = cnt + __popc(bal & ((1u << lane) - 1u));
+            if (in && pos < resize) mine[pos] = p;
+            cnt += __popc(bal);
+        }
+        if (cnt > resize) cnt = resize;
+        __syncthreads();  // (indexed overflow: every warp is done with the hit list before it is reused)
+        if (lane == 0) wcount[warp] = cnt;
+        __syncthreads();
+        int offset = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kCropWarps; ++w) {
+            int c = wcount[w];
+            if (w < warp) offset += c;
+            total += c;
+        }
+        count = min(total, resize);
+        for (int i = lane; i < cnt; i += 32) {
+            int pos = offset + i;
+            if (pos < resize) sel[pos] = mine[i];
+        }
+        __syncthreads();
     }
-    __syncthreads();
     // ---- 2. pad ----
     if (count > 0) {
         for (int s = count + t; s < resize; s += kCropThreads) sel[s] = sel[(s - count) % count];
@@ -166,12 +252,32 @@ __global__ void __launch_bounds__(kCropThreads)
 }  // namespace
 }  // namespace hf
 
-extern "C" int hf_pc_crop_and_sample(const float *pts, const float *fts, const float *intensities,
-                                     const uint8_t *mask, const float *boxes, const int *box_ind, int num_boxes,
-                                     int batch, int npts, int resize, int channel, int intensity_channel,
-                                     float *crop_pts, float *crop_fts, float *crop_intensities,
-                                     uint8_t *crop_mask, int *crop_ind, uint8_t *non_empty_box,
-                                     hf_stream_t stream) {
+extern "C" size_t hf_cloud_index_bytes(int b, int n);
+
+namespace hf {
+namespace {
+template <bool VEC4, bool INDEXED>
+int launch_crop(size_t smem, cudaStream_t s, const float *pts, const float *fts, const float *intensities, const uint8_t *mask,
+                const float *boxes, const int *box_ind, int num_boxes, int npts, int resize, int channel,
+                int intensity_channel, float *crop_pts, float *crop_fts, float *crop_intensities, uint8_t *crop_mask,
+                int *crop_ind, uint8_t *non_empty_box, const float4 *ix_sorted, const float4 *ix_boxes, int npad) {
+    auto kern = crop_kernel<VEC4, INDEXED>;
+    if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
+                                               intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask, crop_ind,
+                                               non_empty_box, ix_sorted, ix_boxes, npad);
+    HF_LAUNCH_OK("crop_kernel");
+    return HF_OK;
+}
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_pc_crop_and_sample_indexed(const float *pts, const float *fts, const float *intensities,
+                                             const uint8_t *mask, const float *boxes, const int *box_ind, int num_boxes,
+                                             int batch, int npts, int resize, int channel, int intensity_channel,
+                                             float *crop_pts, float *crop_fts, float *crop_intensities,
+                                             uint8_t *crop_mask, int *crop_ind, uint8_t *non_empty_box,
+                                             const void *pts_index, hf_stream_t stream) {
     using namespace hf;
     HF_REQUIRE(resize > 0, "PcCropAndSample expects positive resize");
     HF_REQUIRE(batch >= 1 && npts > 0, "PcCropAndSample expects (B, P, 3) pts shape");
@@ -187,22 +293,29 @@ extern "C" int hf_pc_crop_and_sample(const float *pts, const float *fts, const f
         set_error("PcCropAndSample: resize=%d needs %zu bytes of shared memory (max 204800)", resize, smem);
         return HF_ERR_UNSUPPORTED;
     }
-    bool vec = (channel % 4 == 0) && ((reinterpret_cast<uintptr_t>(fts) & 15) == 0) &&
-               ((reinterpret_cast<uintptr_t>(crop_fts) & 15) == 0);
+    const bool vec = (channel % 4 == 0) && ((reinterpret_cast<uintptr_t>(fts) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(crop_fts) & 15) == 0);
+    // cloud index layout (spatial.cu:carve_index): [sorted: batch x npad float4][boxes: batch x npad/32 x 2 float4]
+    const bool indexed = pts_index && (reinterpret_cast<uintptr_t>(pts_index) & 15) == 0 && hf_cloud_index_bytes(batch, npts) != 0;
+    const int npad = (npts + 31) & ~31;
+    const float4 *ix_sorted = static_cast<const float4 *>(pts_index);
+    const float4 *ix_boxes = indexed ? ix_sorted + (size_t)batch * npad : nullptr;
     cudaStream_t s = (cudaStream_t)stream;
-    if (vec) {
-        auto kern = crop_kernel<true>;
-        if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
-                                                   intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask,
-                                                   crop_ind, non_empty_box);
-    } else {
-        auto kern = crop_kernel<false>;
-        if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
-                                                   intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask,
-                                                   crop_ind, non_empty_box);
-    }
-    HF_LAUNCH_OK("crop_kernel");
-    return HF_OK;
+#define HF_CROP_ARGS                                                                                                     \
+    smem, s, pts, fts, intensities, mask, boxes, box_ind, num_boxes, npts, resize, channel, intensity_channel, crop_pts, \
+        crop_fts, crop_intensities, crop_mask, crop_ind, non_empty_box, ix_sorted, ix_boxes, npad
+    if (vec) return indexed ? launch_crop<true, true>(HF_CROP_ARGS) : launch_crop<true, false>(HF_CROP_ARGS);
+    return indexed ? launch_crop<false, true>(HF_CROP_ARGS) : launch_crop<false, false>(HF_CROP_ARGS);
+#undef HF_CROP_ARGS
+}
+
+extern "C" int hf_pc_crop_and_sample(const float *pts, const float *fts, const float *intensities,
+                                     const uint8_t *mask, const float *boxes, const int *box_ind, int num_boxes,
+                                     int batch, int npts, int resize, int channel, int intensity_channel,
+                                     float *crop_pts, float *crop_fts, float *crop_intensities,
+                                     uint8_t *crop_mask, int *crop_ind, uint8_t *non_empty_box,
+                                     hf_stream_t stream) {
+    return hf_pc_crop_and_sample_indexed(pts, fts, intensities, mask, boxes, box_ind, num_boxes, batch, npts, resize, channel,
+                                         intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask, crop_ind,
+                                         non_empty_box, nullptr, stream);
 }

@@ -157,6 +157,15 @@ int hf_pc_crop_and_sample(const float *pts, const float *fts, const float *inten
                           int intensity_channel, float *crop_pts, float *crop_fts,
                           float *crop_intensities, uint8_t *crop_mask, int *crop_ind,
                           uint8_t *non_empty_box, hf_stream_t stream);
+/* The same with the cloud index of pts (hf_cloud_index_build(batch, npts, pts, ...)): the select phase
+ * tests bucket boxes against the RoI instead of every point.  Results are identical; a NULL index
+ * (or a scan too large to index) is the plain call. */
+int hf_pc_crop_and_sample_indexed(const float *pts, const float *fts, const float *intensities,
+                                  const uint8_t *mask, const float *boxes, const int *box_ind,
+                                  int num_boxes, int batch, int npts, int resize, int channel,
+                                  int intensity_channel, float *crop_pts, float *crop_fts,
+                                  float *crop_intensities, uint8_t *crop_mask, int *crop_ind,
+                                  uint8_t *non_empty_box, const void *pts_index, hf_stream_t stream);
 
 /* ---- bev_iou ------------------------------------------------------------ */
 /* Replaces compute_bev_iou_gpu(num_a,boxes_a,num_b,boxes_b,ans_overlap,ans_iou),

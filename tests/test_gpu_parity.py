@@ -400,6 +400,25 @@ def test_crop_matches_oracle(cuda, oracle, C, R):
         assert np.array_equal(N(g), w), name
 
 
+@pytest.mark.parametrize("C,R,P,nbox", [(288, 512, 16384, 40), (7, 64, 16384, 40), (4, 16, 16384, 40), (8, 128, 5000, 25),
+                                        (4, 32, 40000, 12), (12, 8, 70000, 6)])
+def test_crop_with_cloud_index_matches_oracle(cuda, oracle, C, R, P, nbox):
+    """The index only prunes the point-in-box scan: identical outputs, incl. boxes with more hits than the hit
+    list holds (R = 16 / 8: falls back to the ordered scan), clouds indexed in parts (40000) and clouds too
+    large to index (70000: plain path)."""
+    from heterofusionrcnn_b200 import spatial
+
+    args = crop_inputs(9 + C, 2, P, C, nbox)
+    want = oracle.pc_crop_and_sample(*args, R)
+    dargs = [T(a, cuda) for a in args]
+    ix = spatial.build_cloud_index(dargs[0])
+    assert (ix is None) == (P > 65536)
+    got = pc_crop_and_sample(*dargs, R, index=ix)
+    assert want[5].any()
+    for name, g, w in zip(["crop_pts", "crop_fts", "crop_intensities", "crop_mask", "crop_ind", "non_empty_box"], got, want):
+        assert np.array_equal(N(g), w), name
+
+
 @needs_ref
 def test_crop_agrees_with_reference_kernel_up_to_its_race(cuda):
     """The reference assigns slots with a racing atomicInc: compare what is race-free
@@ -566,3 +585,29 @@ def test_three_nn_weights_matches_three_nn_plus_reference_formula(cuda, oracle, 
     want = synthetic.fp_weights(wd)
     assert close(N(w), want)
     assert np.allclose(N(w).sum(axis=2), 1.0, atol=1e-6)
+
+
+# ---------------------------------------------------------------- the chain as a captured CUDA graph
+def test_chain_graph_replay_equals_eager_issue(cuda):
+    """chain.ChainGraph (one cudaGraphLaunch per step, what bench.py times) gives the results of eager issue."""
+    from heterofusionrcnn_b200 import chain
+
+    cfg = chain.ChainConfig().scaled(4096)
+    cfg.crop_boxes, cfg.crop_resize, cfg.crop_channels, cfg.nms_boxes = 32, 64, 32, 800
+    dev = chain.to_device(chain.make_host_inputs(cfg, batch=3, seed=11), cuda)
+    eager = chain.run_chain(dev, cfg)
+    torch.cuda.synchronize()
+    graph = chain.ChainGraph(dev, cfg)
+    assert graph.launches == chain.chain_launches(cfg)
+    for _ in range(2):
+        res = graph.replay()
+    torch.cuda.synchronize()
+    for l in range(4):
+        assert torch.equal(res["fps_idx"][l], eager["fps_idx"][l])
+        for g, e in zip(res["sa%d" % (l + 1)], eager["sa%d" % (l + 1)]):
+            assert torch.equal(g, e)
+        for g, e in zip(res["fp%d" % (l + 1)], eager["fp%d" % (l + 1)]):
+            assert torch.equal(g, e)
+    for g, e in zip(res["crop"], eager["crop"]):
+        assert torch.equal(g, e)
+    assert torch.equal(res["nms_keep"], eager["nms_keep"]) and torch.equal(res["nms_num"], eager["nms_num"])
