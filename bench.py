@@ -579,7 +579,14 @@ def ncu_traffic(launch):
     if launch not in NCU_KERNEL_OF:
         return None
     frag, grid = NCU_KERNEL_OF[launch]
-    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_ncu_full_*_summary.csv")))
+    import re
+
+    def version(path):  # r<round>_ncu_full_v<pass>_summary.csv -> (round, pass): numeric, not lexicographic
+        m = re.search(r"r(\d+)_ncu_full_v(\d+)_summary", os.path.basename(path))
+        return (int(m.group(1)), int(m.group(2))) if m else (0, 0)
+
+    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_ncu_full_*_summary.csv")),
+                   key=version)
     if not files:
         return None
     rows = list(csv.reader(open(files[-1])))
