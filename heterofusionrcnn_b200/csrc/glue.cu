@@ -31,6 +31,29 @@ __global__ void boxes3d_to_bev_kernel(long long total, const float *__restrict__
     }
 }
 
+// box_8c_encoder.py:101-184 (tf_box_3d_to_box_8co) after the proposal expansion of rcnn_model.py:462-476:
+// corners (N,3,8), rows x/y/z, columns P1..P8; x' = cos*x + sin*z, z' = -sin*x + cos*z about the box origin.
+__global__ void boxes3d_to_corners_kernel(long long num, const float *__restrict__ b3, float expand,
+                                          float *__restrict__ corners) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < num * 8; i += (long long)gridDim.x * blockDim.x) {
+        const long long bx = i >> 3;
+        const int k = (int)(i & 7);
+        const float *p = b3 + bx * 7;
+        const float e2 = __fmul_rn(2.f, expand);
+        const float l = __fadd_rn(p[3], e2), w = __fadd_rn(p[4], e2), h = __fadd_rn(p[5], e2);
+        const float cy = __fadd_rn(p[1], expand);
+        const float hl = l / 2, hw = w / 2;
+        const float xc = (k & 2) ? -hl : hl;                      // P1 P2 +, P3 P4 -
+        const float zc = ((k & 3) == 1 || (k & 3) == 2) ? -hw : hw;  // P1 +, P2 -, P3 -, P4 +
+        const float yc = (k & 4) ? -h : 0.f;
+        const float c = cosf(p[6]), sn = sinf(p[6]);
+        float *o = corners + bx * 24;
+        o[k] = __fadd_rn(__fadd_rn(__fmul_rn(c, xc), __fmul_rn(sn, zc)), p[0]);
+        o[8 + k] = __fadd_rn(yc, cy);
+        o[16 + k] = __fadd_rn(__fadd_rn(__fmul_rn(-sn, xc), __fmul_rn(c, zc)), p[2]);
+    }
+}
+
 // iou3d holds the BEV overlap on entry (compute_iou.py:38-62).
 __global__ void box3d_iou_kernel(int na, int nb, const float *__restrict__ a, const float *__restrict__ b,
                                  float *__restrict__ iou3d) {
@@ -110,6 +133,17 @@ extern "C" int hf_boxes3d_to_bev(long long num, const float *boxes3d, float *box
     if (num == 0) return HF_OK;
     boxes3d_to_bev_kernel<<<grid_for(num), 256, 0, (cudaStream_t)stream>>>(num, boxes3d, nullptr, 1, boxes_bev);
     HF_LAUNCH_OK("boxes3d_to_bev_kernel");
+    return HF_OK;
+}
+
+extern "C" int hf_boxes3d_to_corners(long long num, const float *boxes3d, float expand_length, float *corners,
+                                     hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(num >= 0, "boxes3d_to_corners expects (N,7) boxes3d");
+    HF_REQUIRE(num == 0 || (boxes3d && corners), "boxes3d_to_corners: null pointer");
+    if (num == 0) return HF_OK;
+    boxes3d_to_corners_kernel<<<grid_for(num * 8), 256, 0, (cudaStream_t)stream>>>(num, boxes3d, expand_length, corners);
+    HF_LAUNCH_OK("boxes3d_to_corners_kernel");
     return HF_OK;
 }
 

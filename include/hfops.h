@@ -260,6 +260,11 @@ int hf_select_top_k(int b, int n, int m, int k, const float *dist, int *outi, fl
 /* ---- glue of hf/core/compute_iou.py --------- */
 /* boxes3d_to_bev_tf, compute_iou.py:7-20: (N,7) [x,y,z,l,w,h,ry] -> (N,5) [x-l/2, z-w/2, x+l/2, z+w/2, ry]. */
 int hf_boxes3d_to_bev(long long num, const float *boxes3d, float *boxes_bev, hf_stream_t stream);
+/* tf_box_3d_to_box_8co, hf/core/box_8c_encoder.py:101-184, with the proposal expansion its caller applies
+ * first (hf/core/models/rcnn_model.py:462-476: y += e, l/w/h += 2e; e = 0 for the plain conversion):
+ * boxes3d (N,7) -> corners (N,3,8), the box input of hf_pc_crop_and_sample. */
+int hf_boxes3d_to_corners(long long num, const float *boxes3d, float expand_length, float *corners,
+                          hf_stream_t stream);
 /* box3d_iou_tf, compute_iou.py:23-64: boxes_a (N,7), boxes_b (M,7) -> iou_3d (N,M), iou_2d (N,M)
  * (BEV overlap x height overlap over the union of the volumes, clipped at 1e-7). */
 size_t hf_box3d_iou_workspace_bytes(int num_a, int num_b);

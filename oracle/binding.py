@@ -357,3 +357,20 @@ def oriented_nms_scored(boxes3d, scores, thresh):
     order = np.argsort(-np.asarray(scores, np.float32), kind="stable").astype(np.int32)
     keep_sorted = oriented_nms(boxes3d_to_bev(np.asarray(boxes3d, np.float32)[order]), thresh)
     return order[keep_sorted]
+
+
+def box_3d_to_box_8co(boxes_3d, expand_length=0.0):
+    """hf/core/box_8c_encoder.py:101-184 after the expansion of rcnn_model.py:462-476 -> (N,3,8), float32."""
+    b = np.asarray(boxes_3d, np.float32).copy()
+    e = np.float32(expand_length)
+    b[:, 1] += e
+    b[:, 3:6] += np.float32(2) * e
+    hl, hw, h = b[:, 3] / np.float32(2), b[:, 4] / np.float32(2), b[:, 5]
+    sx = np.array([1, 1, -1, -1, 1, 1, -1, -1], np.float32)
+    sz = np.array([1, -1, -1, 1, 1, -1, -1, 1], np.float32)
+    top = np.array([0, 0, 0, 0, 1, 1, 1, 1], np.float32)
+    xc, zc, yc = hl[:, None] * sx[None], hw[:, None] * sz[None], -h[:, None] * top[None]
+    c, s = np.cos(b[:, 6]).astype(np.float32)[:, None], np.sin(b[:, 6]).astype(np.float32)[:, None]
+    x = c * xc + s * zc + b[:, 0:1]
+    z = -s * xc + c * zc + b[:, 2:3]
+    return np.stack([x, yc + b[:, 1:2], z], axis=1).astype(np.float32)

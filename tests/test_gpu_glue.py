@@ -57,3 +57,27 @@ def test_oriented_nms_tf_matches_oracle(cuda, oracle, s, n, thresh, ties):
     assert len(set(k0[:n0].tolist())) == n0 and (np.diff(scores[0][k0[:n0]]) <= 0).all()
     single = oriented_nms_tf(T(boxes[0], cuda), T(scores[0], cuda), thresh)
     assert torch.equal(single, keep[0])
+
+
+def test_box_3d_to_box_8co_feeds_the_crop(cuda, oracle):
+    """tf_box_3d_to_box_8co (+ the proposal expansion) against the oracle, and as the crop's box input."""
+    from heterofusionrcnn_b200.box_8c_encoder import tf_box_3d_to_box_8co
+    from heterofusionrcnn_b200.cropping.tf_cropping import pc_crop_and_sample
+
+    xyz, inten = synthetic.make_scans(5, 2, 8192)
+    b3 = np.concatenate([synthetic.make_boxes3d(70 + i, xyz[i], 20) for i in range(2)])
+    for e in (0.0, 1.0):
+        want = oracle.box_3d_to_box_8co(b3, e)
+        got = tf_box_3d_to_box_8co(T(b3, cuda), e)
+        assert got.shape == (40, 3, 8)
+        assert np.allclose(N(got), want, rtol=1e-5, atol=2e-5)
+    rng = np.random.default_rng(1)
+    fts = rng.standard_normal((2, 8192, 8)).astype(np.float32)
+    mask = rng.random((2, 8192)) < 0.3
+    box_ind = np.repeat(np.arange(2, dtype=np.int32), 20)
+    corners = tf_box_3d_to_box_8co(T(b3, cuda), 1.0)
+    got = pc_crop_and_sample(T(xyz, cuda), T(fts, cuda), T(inten, cuda), T(mask, cuda), corners, T(box_ind, cuda), 64)
+    want = oracle.pc_crop_and_sample(xyz, fts, inten, mask, N(corners), box_ind, 64)
+    for g, w in zip(got, want):
+        assert np.array_equal(N(g), w)
+    assert N(got[5]).all()

@@ -265,3 +265,21 @@ def test_oracle_knn_point_is_a_stable_top_k_of_the_squared_distances(oracle):
     # the reference's expanded form r2 - 2*x2.x1 + r1 agrees up to its cancellation error
     exp = (x2 ** 2).sum(-1)[:, :, None] - 2 * np.einsum("bmc,bnc->bmn", x2, x1) + (x1 ** 2).sum(-1)[:, None, :]
     assert np.allclose(np.sort(exp, axis=2)[:, :, :8], val, atol=1e-4)
+
+
+def test_oracle_box_8co_matches_the_reference_numpy_encoder(oracle):
+    """tests/golden/box8co_ref.npz = hf/core/box_8c_encoder.py:np_box_3d_to_box_8co run on seeded boxes
+    (tests/golden/make_golden_box8co.py); the oracle returns the (N,3,8) layout of tf_box_3d_to_box_8co."""
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "box8co_ref.npz"))
+    got = oracle.box_3d_to_box_8co(g["boxes"])
+    assert got.shape == (64, 3, 8)
+    assert np.allclose(np.transpose(got, (0, 2, 1)), g["corners_n83"], rtol=1e-5, atol=2e-5)
+    # the proposal expansion of rcnn_model.py:462-476 == the plain conversion of the expanded box
+    b = g["boxes"].copy()
+    b[:, 1] += 0.5
+    b[:, 3:6] += 1.0
+    assert np.array_equal(oracle.box_3d_to_box_8co(g["boxes"], 0.5), oracle.box_3d_to_box_8co(b))
+    # and the synthetic generator of the bench uses the same corner order
+    from heterofusionrcnn_b200 import synthetic
+
+    assert np.allclose(synthetic.boxes3d_to_corners(g["boxes"]), got, rtol=1e-5, atol=2e-5)
