@@ -163,6 +163,42 @@ __global__ void __launch_bounds__(kGpThreads)
     }
 }
 
+// sample_and_group's tail in one pass (hf/core/feature_extractors/pointnet_util.py:49-60): out row r =
+// [xyz[idx[r]] - new_xyz[r / nsample], points[idx[r]]], width 3 + c (c = 0: the translated xyz only).
+// The reference runs two group_point ops, a tile + subtract and a concat: four passes over the big tensor.
+// One warp per output row, four rows in flight; rows are 3 + c floats, so accesses are 32-bit, coalesced.
+__global__ void __launch_bounds__(kGpThreads)
+    group_concat_kernel(int n, int c, int rows, int nsample, const float *__restrict__ xyz, const float *__restrict__ points,
+                        const int *__restrict__ idx, const float *__restrict__ new_xyz, float *__restrict__ out) {
+    const int scene = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * kGpThreads + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * kGpThreads) >> 5;
+    const int width = 3 + c;
+    const float *x = xyz + (size_t)scene * n * 3;
+    const float *pts = points ? points + (size_t)scene * n * c : nullptr;
+    const int *ind = idx + (size_t)scene * rows;
+    const float *ctr = new_xyz + (size_t)scene * (rows / nsample) * 3;
+    float *o = out + (size_t)scene * rows * width;
+    for (int r0 = warp * 4; r0 < rows; r0 += nwarps * 4) {
+        int src[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) src[u] = (r0 + u < rows) ? __ldg(&ind[r0 + u]) : -1;
+        for (int j = lane; j < width; j += 32) {
+            float v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (src[u] < 0) continue;
+                if (j < 3) v[u] = __fsub_rn(__ldg(&x[(size_t)src[u] * 3 + j]), __ldg(&ctr[(size_t)((r0 + u) / nsample) * 3 + j]));
+                else v[u] = __ldg(&pts[(size_t)src[u] * c + (j - 3)]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (src[u] >= 0) o[(size_t)(r0 + u) * width + j] = v[u];
+        }
+    }
+}
+
 }  // namespace
 
 // Smallest float t with sqrtf(t) >= radius; d2 < t  <=>  sqrtf(d2) < radius for d2 >= 0.
@@ -237,5 +273,24 @@ extern "C" int hf_group_point(int b, int n, int c, int m, int nsample, const flo
         group_point_scalar_kernel<<<dim3((unsigned)blocks, b), kGpThreads, 0, s>>>(n, c, rows, points, idx, out);
         HF_LAUNCH_OK("group_point_scalar_kernel");
     }
+    return HF_OK;
+}
+
+extern "C" int hf_group_point_concat(int b, int n, int c, int m, int nsample, const float *xyz, const float *points,
+                                     const int *idx, const float *new_xyz, float *out, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(b >= 0 && n >= 1 && c >= 0 && m >= 0 && nsample >= 1,
+               "GroupPoint expects (batch_size, num_points, channel) points shape");
+    HF_REQUIRE(b <= 65535, "GroupPoint: batch_size > 65535 not supported");
+    HF_REQUIRE((long long)m * nsample < (1ll << 31), "GroupPoint: npoint*nsample must fit int32");
+    const int rows = m * nsample;
+    if (b == 0 || rows == 0) return HF_OK;
+    HF_REQUIRE(xyz && idx && new_xyz && out && (c == 0 || points), "GroupPoint: null pointer");
+    int blocks = (rows + 4 * (kGpThreads / 32) - 1) / (4 * (kGpThreads / 32));
+    const int cap = (num_sms() * 8 + b - 1) / b;
+    if (blocks > cap) blocks = cap;
+    group_concat_kernel<<<dim3(blocks, b), kGpThreads, 0, (cudaStream_t)stream>>>(n, c, rows, nsample, xyz, c ? points : nullptr,
+                                                                                   idx, new_xyz, out);
+    HF_LAUNCH_OK("group_concat_kernel");
     return HF_OK;
 }

@@ -163,3 +163,34 @@ def knn_point(k, xyz1, xyz2):
                               ws.data_ptr() if ws is not None else None, ws_bytes, stream_ptr(xyz1.device))
     _lib.check(rc, "knn_point")
     return val, idx
+
+
+def group_point_concat(xyz, points, idx, new_xyz):
+    """The tail of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49-60) as one kernel:
+
+        grouped_xyz = group_point(xyz, idx) - new_xyz[:, :, None, :]
+        new_points  = concat([grouped_xyz, group_point(points, idx)], -1)     (points None: grouped_xyz)
+
+    xyz (b,n,3), points (b,n,c) or None, idx (b,m,nsample) int32, new_xyz (b,m,3) -> (b,m,nsample,3+c).
+    """
+    xyz = dev_tensor(xyz, torch.float32, "xyz")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    new_xyz = dev_tensor(new_xyz, torch.float32, "new_xyz")
+    require(xyz.dim() == 3 and xyz.shape[2] == 3, "GroupPoint expects (batch_size, num_points, 3) xyz shape")
+    b, n = xyz.shape[0], xyz.shape[1]
+    require(idx.dim() == 3 and idx.shape[0] == b, "GroupPoint expects (batch_size, npoints, nsample) idx shape")
+    m, nsample = idx.shape[1], idx.shape[2]
+    require(nsample >= 1, "GroupPoint expects (batch_size, npoints, nsample) idx shape")
+    require(tuple(new_xyz.shape) == (b, m, 3), "GroupPoint expects (batch_size, npoints, 3) new_xyz shape")
+    c = 0
+    if points is not None:
+        points = dev_tensor(points, torch.float32, "points")
+        require(points.dim() == 3 and points.shape[0] == b and points.shape[1] == n,
+                "GroupPoint expects (batch_size, num_points, channel) points shape")
+        c = points.shape[2]
+    out = torch.empty((b, m, nsample, 3 + c), dtype=torch.float32, device=xyz.device)
+    with torch.cuda.device(xyz.device):
+        rc = _lib.load().hf_group_point_concat(b, n, c, m, nsample, xyz.data_ptr(), points.data_ptr() if c else None,
+                                               idx.data_ptr(), new_xyz.data_ptr(), out.data_ptr(), stream_ptr(xyz.device))
+    _lib.check(rc, "group_point_concat")
+    return out

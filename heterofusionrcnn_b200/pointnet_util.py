@@ -1,0 +1,54 @@
+"""Mirror of the operator part of hf/core/feature_extractors/pointnet_util.py: what the RPN / RCNN PointNet++
+set-abstraction and feature-propagation layers call before their MLPs (which are out of scope).
+
+Same function names, argument order and return values as the reference (:23-62, :286-308); eager on torch
+CUDA tensors.  Each function is a short sequence of libhfops calls with the glue fused into the kernels.
+"""
+from . import spatial
+from .grouping.tf_grouping import group_point, group_point_concat, knn_point, query_ball_point
+from .interpolate.tf_interpolate import three_interpolate, three_nn_weights
+from .sampling.tf_sampling import farthest_point_sample, gather_point
+
+
+def sample_and_group(npoint, radius, nsample, xyz, points, knn=False, use_xyz=True):
+    """
+    Input:
+        npoint: int32
+        radius: float32
+        nsample: int32
+        xyz: (batch_size, ndataset, 3) tensor
+        points: (batch_size, ndataset, channel) tensor, if None will just use xyz as points
+        knn: bool, if True use kNN instead of radius search
+        use_xyz: bool, if True concat XYZ with local point features, otherwise just use point features
+    Output:
+        new_xyz: (batch_size, npoint, 3) tensor
+        new_points: (batch_size, npoint, nsample, 3+channel) tensor
+        idx: (batch_size, npoint, nsample) tensor, indices of local points as in ndataset points
+        grouped_xyz: (batch_size, npoint, nsample, 3) tensor, normalized point XYZs
+            (subtracted by seed point XYZ) in local regions
+
+    Reference: hf/core/feature_extractors/pointnet_util.py:23-62.
+    """
+    new_xyz = gather_point(xyz, farthest_point_sample(npoint, xyz))
+    if knn:
+        _, idx = knn_point(nsample, xyz, new_xyz)
+    else:
+        idx, _ = query_ball_point(radius, nsample, xyz, new_xyz)
+    if points is not None and use_xyz:
+        new_points = group_point_concat(xyz, points, idx, new_xyz)  # [grouped_xyz - new_xyz, grouped_points]
+        grouped_xyz = new_points[..., :3]
+    else:
+        grouped_xyz = group_point_concat(xyz, None, idx, new_xyz)
+        new_points = group_point(points, idx) if points is not None else grouped_xyz
+    return new_xyz, new_points, idx, grouped_xyz
+
+
+def interpolate_points(xyz1, xyz2, points2):
+    """The operator part of pointnet_fp_module (hf/core/feature_extractors/pointnet_util.py:301-308):
+    three_nn, inverse-distance weights (clamped at 1e-10), three_interpolate.
+    xyz1 (b,n1,3) dense, xyz2 (b,n2,3) sparse, points2 (b,n2,c) -> interpolated_points (b,n1,c)."""
+    ix = (None, None)
+    if spatial.applies(xyz1.shape[1], xyz2.shape[1]):
+        ix = (spatial.build_cloud_index(xyz1), spatial.build_cloud_index(xyz2))
+    _, idx, weight = three_nn_weights(xyz1, xyz2, index1=ix[0], index2=ix[1])
+    return three_interpolate(points2, idx, weight)

@@ -120,6 +120,12 @@ int hf_three_nn_weights(int b, int n, int m, const float *unknown, const float *
  * points (b,n,c), idx (b,m,nsample) -> out (b,m,nsample,c). */
 int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,
                    float *out, hf_stream_t stream);
+/* The tail of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49-60) in one pass:
+ * out (b,m,nsample,3+c) = concat(xyz[idx] - new_xyz (translation normalisation), points[idx]); c = 0 (points
+ * NULL) gives the translated grouped_xyz alone.  Replaces two group_point calls, a tile + subtract and a concat. */
+int hf_group_point_concat(int b, int n, int c, int m, int nsample, const float *xyz,
+                          const float *points, const int *idx, const float *new_xyz, float *out,
+                          hf_stream_t stream);
 
 /* ---- interpolate -------------------------------------------------------- */
 /* Replaces three_nn_gpu(b,n,m,unknown,known,dist2,idx), interpolate/tf_interpolate_g.cu:68.

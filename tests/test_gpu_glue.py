@@ -81,3 +81,34 @@ def test_box_3d_to_box_8co_feeds_the_crop(cuda, oracle):
     for g, w in zip(got, want):
         assert np.array_equal(N(g), w)
     assert N(got[5]).all()
+
+
+@pytest.mark.parametrize("knn,use_xyz,c", [(False, True, 5), (False, True, 96), (True, True, 7), (False, False, 4), (False, True, 0)])
+def test_sample_and_group_and_fp_interpolation(cuda, oracle, knn, use_xyz, c):
+    """pointnet_util.sample_and_group / interpolate_points against the same composition of oracle ops."""
+    from heterofusionrcnn_b200 import pointnet_util
+
+    rng = np.random.default_rng(c + 3)
+    b, n, m, ns, radius = 2, 4096, 512, 16, 1.0
+    xyz, _ = synthetic.make_scans(23, b, n)
+    pts = rng.standard_normal((b, n, c)).astype(np.float32) if c else None
+    new_xyz, new_points, idx, grouped_xyz = pointnet_util.sample_and_group(
+        m, radius, ns, T(xyz, cuda), T(pts, cuda) if c else None, knn=knn, use_xyz=use_xyz)
+    w_new = oracle.gather_point(xyz, oracle.farthest_point_sample(m, xyz))
+    w_idx = oracle.knn_point(ns, xyz, w_new)[1] if knn else oracle.query_ball_point(radius, ns, xyz, w_new)[0]
+    w_gxyz = oracle.group_point(xyz, w_idx) - w_new[:, :, None, :]
+    assert np.array_equal(N(new_xyz), w_new) and np.array_equal(N(idx), w_idx)
+    assert np.array_equal(N(grouped_xyz), w_gxyz)
+    if c == 0:
+        want = w_gxyz
+    elif use_xyz:
+        want = np.concatenate([w_gxyz, oracle.group_point(pts, w_idx)], axis=-1)
+    else:
+        want = oracle.group_point(pts, w_idx)
+    assert N(new_points).shape == want.shape and np.array_equal(N(new_points), want)
+    if c:
+        feats = rng.standard_normal((b, m, c)).astype(np.float32)
+        got = pointnet_util.interpolate_points(T(xyz, cuda), new_xyz, T(feats, cuda))
+        wd, wi = oracle.three_nn(xyz, w_new)
+        want = oracle.three_interpolate(feats, wi, synthetic.fp_weights(wd))
+        assert np.allclose(N(got), want, rtol=1e-5, atol=1e-6)
