@@ -611,3 +611,35 @@ def test_chain_graph_replay_equals_eager_issue(cuda):
     for g, e in zip(res["crop"], eager["crop"]):
         assert torch.equal(g, e)
     assert torch.equal(res["nms_keep"], eager["nms_keep"]) and torch.equal(res["nms_num"], eager["nms_num"])
+
+
+# ---------------------------------------------------------------- BASELINE configs[0]: a real KITTI scan
+def test_config0_real_kitti_scan(cuda, oracle):
+    """Fixture scan 000000 (reference loader + FOV filter + 16384 sampling, tests/golden/make_golden_kitti.py):
+    the SA / FP ops of level 1 against the oracle, bit-exact indices, and the unmodified reference kernels."""
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kitti_000000_16384.npz"))
+    xyz = g["xyz"][None]
+    x = T(xyz, cuda)
+    want_f = oracle.farthest_point_sample(4096, xyz)
+    fidx = farthest_point_sample(4096, x)
+    assert np.array_equal(N(fidx), want_f)
+    known = gather_point(x, fidx)
+    wk = oracle.gather_point(xyz, want_f)
+    assert np.array_equal(N(known), wk)
+    for r in (0.1, 0.5, 1.0):
+        wi, wc = oracle.query_ball_point(r, 32, xyz, wk)
+        gi, gc = query_ball_point(r, 32, x, known)
+        assert np.array_equal(N(gc), wc) and np.array_equal(N(gi), wi), r
+    wd, wi = oracle.three_nn(xyz, wk)
+    gd, gi = three_nn(x, known)
+    assert np.array_equal(N(gi), wi) and np.array_equal(N(gd), wd)
+    w = synthetic.fp_weights(wd)
+    feats = np.random.default_rng(0).standard_normal((1, 4096, 128)).astype(np.float32)
+    got = three_interpolate(T(feats, cuda), gi, T(w, cuda))
+    assert close(N(got), oracle.three_interpolate(feats, wi, w))
+    if _refcuda.available():
+        assert torch.equal(_refcuda.fps(4096, x), fidx)
+        rd, ri = _refcuda.three_nn(x, known)
+        assert torch.equal(ri, gi) and torch.equal(rd, gd)

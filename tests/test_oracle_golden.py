@@ -283,3 +283,35 @@ def test_oracle_box_8co_matches_the_reference_numpy_encoder(oracle):
     from heterofusionrcnn_b200 import synthetic
 
     assert np.allclose(synthetic.boxes3d_to_corners(g["boxes"]), got, rtol=1e-5, atol=2e-5)
+
+
+# ---------------------------------------------------------------- BASELINE configs[0]: a real KITTI scan
+def kitti_scan():
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kitti_000000_16384.npz"))
+    return g["xyz"][None], g["intensity"][None, :, None]
+
+
+def test_config0_real_kitti_scan_on_the_cpu_path(oracle):
+    """configs[0]: three_nn + three_interpolate (16384 <- 4096, C = 128) on fixture scan 000000, loaded and
+    FOV-filtered by the reference's own code (tests/golden/make_golden_kitti.py).  The oracle's interpolate and
+    ball query / group agree with the reference's CPU files compiled where they lie (oracle/_ref): indices bit for
+    bit, interpolated values within 1e-5."""
+    xyz, _ = kitti_scan()
+    assert xyz.shape == (1, 16384, 3) and 4.0 < xyz[0, :, 2].min() and xyz[0, :, 2].max() < 80.0
+    known = oracle.gather_point(xyz, oracle.farthest_point_sample(4096, xyz))
+    dist, idx = oracle.three_nn(xyz, known)
+    assert (np.diff(dist, axis=2) >= 0).all() and idx.max() < 4096
+    from heterofusionrcnn_b200 import synthetic
+
+    w = synthetic.fp_weights(dist)
+    feats = np.random.default_rng(0).standard_normal((1, 4096, 128)).astype(np.float32)
+    out = oracle.three_interpolate(feats, idx, w)
+    assert out.shape == (1, 16384, 128) and np.isfinite(out).all()
+    if not oracle.ref_available("libref_interpolate_cpu.so"):
+        pytest.skip("oracle/_ref not built")
+    # floats: 1e-5 relative (the oracle spells the FMA order nvcc gives the reference KERNEL; g++ does not contract)
+    assert np.allclose(out, oracle.ref_interpolate_cpu(feats, idx, w), rtol=1e-5, atol=1e-6)
+    gi, gc = oracle.query_ball_point(0.5, 32, xyz, known)
+    ri = oracle.ref_query_ball_point_cpu(0.5, 32, xyz, known)  # the prototype returns indices only
+    assert np.array_equal(gi[gc > 0], ri[gc > 0])
+    assert np.array_equal(oracle.group_point(xyz, gi), oracle.ref_group_point_cpu(xyz, gi))
