@@ -88,3 +88,30 @@ def gather_point_grad(inp, idx, out_g):
                                       stream_ptr(inp.device))
     _lib.check(rc, "gather_point_grad")
     return inp_g
+
+
+def prob_sample(inp, inpr):
+    """
+input:
+    batch_size * ncategory float32
+    batch_size * npoints   float32
+returns:
+    batch_size * npoints   int32
+
+    Reference: sampling/tf_sampling.py:18-27, op checks sampling/tf_sampling.cpp:68-93.  inp holds
+    (unnormalised) category weights, inpr uniform random numbers in [0, 1); the result is the index
+    the reference's binary search finds in its float32 prefix sum (same rounding, bit for bit).
+    """
+    inp = dev_tensor(inp, torch.float32, "inp")
+    inpr = dev_tensor(inpr, torch.float32, "inpr")
+    require(inp.dim() == 2 and inp.shape[1] >= 1, "ProbSample expects (batch_size,num_choices) inp shape")
+    b, n = inp.shape
+    require(inpr.dim() == 2 and inpr.shape[0] == b, "ProbSample expects (batch_size,num_points) inpr shape")
+    m = inpr.shape[1]
+    out = torch.empty((b, m), dtype=torch.int32, device=inp.device)
+    temp = torch.empty((b, n), dtype=torch.float32, device=inp.device)
+    with torch.cuda.device(inp.device):
+        rc = _lib.load().hf_prob_sample(b, n, m, inp.data_ptr(), inpr.data_ptr(), temp.data_ptr(), out.data_ptr(),
+                                        stream_ptr(inp.device))
+    _lib.check(rc, "prob_sample")
+    return out

@@ -66,6 +66,12 @@ void hf_fps_set_variant(int algo, int warps, int buckets_per_warp);
  * inp (b,n,3), idx (b,m) -> out (b,m,3). */
 int hf_gather_point(int b, int n, int m, const float *inp, const int *idx, float *out,
                     hf_stream_t stream);
+/* Replaces probsampleLauncher(b,n,m,inp_p,inp_r,temp,out), sampling/tf_sampling_g.cu:198-201 (and
+ * cumsumLauncher, :194-196: temp (b,n) receives the float32 prefix sums, same rounding as the reference's
+ * scan tree; m = 0 computes only them).  inp_p (b,n) weights, inp_r (b,m) uniform numbers in [0,1)
+ * -> out (b,m): smallest index whose prefix sum is >= r * total. */
+int hf_prob_sample(int b, int n, int m, const float *inp_p, const float *inp_r, float *temp, int *out,
+                   hf_stream_t stream);
 
 /* ---- grouping ----------------------------------------------------------- */
 /* Replaces queryBallPointLauncher(b,n,m,radius,nsample,xyz1,xyz2,idx,pts_cnt),

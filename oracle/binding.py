@@ -374,3 +374,21 @@ def box_3d_to_box_8co(boxes_3d, expand_length=0.0):
     x = c * xc + s * zc + b[:, 0:1]
     z = -s * xc + c * zc + b[:, 2:3]
     return np.stack([x, yc + b[:, 1:2], z], axis=1).astype(np.float32)
+
+
+def cumsum(inp):
+    inp = _c(inp, np.float32)
+    b, n = inp.shape
+    out = np.zeros((b, n), np.float32)
+    lib().hf_oracle_cumsum(_i(b), _i(n), _ptr(inp), _ptr(out))
+    return out
+
+
+def prob_sample(inp, inpr):
+    """sampling/tf_sampling.py:18-27: inp (b,ncategory) weights, inpr (b,npoints) uniform numbers -> (b,npoints) int32."""
+    inp, inpr = _c(inp, np.float32), _c(inpr, np.float32)
+    b, n = inp.shape
+    m = inpr.shape[1]
+    out = np.zeros((b, m), np.int32)
+    lib().hf_oracle_prob_sample(_i(b), _i(n), _i(m), _ptr(inp), _ptr(inpr), _ptr(out))
+    return out

@@ -726,4 +726,72 @@ void hf_oracle_knn_point(int b, int n, int m, int k, const float *xyz1, const fl
     });
 }
 
+// ---------------------------------------------------------------------------
+// prob_sample: sampling/tf_sampling_g.cu:7-104,198-201.
+// The sampled index is the result of a binary search in a FLOAT prefix sum, so the prefix sum's
+// association order is part of the contract.  cumsumKernel's order, restated serially: rows are cut
+// into chunks of 8192; inside a chunk, quads (a,b,c,d) become (a, a+b, c+(a+b), (c+d)+(a+b)); the quad
+// totals go through a work-efficient up-sweep / down-sweep scan (tree bounds exactly as :46-65); element
+// = (quad prefix + scanned total of the quads before it) + running sum; the running sum is carried
+// between chunks with a two-float compensated add (:79-82).
+// ---------------------------------------------------------------------------
+static void oracle_cumsum_row(int n, const float *inp, float *out) {
+    const int CH = 8192;
+    std::vector<float> q(CH), tot(CH / 4);
+    float running = 0.f, running2 = 0.f;
+    for (int j = 0; j < n; j += CH) {
+        const int ni = std::min(n - j, CH), n24 = (ni + 3) & ~3, n2 = n24 >> 2;
+        for (int k = 0; k < ni; k += 4) {
+            if (k + 3 < ni) {
+                const float a = inp[j + k], b = inp[j + k + 1], c = inp[j + k + 2], d = inp[j + k + 3];
+                const float ab = b + a, cd = d + c;
+                q[k] = a; q[k + 1] = ab; q[k + 2] = c + ab; q[k + 3] = cd + ab;
+                tot[k >> 2] = q[k + 3];
+            } else {
+                float v = 0.f;
+                for (int k2 = k; k2 < ni; ++k2) { v += inp[j + k2]; q[k2] = v; }
+                for (int k2 = ni; k2 < n24; ++k2) q[k2] = v;
+                tot[k >> 2] = v;
+            }
+        }
+        int u = 0;
+        for (; (2 << u) <= n2; ++u)
+            for (int k = 0; k < (n2 >> (u + 1)); ++k) tot[(((k << 1) + 2) << u) - 1] += tot[(((k << 1) + 1) << u) - 1];
+        for (--u; u >= 0; --u)
+            for (int k = 0; k < ((n2 - (1 << u)) >> (u + 1)); ++k) tot[(((k << 1) + 3) << u) - 1] += tot[(((k << 1) + 2) << u) - 1];
+        for (int k = 0; k < ni; ++k) {
+            float v = q[k];
+            if ((k >> 2) != 0) v += tot[(k >> 2) - 1];
+            out[j + k] = v + running;
+        }
+        volatile float t = tot[n2 - 1] + running2;
+        volatile float r2 = running + t;
+        volatile float diff = r2 - running;
+        running2 = t - diff;
+        running = r2;
+    }
+}
+
+void hf_oracle_cumsum(int b, int n, const float *inp, float *out) {
+    for (int i = 0; i < b; ++i) oracle_cumsum_row(n, inp + (int64_t)i * n, out + (int64_t)i * n);
+}
+
+// binarysearchKernel, tf_sampling_g.cu:86-104.  inp_p (b,n) weights, inp_r (b,m) uniform numbers -> out (b,m).
+void hf_oracle_prob_sample(int b, int n, int m, const float *inp_p, const float *inp_r, int *out) {
+    std::vector<float> cs(n);
+    int base = 1;
+    while (base < n) base <<= 1;
+    for (int64_t i = 0; i < b; ++i) {
+        oracle_cumsum_row(n, inp_p + i * n, cs.data());
+        for (int64_t j = 0; j < m; ++j) {
+            volatile float qv = inp_r[i * m + j] * cs[n - 1];
+            const float q = qv;
+            int r = n - 1;
+            for (int k = base; k >= 1; k >>= 1)
+                if (r >= k && cs[r - k] >= q) r -= k;
+            out[i * m + j] = r;
+        }
+    }
+}
+
 }  // extern "C"

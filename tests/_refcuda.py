@@ -190,3 +190,14 @@ def select_top_k(k, dist):
     _fn("selectionSortLauncher")(_i(b), _i(n), _i(m), _i(int(k)), _d(dist), _d(outi), _d(out))
     torch.cuda.synchronize()
     return outi, out
+
+
+def prob_sample(inp, inpr):
+    b, n = inp.shape
+    m = inpr.shape[1]
+    temp = torch.zeros((b, n), dtype=torch.float32, device=inp.device)
+    out = torch.zeros((b, m), dtype=torch.int32, device=inp.device)
+    torch.cuda.synchronize()
+    _fn("probsampleLauncher")(_i(b), _i(n), _i(m), _d(inp), _d(inpr), _d(temp), _d(out))
+    torch.cuda.synchronize()
+    return out, temp

@@ -82,3 +82,25 @@ def test_select_top_k_of_the_distance_matrix_agrees_with_knn_point(cuda):
     oi, _ = select_top_k(8, d)
     _, ki = knn_point(8, x1, x2)
     assert (oi[:, :, :8] == ki).float().mean().item() > 0.999  # the torch matrix rounds differently from sqdist
+
+
+# ---------------------------------------------------------------- prob_sample
+@pytest.mark.parametrize("b,n,m", [(2, 40, 1000), (3, 8192, 4096), (2, 20000, 5000), (1, 8195, 300), (2, 1, 10), (1, 3, 7),
+                                   (1, 100000, 20000)])
+def test_prob_sample_matches_oracle_and_reference_kernel(cuda, oracle, b, n, m):
+    """The sampled indices depend on the rounding of the float32 prefix sum: bit-exact against the oracle's
+    restatement of the reference's scan tree and against the unmodified reference kernel on the same B200."""
+    from heterofusionrcnn_b200.sampling.tf_sampling import prob_sample
+
+    rng = np.random.default_rng(n + m)
+    w = rng.random((b, n)).astype(np.float32)
+    w[:, ::7] = 0.0  # zero-weight categories: runs of equal prefix sums
+    r = rng.random((b, m)).astype(np.float32)
+    r[:, 0] = 0.0
+    want = oracle.prob_sample(w, r)
+    got = prob_sample(T(w, cuda), T(r, cuda))
+    assert got.dtype == torch.int32 and np.array_equal(N(got), want)
+    if _refcuda.available():
+        ref, ref_cs = _refcuda.prob_sample(T(w, cuda), T(r, cuda))
+        assert torch.equal(got, ref)
+        assert np.array_equal(N(ref_cs), oracle.cumsum(w))

@@ -315,3 +315,19 @@ def test_config0_real_kitti_scan_on_the_cpu_path(oracle):
     ri = oracle.ref_query_ball_point_cpu(0.5, 32, xyz, known)  # the prototype returns indices only
     assert np.array_equal(gi[gc > 0], ri[gc > 0])
     assert np.array_equal(oracle.group_point(xyz, gi), oracle.ref_group_point_cpu(xyz, gi))
+
+
+def test_oracle_prob_sample_is_an_inverse_cdf_lookup(oracle):
+    """prob_sample = lower bound of r * total in the float32 prefix sum (tf_sampling_g.cu:86-104); the prefix sum
+    follows the reference's scan tree (pinned against the reference kernel in the GPU tests) and agrees with a
+    float64 cumsum to float32 accuracy; zero-weight categories are never drawn for r > 0."""
+    rng = np.random.default_rng(4)
+    w = rng.random((2, 9000)).astype(np.float32)
+    w[:, ::5] = 0.0
+    r = rng.random((2, 3000)).astype(np.float32)
+    cs = oracle.cumsum(w)
+    assert np.allclose(cs, np.cumsum(w.astype(np.float64), axis=1), rtol=2e-6)
+    got = oracle.prob_sample(w, r)
+    for i in range(2):
+        assert np.array_equal(got[i], np.searchsorted(cs[i], r[i] * cs[i, -1], side="left"))
+        assert (w[i, got[i][r[i] > 0]] > 0).all()
