@@ -526,6 +526,8 @@ def run_b200(args):
     top_fps = max((o for o in own if o["launch"].startswith("fps/")), key=lambda o: o["ms"])
     top_hbm = max((o for o in own if o["bound"] == "hbm"), key=lambda o: o["ms"])
 
+    step_bytes = sum(o["bytes"] * o["per_step"] for o in ops)
+
     def roof(o):
         default_cfg = args.batch == 16 and args.points == 16384 and not args.msg_radii
         return {"kernel": o["launch"], "bound": o["bound"], "achieved": o["achieved"], "peak": o["peak"],
@@ -534,7 +536,10 @@ def run_b200(args):
                 "ms_per_launch_alone": o["ms_alone"], "frac_alone": o["frac_alone"],
                 "algorithmic_bytes": o["bytes"], "algorithmic_flops": o["flops"],
                 "peak_source": hbm_src if o["bound"] == "hbm" else "derived 148 SM x 128 lanes x 2 x 1.965 GHz (not measured)",
-                "share_of_step": o["share_of_step"]}
+                "share_of_step": o["share_of_step"],
+                "note": "frac: this launch inside an overlapped step (issued eagerly right after the timed graph replays), where "
+                        "it shares the GPU with the other 12 streams - the crop at the lowest priority; frac_alone: the same "
+                        "launch with the GPU to itself"}
 
     line = {
         "metric": METRIC, "value": args.batch * n_gpus * args.steps / (ms / 1e3), "unit": UNIT, "n_gpus": n_gpus,
@@ -544,6 +549,9 @@ def run_b200(args):
         # `roofline` = the dominant HBM-bound kernel (the RoI crop writes 4.9 of the step's 5.6 GB); the other
         # quarter of the step is the level-1 FPS, a latency chain with no HBM traffic: `roofline_fps`
         "roofline": roof(top_hbm), "roofline_fps": roof(top_fps),
+        # the whole step against the HBM roofline: algorithmic bytes of every launch of the step / step time
+        "roofline_step": {"bound": "hbm", "algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms / args.steps) / 1e6,
+                          "peak": hbm_peak, "unit": "GB/s", "frac": step_bytes / (ms / args.steps) / 1e6 / hbm_peak},
         "roofline_ops": [{k: o[k] for k in ("launch", "bound", "ms", "ms_alone", "per_step", "achieved", "unit", "frac",
                                             "frac_alone", "share_of_step")} for o in ops],
         "serial_ms_per_step": serial_step_ms,
