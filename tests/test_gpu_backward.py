@@ -153,3 +153,44 @@ def test_gradients_match_reference_kernels(cuda):
     abs_sum = N(_refcuda.three_interpolate_grad_channel_first(known, nidx, w, g_cf.abs()))
     assert reorder_close(N(three_interpolate_grad_channel_first(known, nidx, w, g_cf)),
                          N(_refcuda.three_interpolate_grad_channel_first(known, nidx, w, g_cf)), abs_sum)
+
+
+# ---------------------------------------------------------------- autograd pairing (the reference's RegisterGradient)
+def test_autograd_functions_use_the_registered_gradients(cuda, oracle):
+    """loss = <forward(x), g>  =>  x.grad == grad_op(g): the torch.autograd pairing of heterofusionrcnn_b200.autograd
+    reproduces tf.RegisterGradient of the reference (points / fts get gradients, indices do not)."""
+    from heterofusionrcnn_b200 import autograd as A
+    from test_gpu_parity import crop_inputs
+
+    rng = np.random.default_rng(8)
+    b, n, m, ns, c = 2, 1024, 256, 16, 32
+    xyz, _ = synthetic.make_scans(3, b, n)
+    x = T(xyz, cuda)
+    fidx = farthest_point_sample(m, x)
+    new_xyz = gather_point(x, fidx)
+    idx, _ = query_ball_point(1.0, ns, x, new_xyz)
+
+    pts = T(rng.standard_normal((b, n, c)).astype(np.float32), cuda).requires_grad_(True)
+    g = T(rng.standard_normal((b, m, ns, c)).astype(np.float32), cuda)
+    (A.group_point(pts, idx) * g).sum().backward()
+    assert np.array_equal(N(pts.grad), oracle.group_point_grad(N(pts), N(idx), N(g)))
+
+    xr = x.clone().requires_grad_(True)
+    g3 = T(rng.standard_normal((b, m, 3)).astype(np.float32), cuda)
+    (A.gather_point(xr, fidx) * g3).sum().backward()
+    assert np.array_equal(N(xr.grad), oracle.gather_point_grad(xyz, N(fidx), N(g3)))
+
+    dist, nidx = three_nn(x, new_xyz)
+    w = T(synthetic.fp_weights(N(dist)), cuda)
+    known = T(rng.standard_normal((b, m, c)).astype(np.float32), cuda).requires_grad_(True)
+    gi = T(rng.standard_normal((b, n, c)).astype(np.float32), cuda)
+    (A.three_interpolate(known, nidx, w) * gi).sum().backward()
+    assert np.array_equal(N(known.grad), oracle.three_interpolate_grad(N(known), N(nidx), N(w), N(gi)))
+
+    cx, cf, ci, cm, cb, cbi = crop_inputs(5, 2, 2048, 8, 12)
+    fts = T(cf, cuda).requires_grad_(True)
+    out = A.pc_crop_and_sample(T(cx, cuda), fts, T(ci, cuda), T(cm, cuda), T(cb, cuda), T(cbi, cuda), 32)
+    gc = T(rng.standard_normal(tuple(out[1].shape)).astype(np.float32), cuda)
+    (out[1] * gc).sum().backward()
+    assert np.array_equal(N(fts.grad), oracle.pc_crop_and_sample_grad_fts(cf, cbi, N(out[4]), N(gc)))
+    assert not out[0].requires_grad and not out[4].requires_grad
