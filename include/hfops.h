@@ -292,6 +292,16 @@ int hf_oriented_nms_scored(const float *boxes3d, const float *scores, int scenes
                            float nms_overlap_thresh, int *keep, int *num_kept, void *workspace,
                            size_t workspace_bytes, hf_stream_t stream);
 
+/* ---- input side --------------------------- */
+/* get_lidar_point_cloud with im_size, hf/core/obj_utils.py:221-277 (lidar_to_cam_frame, hf/core/calib_utils.py:
+ * 370-407; project_to_image, :280-296): points (S,n,4) raw velodyne [x,y,z,i]; calib (S,24) float64 = the first
+ * three rows of r0_rect(4x4) @ tr_velodyne_to_cam(4x4) followed by p2 (3,4), row major -> out (S,n,4)
+ * [x,y,z,i] in the rectified camera frame, the points with z > 0 that project inside (0,w)x(0,h), in scan
+ * order, count (S) of them (rows past count[s] are not written).  Arithmetic in float64 like the reference. */
+size_t hf_lidar_fov_filter_workspace_bytes(int scans, int n);
+int hf_lidar_fov_filter(int scans, int n, const float *points, const double *calib, int im_w, int im_h,
+                        float *out, int *count, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

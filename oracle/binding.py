@@ -392,3 +392,27 @@ def prob_sample(inp, inpr):
     out = np.zeros((b, m), np.int32)
     lib().hf_oracle_prob_sample(_i(b), _i(n), _i(m), _ptr(inp), _ptr(inpr), _ptr(out))
     return out
+
+
+def lidar_fov_filter(points, r0_rect, tr_velodyne_to_cam, p2, im_size):
+    """CPU restatement of get_lidar_point_cloud with im_size (hf/core/obj_utils.py:242-272; lidar_to_cam_frame,
+    hf/core/calib_utils.py:388-407; project_to_image, :289-296): raw (n,4) float32 [x,y,z,i] -> float64 (N,4)
+    [x,y,z,i] in the rectified camera frame of the points with z > 0 that project into (0,w) x (0,h), scan order.
+    Also returns the indices of the kept points."""
+    points = np.asarray(points, dtype=np.float32)
+    r0 = np.zeros((4, 4))
+    r0[:3, :3] = np.asarray(r0_rect, dtype=np.float64)
+    r0[3, 3] = 1.0
+    tf = np.zeros((4, 4))
+    tf[:3, :4] = np.asarray(tr_velodyne_to_cam, dtype=np.float64)
+    tf[3, 3] = 1.0
+    homog = np.concatenate([points[:, :3].astype(np.float64), np.ones((len(points), 1))], axis=1)
+    cam = np.dot(np.dot(r0, tf), homog.T)[:3].T
+    front = np.where(cam[:, 2] > 0)[0]
+    cam = cam[front]
+    uvw = np.dot(np.asarray(p2, dtype=np.float64), np.concatenate([cam.T, np.ones((1, len(cam)))], axis=0))
+    with np.errstate(divide="ignore", invalid="ignore"):
+        u, v = uvw[0] / uvw[2], uvw[1] / uvw[2]
+    inside = (u > 0) & (u < im_size[0]) & (v > 0) & (v < im_size[1])
+    kept = front[inside]
+    return np.hstack([cam[inside], points[kept, 3:4].astype(np.float64)]), kept

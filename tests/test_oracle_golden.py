@@ -331,3 +331,14 @@ def test_oracle_prob_sample_is_an_inverse_cdf_lookup(oracle):
     for i in range(2):
         assert np.array_equal(got[i], np.searchsorted(cs[i], r[i] * cs[i, -1], side="left"))
         assert (w[i, got[i][r[i] > 0]] > 0).all()
+
+
+def test_oracle_lidar_fov_filter_equals_the_reference_input_code(oracle):
+    """Pin: tests/golden/lidar_fov_000000.npz holds the output of the reference's own get_lidar_point_cloud on the
+    first 49152 records of its fixture scan (tests/golden/make_golden_lidar_fov.py)."""
+    g = np.load(os.path.join(os.path.dirname(GOLD), "lidar_fov_000000.npz"))
+    got, kept = oracle.lidar_fov_filter(g["raw"], g["r0_rect"], g["tr_velodyne_to_cam"], g["p2"], g["image_size"])
+    assert got.shape == g["expect"].shape == (12045, 4) and np.all(np.diff(kept) > 0)
+    assert np.allclose(got, g["expect"], rtol=1e-12, atol=1e-12)
+    assert np.array_equal(got[:, 3], g["raw"][kept, 3].astype(np.float64))
+    assert (g["raw"][:, 0] < 0).any() and len(kept) < (g["raw"][:, 0] > 0).sum()  # both filters act
