@@ -6,9 +6,10 @@
 // arithmetic here is double too; the kept points are written as float32 [x, y, z, intensity], the type the network
 // input is cast to (hf/datasets/kitti/kitti_dataset.py:341-370).
 //
-// Two launches, no atomics, deterministic order: (1) every CTA counts the kept points of its tile of 1024,
-// (2) every CTA sums the counts of the tiles before it (at most a few hundred values), redoes the cheap transform
-// and writes its kept points at their rank.  HBM-bound: 16 B read twice + 16 B written per kept point.
+// Two launches, no atomics, deterministic order: (1) every CTA tests its tile of 1024 points, stores one keep bit
+// per point and the tile's count, (2) every CTA sums the counts of the tiles before it (at most a few hundred
+// values), redoes the frame change of its kept points only (no projection, no divisions) and writes them at their
+// rank.  Traffic: 16 B read per point, 16 B read again + 16 B written per kept point.
 #include "common.cuh"
 
 namespace hf {
@@ -39,8 +40,7 @@ __device__ __forceinline__ bool fov_keep(const Calib &c, float4 p, double im_w, 
     return u > 0.0 && u < im_w && v > 0.0 && v < im_h;
 }
 
-__device__ __forceinline__ int block_count(bool keep, int *warp_sums, int &before_in_block) {
-    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+__device__ __forceinline__ int block_count(unsigned ballot, int *warp_sums, int &before_in_block) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) warp_sums[warp] = __popc(ballot);
     __syncthreads();
@@ -60,8 +60,8 @@ __device__ __forceinline__ int block_count(bool keep, int *warp_sums, int &befor
 template <bool WRITE>
 __global__ void __launch_bounds__(kTile) fov_filter_kernel(int n, int tiles, const float4 *__restrict__ pts,
                                                            const Calib *__restrict__ calib, double im_w, double im_h,
-                                                           int *__restrict__ tile_counts, float4 *__restrict__ out,
-                                                           int *__restrict__ count) {
+                                                           int *__restrict__ tile_counts, unsigned *__restrict__ keep_bits,
+                                                           float4 *__restrict__ out, int *__restrict__ count) {
     __shared__ int warp_sums[kTile / 32];
     __shared__ int tile_base;
     __shared__ Calib c;
@@ -76,20 +76,28 @@ __global__ void __launch_bounds__(kTile) fov_filter_kernel(int n, int tiles, con
     }
     __syncthreads();
     const int i = tile * kTile + threadIdx.x;
-    bool keep = false;
+    const int words = tiles * (kTile / 32);
+    unsigned *bits = keep_bits + (size_t)scan * words + (i >> 5);
     double X = 0, Y = 0, Z = 0;
-    float4 p = make_float4(0, 0, 0, 0);
-    if (i < n) {
-        p = __ldg(pts + (size_t)scan * n + i);
-        keep = fov_keep(c, p, im_w, im_h, X, Y, Z);
-    }
     int before;
-    const int total = block_count(keep, warp_sums, before);
     if (!WRITE) {
+        bool keep = false;
+        if (i < n) keep = fov_keep(c, __ldg(pts + (size_t)scan * n + i), im_w, im_h, X, Y, Z);
+        const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+        if ((threadIdx.x & 31) == 0) *bits = ballot;
+        const int total = block_count(ballot, warp_sums, before);
         if (threadIdx.x == 0) tile_counts[(size_t)scan * tiles + tile] = total;
         return;
     }
-    if (keep) out[(size_t)scan * n + tile_base + before] = make_float4((float)X, (float)Y, (float)Z, p.w);
+    const unsigned ballot = *bits;
+    const int total = block_count(ballot, warp_sums, before);
+    if ((ballot >> (threadIdx.x & 31)) & 1u) {
+        const float4 p = __ldg(pts + (size_t)scan * n + i);
+        X = row4(c.rect + 0, p.x, p.y, p.z);
+        Y = row4(c.rect + 4, p.x, p.y, p.z);
+        Z = row4(c.rect + 8, p.x, p.y, p.z);
+        out[(size_t)scan * n + tile_base + before] = make_float4((float)X, (float)Y, (float)Z, p.w);
+    }
     if (tile == tiles - 1 && threadIdx.x == 0) count[scan] = tile_base + total;
 }
 
@@ -99,7 +107,7 @@ __global__ void __launch_bounds__(kTile) fov_filter_kernel(int n, int tiles, con
 extern "C" size_t hf_lidar_fov_filter_workspace_bytes(int scans, int n) {
     if (scans <= 0 || n <= 0) return 16;
     const size_t tiles = ((size_t)n + hf::kTile - 1) / hf::kTile;
-    return ((size_t)scans * tiles * sizeof(int) + 15) & ~(size_t)15;
+    return (((size_t)scans * tiles * sizeof(int) + 15) & ~(size_t)15) + (size_t)scans * tiles * (hf::kTile / 32) * sizeof(unsigned);
 }
 
 extern "C" int hf_lidar_fov_filter(int scans, int n, const float *points, const double *calib, int im_w, int im_h,
@@ -127,12 +135,14 @@ extern "C" int hf_lidar_fov_filter(int scans, int n, const float *points, const 
     const int tiles = (n + kTile - 1) / kTile;
     const dim3 grid(tiles, scans);
     int *tile_counts = static_cast<int *>(workspace);
+    unsigned *keep_bits = reinterpret_cast<unsigned *>(static_cast<unsigned char *>(workspace) +
+                                                       (((size_t)scans * tiles * sizeof(int) + 15) & ~(size_t)15));
     const Calib *c = reinterpret_cast<const Calib *>(calib);
     const float4 *p = reinterpret_cast<const float4 *>(points);
-    fov_filter_kernel<false><<<grid, kTile, 0, s>>>(n, tiles, p, c, (double)im_w, (double)im_h, tile_counts, nullptr, nullptr);
+    fov_filter_kernel<false><<<grid, kTile, 0, s>>>(n, tiles, p, c, (double)im_w, (double)im_h, tile_counts, keep_bits, nullptr, nullptr);
     HF_LAUNCH_OK("fov_filter_kernel<count>");
     fov_filter_kernel<true><<<grid, kTile, 0, s>>>(n, tiles, p, c, (double)im_w, (double)im_h, tile_counts,
-                                                  reinterpret_cast<float4 *>(out), count);
+                                                  keep_bits, reinterpret_cast<float4 *>(out), count);
     HF_LAUNCH_OK("fov_filter_kernel<write>");
     return HF_OK;
 }

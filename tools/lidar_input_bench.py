@@ -32,7 +32,7 @@ for scans, n in [(1, 122880), (16, 122880), (64, 122880)]:
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     kept = int(count.sum().item())
-    algo = scans * n * 16 * 2 + kept * 16  # the scan read by both launches + kept points written
+    algo = scans * n * 16 + kept * 32  # the scan read once, kept points read again and written
     t0 = time.perf_counter()
     from oracle import binding  # noqa: E402
 
