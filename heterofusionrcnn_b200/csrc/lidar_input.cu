@@ -66,33 +66,34 @@ __global__ void __launch_bounds__(kTile) fov_filter_kernel(int n, int tiles, con
     __shared__ int tile_base;
     __shared__ Calib c;
     const int scan = blockIdx.y, tile = blockIdx.x;
-    if (threadIdx.x < 24) reinterpret_cast<double *>(&c)[threadIdx.x] = reinterpret_cast<const double *>(calib + scan)[threadIdx.x];
-    if (WRITE && threadIdx.x < 32) {
-        int s = 0;
-        for (int t = threadIdx.x; t < tile; t += 32) s += tile_counts[(size_t)scan * tiles + t];
-#pragma unroll
-        for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (threadIdx.x == 0) tile_base = s;
-    }
-    __syncthreads();
     const int i = tile * kTile + threadIdx.x;
     const int words = tiles * (kTile / 32);
     unsigned *bits = keep_bits + (size_t)scan * words + (i >> 5);
+    // every global load of the thread is issued before the first barrier: one memory latency per CTA, not four
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n) p = __ldg(pts + (size_t)scan * n + i);
+    const unsigned stored = WRITE ? *bits : 0u;
+    if (threadIdx.x < 24) reinterpret_cast<double *>(&c)[threadIdx.x] = reinterpret_cast<const double *>(calib + scan)[threadIdx.x];
+    if (WRITE && threadIdx.x >= 32 && threadIdx.x < 64) {  // warp 1: rank of the tile's first kept point
+        int s = 0;
+        for (int t = threadIdx.x - 32; t < tile; t += 32) s += tile_counts[(size_t)scan * tiles + t];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (threadIdx.x == 32) tile_base = s;
+    }
+    __syncthreads();
     double X = 0, Y = 0, Z = 0;
     int before;
     if (!WRITE) {
-        bool keep = false;
-        if (i < n) keep = fov_keep(c, __ldg(pts + (size_t)scan * n + i), im_w, im_h, X, Y, Z);
+        const bool keep = i < n && fov_keep(c, p, im_w, im_h, X, Y, Z);
         const unsigned ballot = __ballot_sync(0xffffffffu, keep);
         if ((threadIdx.x & 31) == 0) *bits = ballot;
         const int total = block_count(ballot, warp_sums, before);
         if (threadIdx.x == 0) tile_counts[(size_t)scan * tiles + tile] = total;
         return;
     }
-    const unsigned ballot = *bits;
-    const int total = block_count(ballot, warp_sums, before);
-    if ((ballot >> (threadIdx.x & 31)) & 1u) {
-        const float4 p = __ldg(pts + (size_t)scan * n + i);
+    const int total = block_count(stored, warp_sums, before);
+    if ((stored >> (threadIdx.x & 31)) & 1u) {
         X = row4(c.rect + 0, p.x, p.y, p.z);
         Y = row4(c.rect + 4, p.x, p.y, p.z);
         Z = row4(c.rect + 8, p.x, p.y, p.z);
