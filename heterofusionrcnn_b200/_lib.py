@@ -25,6 +25,9 @@ SIGNATURES = {
     "hf_version": (ctypes.c_char_p, []),
     "hf_last_error": (ctypes.c_char_p, []),
     "hf_launch_count": (ctypes.c_ulonglong, []),
+    "hf_fp32_probe_out_floats": (_size_t, [_c_int]),
+    "hf_fp32_probe_flops": (ctypes.c_double, [_c_int, _c_int, _c_int]),
+    "hf_fp32_probe": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr]),
     "hf_farthest_point_sample": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_fps_set_cluster": (None, [_c_int]),
     "hf_fps_set_threads": (None, [_c_int]),

@@ -998,7 +998,7 @@ NmsWorkspace nms_workspace(int scenes, int boxes_num) {
 
 namespace hf {
 namespace {
-int g_nms_spatial_sort = 1;
+thread_local int g_nms_spatial_sort = 1;
 }
 }  // namespace hf
 extern "C" void hf_nms_set_spatial_sort(int on) { hf::g_nms_spatial_sort = on; }

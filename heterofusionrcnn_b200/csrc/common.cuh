@@ -45,14 +45,16 @@ void count_launch(unsigned n = 1);
         hf::count_launch();                                                           \
     } while (0)
 
+// SM count of the CURRENT device, cached per device ordinal (a process may drive several device types).
 inline int num_sms() {
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
-            sms = 148;
-    }
+    constexpr int kMaxDev = 64;
+    static int cache[kMaxDev] = {0};  // 0 = unknown; racing first calls write the same value
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev >= 0 && dev < kMaxDev && cache[dev] > 0) return cache[dev];
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    if (dev >= 0 && dev < kMaxDev) cache[dev] = sms;
     return sms;
 }
 

@@ -117,9 +117,11 @@ __global__ void __launch_bounds__(kCropThreads)
         }
         __syncthreads();
         const int total = hcount;
-        if (total <= hcap) {
-            int P = 32;
-            while (P < total) P <<= 1;
+        // the list is sorted over P = next power of two >= max(32, total) entries: it must hold P, not just
+        // `total` (resize = 100: hcap = 800, 600 hits would pad and sort 1024 entries; resize < 4: hcap < 32)
+        int P = 32;
+        while (P < total) P <<= 1;
+        if (P <= hcap) {
             for (int i = total + t; i < P; i += kCropThreads) hits[i] = INT_MAX;
             __syncthreads();
             for (int k2 = 2; k2 <= P; k2 <<= 1) {

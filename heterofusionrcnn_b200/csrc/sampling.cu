@@ -281,7 +281,7 @@ __global__ void gather_point_kernel(long long total, int n, int m, const float *
     dst[2] = v2;
 }
 
-int g_cluster_override = 0;
+thread_local int g_cluster_override = 0;  // per calling thread: a tuning override never changes what another thread launches
 
 template <int CLUSTER, int THREADS, int PTS>
 int launch_fps(int b, int n, int m, const float *inp, int *out, cudaStream_t stream) {
@@ -305,8 +305,8 @@ int launch_fps(int b, int n, int m, const float *inp, int *out, cudaStream_t str
     return HF_OK;
 }
 
-int g_threads_override = 0;
-int g_algo = 0, g_bucket_w = 0, g_bucket_j = 0;  // hf_fps_set_variant
+thread_local int g_threads_override = 0;
+thread_local int g_algo = 0, g_bucket_w = 0, g_bucket_j = 0;  // hf_fps_set_variant
 
 template <int CLUSTER>
 int dispatch_pts(int per_cta, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {

@@ -707,7 +707,7 @@ int launch_knn(bool indexed, int b, int n, int m, int k, const float *xyz1, cons
     return HF_OK;
 }
 
-int g_spatial_mode = 0;  // 0 = auto, 1 = never (every-pair kernels), 2 = whenever a shape exists
+thread_local int g_spatial_mode = 0;  // 0 = auto, 1 = never (every-pair kernels), 2 = whenever a shape exists
 
 inline int round32(int v) { return (v + 31) & ~31; }
 inline size_t cloud_bytes(int b, int n) { return (size_t)b * round32(n) * 17; }  // 16 B/point + 32 B/bucket

@@ -23,9 +23,24 @@ class CloudIndex:
     def __init__(self, xyz, buf):
         self.xyz, self.buf = xyz, buf  # the cloud stays referenced: the index is only valid for its contents
         self.b, self.n = xyz.shape[0], xyz.shape[1]
+        self.version = xyz._version  # bumped by every in-place write torch knows about (copy_, mul_, ...)
 
     def matches(self, xyz):
-        return xyz.data_ptr() == self.xyz.data_ptr() and tuple(xyz.shape) == (self.b, self.n, 3)
+        """True if the index was built from exactly this tensor AND the tensor has not been written in place
+        since (a stale index would silently prune against the old point positions).  Writes torch cannot see
+        (a raw pointer handed to another library) are the caller's responsibility: call refresh()."""
+        return (xyz.data_ptr() == self.xyz.data_ptr() and tuple(xyz.shape) == (self.b, self.n, 3)
+                and xyz._version == self.version)
+
+    def refresh(self):
+        """Rebuild the index in place from the current contents of its cloud (current stream)."""
+        lib = _lib.load()
+        with torch.cuda.device(self.xyz.device):
+            rc = lib.hf_cloud_index_build(self.b, self.n, self.xyz.data_ptr(), self.buf.data_ptr(), self.buf.numel(),
+                                          stream_ptr(self.xyz.device))
+        _lib.check(rc, "build_cloud_index")
+        self.version = self.xyz._version
+        return self
 
     def ptr_for(self, xyz):
         """Device pointer of the index if it belongs to `xyz`, else None (the op then works without it)."""

@@ -13,8 +13,11 @@
  *   - no hidden allocation: scratch is passed in by the caller and sized by a
  *     *_workspace_bytes() query;
  *   - all pointers are DEVICE pointers unless the name ends in _host;
- *   - re-entrant: no global state besides a launch counter and a per-thread
- *     last-error string.
+ *   - re-entrant: the only process-wide state is a launch counter (atomic) and
+ *     per-device caches of device attributes; the last-error string and the
+ *     tuning overrides (hf_fps_set_*, hf_spatial_set_mode, hf_nms_set_spatial_sort)
+ *     are PER CALLING THREAD, so an override never changes what another thread
+ *     launches.
  * Layouts are the reference's: row-major contiguous (batch, points, channels),
  * fp32 / int32, bool = 1 byte.
  */
@@ -42,6 +45,14 @@ const char *hf_version(void);
 const char *hf_last_error(void);
 /* Number of kernels this library has launched in this process (all threads). */
 unsigned long long hf_launch_count(void);
+
+/* Measurement aid (roofline denominator): runs `blocks` CTAs of 1024 threads, each thread `iters` rounds of 8
+ * independent FMA chains and nothing else (packed != 0: fma.rn.f32x2, two FMAs per instruction).  Time the launch
+ * with CUDA events and divide hf_fp32_probe_flops(blocks, iters, packed) by it = the FP32 non-tensor peak of
+ * the device.  out: hf_fp32_probe_out_floats(blocks) floats. */
+size_t hf_fp32_probe_out_floats(int blocks);
+double hf_fp32_probe_flops(int blocks, int iters, int packed);
+int hf_fp32_probe(int blocks, int iters, int packed, float *out, hf_stream_t stream);
 
 /* ---- sampling ----------------------------------------------------------- */
 /* Replaces farthestpointsamplingLauncher(b,n,m,inp,temp,out), sampling/tf_sampling_g.cu:203

@@ -419,6 +419,38 @@ def test_crop_with_cloud_index_matches_oracle(cuda, oracle, C, R, P, nbox):
         assert np.array_equal(N(g), w), name
 
 
+@pytest.mark.parametrize("R,scale", [(3, 1.0), (1, 1.0), (2, 6.0), (100, 6.0), (500, 6.0), (100, 1.0), (37, 3.0)])
+def test_crop_with_cloud_index_odd_resize(cuda, oracle, R, scale):
+    """resize that is not a power of two / smaller than 4: the indexed select's hit list holds 8*R entries but
+    is sorted over the next power of two, so boxes with hcap/2 < hits <= hcap (and any hit at R < 4) must take
+    the ordered scan instead (cropping.cu wrote past the list there).  Boxes are blown up so that
+    several hold more than R and more than 8*R points."""
+    from heterofusionrcnn_b200 import spatial
+
+    B, P, C, nbox = 2, 16384, 8, 24
+    xyz, inten = synthetic.make_scans(300 + R, B, P)
+    rng = np.random.default_rng(R)
+    fts = rng.standard_normal((B, P, C)).astype(np.float32)
+    mask = rng.random((B, P)) < 0.3
+    b3 = [synthetic.make_boxes3d(R * 13 + i, xyz[i], nbox) for i in range(B)]
+    for i in range(B):
+        b3[i][:, 3:6] *= np.linspace(0.5, 2.0, nbox)[:, None] * scale  # hit counts sweep through R, 4R, 8R
+    b3[-1][0, 0] += 500.0
+    boxes = np.concatenate([synthetic.boxes3d_to_corners(x) for x in b3])
+    box_ind = np.repeat(np.arange(B, dtype=np.int32), nbox)
+    args = (xyz, fts, inten, mask, boxes, box_ind)
+    want = oracle.pc_crop_and_sample(*args, R)
+    dargs = [T(a, cuda) for a in args]
+    ix = spatial.build_cloud_index(dargs[0])
+    for index in (ix, None):
+        got = pc_crop_and_sample(*dargs, R, index=index)
+        for name, g, w in zip(["crop_pts", "crop_fts", "crop_intensities", "crop_mask", "crop_ind", "non_empty_box"], got, want):
+            assert np.array_equal(N(g), w), (name, index is not None)
+    # the sweep really crosses the list capacity: some boxes hold more than 8*R points, some fewer than R
+    inside = np.array([len(np.unique(want[4][k])) for k in range(len(boxes))])
+    assert (inside >= min(R, 2)).any() and want[5].any() and not want[5].all()
+
+
 @needs_ref
 def test_crop_agrees_with_reference_kernel_up_to_its_race(cuda):
     """The reference assigns slots with a racing atomicInc: compare what is race-free
