@@ -39,7 +39,36 @@ if ROOT not in sys.path:
 
 METRIC = "scans_per_sec_16k_sa_fp_crop_nms_chain"
 UNIT = "scans/s"
-FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # derived: SMs x lanes x FMA x max clock (no measured figure)
+FP32_PEAK_DERIVED = 148 * 128 * 2 * 1.965e9 / 1e12  # SMs x lanes x FMA x max clock; the line reports the MEASURED figure
+
+
+def measure_fp32_peak(torch, hf, dev):
+    """FP32 non-tensor peak of this GPU: hf_fp32_probe (csrc/api.cu) = nothing but independent FFMA chains, 2048
+    resident threads per SM, timed with CUDA events, best of 5.  Scalar FFMA and packed FFMA2 (fma.rn.f32x2) are
+    both measured; the roofline denominator is the larger."""
+    from heterofusionrcnn_b200 import _lib
+
+    lib = _lib.load()
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    blocks, iters = sms * 2 * 4, 8192
+    out = torch.empty((int(lib.hf_fp32_probe_out_floats(blocks)),), dtype=torch.float32, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    res = {}
+    for packed in (0, 1):
+        best = None
+        for it in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.check(lib.hf_fp32_probe(blocks, iters, packed, out.data_ptr(), st), "fp32 probe")
+            e1.record()
+            e1.synchronize()
+            ms = e0.elapsed_time(e1)
+            if it > 0 and (best is None or ms < best):
+                best = ms
+        res["ffma2" if packed else "ffma"] = float(lib.hf_fp32_probe_flops(blocks, iters, packed)) / (best / 1e3) / 1e12
+    res["peak"] = max(res["ffma"], res["ffma2"])
+    res["derived"] = FP32_PEAK_DERIVED
+    return res
 
 
 def parse_args():
@@ -69,6 +98,10 @@ def parse_args():
                     help="print (stderr) when every op of the last timed step started and ended, relative to the step's start")
     ap.add_argument("--profile-range", action="store_true",
                     help="bracket the timed region with cudaProfilerStart/Stop (ncu --profile-from-start off)")
+    ap.add_argument("--no-config5", action="store_true",
+                    help="skip the BASELINE configs[4] leg (128 scans x 65536 points in total, strong scaling over the ranks)")
+    ap.add_argument("--config5-steps", type=int, default=3, help="timed passes over the 128 scans of the configs[4] leg")
+    ap.add_argument("--config5-scans", type=int, default=128, help="total scans of the configs[4] leg (multiple of 16 x ranks)")
     ap.add_argument("--serial", action="store_true",
                     help="issue the whole chain on one stream in program order (default: independent branches overlap on streams)")
     return ap.parse_args()
@@ -107,7 +140,7 @@ def config_dict(args, cfg, n_gpus):
         "points_per_scan": cfg.points,
         "sharding": "batch slices, one per GPU, no collective" if n_gpus > 1 else "single GPU",
         "issue": "one stream, program order" if args.serial else
-                 "independent branches of the chain on 13 CUDA streams%s, %d batch(es) in flight (e2e leg: eager, %d)" % (
+                 "independent branches of the chain on CUDA streams%s, %d batch(es) in flight (e2e leg: eager, %d)" % (
                      "" if (args.no_graph or args.timeline) else ", one step = one replay of the captured CUDA graph",
                      max(1, args.resident_inflight), max(1, args.inflight)),
         "l2": "no explicit flush: one step reads 0.45 GB and writes 5.6 GB per GPU, far beyond the 126 MB L2",
@@ -259,42 +292,59 @@ def cpu_chain(O, host, cfg, scenes):
     return keeps
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        return os.cpu_count() or 1
+
+
 def cpu_sample_size(args, cores):
+    """Scans per CPU pass: one per host core, so that the scene-parallel ops (FPS is one thread per scan) keep
+    every core busy like the row-parallel ones do (scene-parallel over ALL host cores)."""
     if args.cpu_scenes > 0:
-        return min(args.cpu_scenes, args.batch)
-    return max(1, min(args.batch, cores // 8, 4))
+        return args.cpu_scenes
+    return max(1, min(cores, 64))
 
 
-def time_cpu(args, cfg, host, steps, warmup):
+def time_cpu(args, cfg, steps, warmup, single_thread):
+    """The CPU path on this box's host cores.  Two figures (SURVEY.md 8d / BASELINE.md section 2):
+    all cores = `cores` std::threads over scenes / rows, one scan per core per pass (no algorithmic change);
+    single thread = the code exactly as the reference is written, one scan."""
+    from heterofusionrcnn_b200 import chain
     from oracle import binding as O
 
     O.build()
-    cores = os.cpu_count() or 1
-    O.set_threads(cores)
+    cores = host_cores()
     scenes = cpu_sample_size(args, cores)
+    host = chain.make_host_inputs(cfg, batch=scenes, seed=2)
+    O.set_threads(cores)
     for _ in range(warmup):
         cpu_chain(O, host, cfg, scenes)
     t0 = time.perf_counter()
     for _ in range(steps):
         cpu_chain(O, host, cfg, scenes)
     dt = (time.perf_counter() - t0) / steps
-    kind = "port"
-    return {"value": scenes / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": "%d of the %d scans of one batch, whole chain, oracle/hf_oracle.cpp (g++ -O2) with %d std::threads "
-                      "over scenes/rows; %.2f s per pass" % (scenes, args.batch, cores, dt)}, dt
+    cb = {"value": scenes / dt, "unit": UNIT, "cores": cores, "kind": "port",
+          "sample": "%d scans (one per host core) of the bench workload, whole chain, oracle/hf_oracle.cpp (g++ -O2), %d std::threads "
+                    "over scenes / rows; %.2f s per pass" % (scenes, cores, dt)}
+    if single_thread:
+        O.set_threads(1)
+        t0 = time.perf_counter()
+        cpu_chain(O, host, cfg, 1)
+        dt1 = time.perf_counter() - t0
+        O.set_threads(cores)
+        cb["single_thread"] = {"value": 1.0 / dt1, "unit": UNIT, "cores": 1,
+                               "sample": "1 scan, whole chain, one thread, the code as the reference is written; %.2f s" % dt1}
+    return cb, dt
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    from heterofusionrcnn_b200 import chain
-
     cfg = make_cfg(args)
-    cores = os.cpu_count() or 1
-    scenes = cpu_sample_size(args, cores)
-    host = chain.make_host_inputs(cfg, batch=scenes, seed=2)
-    cb, dt = time_cpu(args, cfg, host, args.steps, args.warmup)
+    cb, dt = time_cpu(args, cfg, args.steps, args.warmup, single_thread=False)
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
@@ -324,6 +374,90 @@ def nbytes_of(obj):
     return 0
 
 
+def parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_rank_to_local_cores(local, world):
+    """Before any CUDA allocation: restrict this rank to its share of the cores that are local to its GPU
+    (/sys/bus/pci/devices/<bdf>/local_cpulist), so that its pinned staging memory is allocated on, and its copies
+    are driven from, the GPU's own NUMA node.  GPUs with the same local core list split it evenly.  Returns a
+    description for the JSON line (None if nothing could be done)."""
+    try:
+        out = subprocess.run(["nvidia-smi", "--query-gpu=index,pci.bus_id", "--format=csv,noheader"], stdout=subprocess.PIPE,
+                             stderr=subprocess.DEVNULL, text=True, timeout=20).stdout
+        lists, nodes = {}, {}
+        for ln in out.strip().splitlines():
+            idx, bdf = [x.strip() for x in ln.split(",")]
+            bdf = bdf.lower()
+            if len(bdf.split(":")[0]) == 8:  # nvidia-smi prints an 8-digit domain, sysfs uses 4
+                bdf = bdf[4:]
+            base = "/sys/bus/pci/devices/" + bdf
+            lists[int(idx)] = parse_cpulist(open(base + "/local_cpulist").read())
+            try:
+                nodes[int(idx)] = int(open(base + "/numa_node").read())
+            except Exception:
+                nodes[int(idx)] = None
+        allowed = os.sched_getaffinity(0)
+        mine = sorted(lists[local] & allowed) or sorted(allowed)
+        peers = [g for g in range(world) if g in lists and lists[g] == lists[local]]
+        share = len(mine) // max(1, len(peers))
+        if share >= 2 and local in peers:
+            k = peers.index(local)
+            mine = mine[k * share:(k + 1) * share]
+        os.sched_setaffinity(0, mine)
+        return {"cpus": "%d-%d (%d)" % (mine[0], mine[-1], len(mine)), "numa_node": nodes.get(local),
+                "gpus_sharing_the_core_list": len(peers)}
+    except Exception as exc:  # no sysfs / nvidia-smi: leave the affinity alone
+        return {"error": str(exc)[:120]}
+
+
+def make_config5(torch, chain, cfg, dev, rank, world, total_scans, batch):
+    """Inputs of the BASELINE configs[4] leg for this rank: its `total_scans / world` scans of 65536 points in
+    batches of `batch`.  Geometry (scans, intensities, masks, proposal boxes, NMS boxes) is distinct per scan
+    (seed = 5000 + global scan index) and generated on the host like every other input; the stand-ins for the
+    MLP feature maps are ONE set of resident tensors shared by all batches (device-generated N(0,1); their values
+    do not influence any kernel's work, and in the reference pipeline they are device-resident MLP outputs)."""
+    import numpy as np
+
+    from heterofusionrcnn_b200 import synthetic
+
+    cfg5 = cfg.scaled(65536)
+    per_rank = total_scans // world
+    nb = per_rank // batch
+    first = rank * per_rank
+    geo = []
+    for k in range(nb):
+        xs, its, bx, nm, mk = [], [], [], [], []
+        for i in range(batch):
+            g = first + k * batch + i
+            x, it = synthetic.make_scan(5000 + g, cfg5.points)
+            xs.append(x)
+            its.append(it)
+            bx.append(synthetic.boxes3d_to_corners(synthetic.make_boxes3d(7000 + g, x, cfg5.crop_boxes)))
+            nm.append(synthetic.make_nms_boxes(9000 + g, cfg5.nms_boxes))
+            mk.append(np.random.default_rng(11000 + g).random(cfg5.points) < 0.3)
+        geo.append({"xyz": torch.from_numpy(np.stack(xs)).to(dev), "intensity": torch.from_numpy(np.stack(its)).to(dev),
+                    "fg_mask": torch.from_numpy(np.stack(mk)).to(dev), "crop_boxes": torch.from_numpy(np.concatenate(bx)).to(dev),
+                    "nms_boxes": torch.from_numpy(np.stack(nm)).to(dev)})
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    n_lv = [cfg5.points] + list(cfg5.npoint)
+    rnd = lambda *shape: torch.randn(shape, dtype=torch.float32, device=dev, generator=gen)  # noqa: E731
+    static = {k: v.clone() for k, v in geo[0].items()}
+    static["box_ind"] = torch.arange(batch, dtype=torch.int32, device=dev).repeat_interleave(cfg5.crop_boxes)
+    static["sa_feats"] = [None] + [rnd(batch, n_lv[l], cfg5.sa_channels[l]) for l in range(1, 4)]
+    static["fp_feats"] = [rnd(batch, n_lv[4 - j], cfg5.fp_channels[j]) for j in range(4)]
+    static["crop_fts"] = rnd(batch, cfg5.points, cfg5.crop_channels)
+    return cfg5, static, geo
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -338,6 +472,7 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device — the hfops operators have no CPU fallback "
                          "(use --impl reference for the CPU path)")
     hf.load()  # raises if libhfops.so is missing
+    binding = bind_rank_to_local_cores(local, world) if world > 1 else None  # before the first CUDA allocation
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -347,9 +482,13 @@ def run_b200(args):
 
     cfg = make_cfg(args)
     host_np = chain.make_host_inputs(cfg, batch=args.batch, seed=2 + rank)
-    pinned = chain.to_pinned(host_np)
-    resident = chain.to_device_from_pinned(pinned, dev)
+    arena = chain.InputArena(host_np)  # ONE pinned buffer holding every input tensor of a step
+    resident_buf = arena.device_buffer(dev)
+    arena.upload(resident_buf)
+    resident = arena.views(resident_buf)
     torch.cuda.synchronize()
+    fp32 = measure_fp32_peak(torch, hf, dev)
+    FP32_PEAK_TFLOPS = fp32["peak"]
 
     def barrier():
         torch.cuda.synchronize()
@@ -441,49 +580,135 @@ def run_b200(args):
     # ---- end to end: host buffers in, host-consumed results out, through the public op API ----
     e2e = None
     if not args.no_e2e:
-        h2d = nbytes_of(pinned)
         depth = max(1, args.inflight) if overlap else 1
-        pipe = chain.ChainPipeline(cfg, depth=depth, overlap=overlap)
-        out_streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]
-        out_host = [None] * depth
+        dev_bufs = [arena.device_buffer(dev) for _ in range(depth)]
+        for b_ in dev_bufs:  # every arena holds the whole step once (the host-originated-only leg keeps the features)
+            arena.upload(b_)
+        dev_views = [arena.views(b_) for b_ in dev_bufs]
+        torch.cuda.synchronize()
         main = torch.cuda.current_stream(dev)
-        for it in range(max(args.warmup, 3) + args.steps):
-            if it == max(args.warmup, 3):
-                for st in out_streams:
-                    main.wait_stream(st)
-                pipe.drain()
-                barrier()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                t0 = time.perf_counter()
-                e0.record()
-            slot = it % depth
-            d = chain.to_device_from_pinned(pinned, dev)  # on the current stream: overlaps the previous batch's kernels
-            res = pipe.submit(d, None)
-            st = out_streams[slot]
-            for e in res["_done"]:
-                st.wait_event(e)
-            if not res["_done"]:
-                st.wait_stream(main)
-            with torch.cuda.stream(st):  # device->host copies of this batch's host-consumed results
-                outs = chain.host_results(res, cfg)
-                if out_host[slot] is None:
-                    out_host[slot] = [torch.empty(o.shape, dtype=o.dtype, pin_memory=True) for o in outs]
-                for o, h in zip(outs, out_host[slot]):
-                    h.copy_(o, non_blocking=True)
-        for st in out_streams:
-            main.wait_stream(st)
-        pipe.drain()
-        e1.record()
+        out_streams = [torch.cuda.Stream(device=dev) for _ in range(depth)]
+
+        def e2e_leg(host_only):
+            """`steps` passes, each: ONE host->device copy of the step's inputs (whole arena, or only the
+            host-originated prefix) -> the chain through the public op API -> device->host copies of the
+            host-consumed results.  `depth` batches in flight; CUDA events on the current stream, max over ranks."""
+            pipe = chain.ChainPipeline(cfg, depth=depth, overlap=overlap)
+            out_host = [None] * depth
+            sent = 0
+            warm = max(args.warmup, 3)
+            for it in range(warm + args.steps):
+                if it == warm:
+                    for st in out_streams:
+                        main.wait_stream(st)
+                    pipe.drain()
+                    barrier()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    t0 = time.perf_counter()
+                    e0.record()
+                slot = pipe.next_slot()
+                pipe.release(slot)  # the pass that read this arena last is over: it may be overwritten
+                sent = arena.upload(dev_bufs[slot], host_originated_only=host_only)  # current stream: overlaps the previous batch's kernels
+                res = pipe.submit(dev_views[slot], None)
+                st = out_streams[slot]
+                for e in res["_done"]:
+                    st.wait_event(e)
+                if not res["_done"]:
+                    st.wait_stream(main)
+                with torch.cuda.stream(st):  # device->host copies of this batch's host-consumed results
+                    outs = chain.host_results(res, cfg)
+                    if out_host[slot] is None:
+                        out_host[slot] = [torch.empty(o.shape, dtype=o.dtype, pin_memory=True) for o in outs]
+                    for o, h in zip(outs, out_host[slot]):
+                        h.copy_(o, non_blocking=True)
+            for st in out_streams:
+                main.wait_stream(st)
+            pipe.drain()
+            e1.record()
+            barrier()
+            wall_ms = (time.perf_counter() - t0) * 1e3
+            ms_ = max_over_ranks(max(e0.elapsed_time(e1), 0.0))
+            del pipe
+            return {"value": args.batch * n_gpus * args.steps / (ms_ / 1e3), "unit": UNIT, "h2d_bytes_per_step": sent,
+                    "d2h_bytes_per_step": nbytes_of(out_host[0]), "ms_per_step": ms_ / args.steps,
+                    "wall_ms_per_step": wall_ms / args.steps}
+
+        def copy_only_leg():
+            """The step's host->device copies alone (no kernels): what the host side of this box delivers per GPU
+            when `world` ranks copy at once."""
+            barrier()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            for it in range(args.steps):
+                arena.upload(dev_bufs[it % depth])
+            c1.record()
+            barrier()
+            ms_ = max_over_ranks(c0.elapsed_time(c1))
+            return {"gbs_per_gpu": arena.nbytes * args.steps / (ms_ / 1e3) / 1e9, "ms_per_step": ms_ / args.steps,
+                    "ranks_copying_at_once": world}
+
+        e2e = e2e_leg(host_only=False)
+        e2e.update({
+            "copied_in": "every input tensor of the step (scans, stand-in feature maps, masks, boxes): one pinned arena, ONE "
+                         "cudaMemcpyAsync per step",
+            "copied_out": "FPS indices (4 levels), ball-query counts, NMS keep lists + counts, crop non_empty flags",
+            "pipelining": "%d batches in flight: a batch's host->device copy overlaps the previous batch's kernels" % depth,
+            "copy_only": copy_only_leg(),
+            "binding": binding,
+        })
+        ho = e2e_leg(host_only=True)
+        ho["copied_in"] = ("only what a caller of the reference pipeline holds on the host: scans, intensities, foreground masks, "
+                           "proposal boxes + box_ind, NMS boxes; the MLP feature maps stay resident (in the reference they are "
+                           "produced on the device, rcnn_model.py:478-489)")
+        e2e["host_originated_only"] = ho
+        del dev_bufs, dev_views
+
+    # ---- BASELINE configs[4]: 128 scans x 65536 points in total, strong scaling over the ranks ----
+    config5 = None
+    if not args.no_config5 and args.points == 16384 and args.config5_scans % (args.batch * world) == 0:
+        torch.cuda.synchronize()
+        cfg5, static5, geo5 = make_config5(torch, chain, cfg, dev, rank, world, args.config5_scans, args.batch)
+        g5 = chain.ChainGraph(static5, cfg5)
+
+        def pass5():
+            for g in geo5:  # this rank's batches: geometry into the graph's input buffers (stream ordered), one replay
+                for k_, v_ in g.items():
+                    static5[k_].copy_(v_, non_blocking=True)
+                g5.replay()
+
+        pass5()
         barrier()
-        wall_ms = (time.perf_counter() - t0) * 1e3
-        e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0))
-        e2e = {"value": args.batch * n_gpus * args.steps / (e2e_ms / 1e3), "unit": UNIT,
-               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": nbytes_of(out_host[0]), "ms_per_step": e2e_ms / args.steps,
-               "wall_ms_per_step": wall_ms / args.steps,
-               "copied_in": "every input tensor of the step (scans, stand-in feature maps, masks, boxes) from pinned host memory",
-               "copied_out": "FPS indices (4 levels), ball-query counts, NMS keep lists + counts, crop non_empty flags",
-               "pipelining": "%d batches in flight: a batch's host->device copies overlap the previous batch's kernels" % depth}
-        del pipe
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(args.config5_steps):
+            pass5()
+        f1.record()
+        barrier()
+        ms5 = max_over_ranks(f0.elapsed_time(f1)) / args.config5_steps
+        alone5 = EventProbe(torch)
+        chain.run_chain(static5, cfg5, None, overlap=False)
+        torch.cuda.synchronize()
+        for _ in range(2):
+            chain.run_chain(static5, cfg5, alone5, overlap=False)
+        torch.cuda.synchronize()
+        a5 = {o["launch"]: o for o in alone5.summarise(2)}
+        crop5 = a5.get("pc_crop_and_sample/c=%d" % cfg5.crop_channels)
+        hbm_peak_, _ = peaks()
+        config5 = {
+            "workload": "configs[4]: the same chain on %d scans x %d points in total, batch-sharded: every rank runs its %d scans "
+                        "in batches of %d (one graph replay per batch)" % (args.config5_scans, cfg5.points,
+                                                                         args.config5_scans // world, args.batch),
+            "scaling": "strong", "n_gpus": n_gpus, "total_scans": args.config5_scans, "steps": args.config5_steps,
+            "scans_per_s": args.config5_scans / (ms5 / 1e3), "ms_per_pass": ms5, "ms_per_scan": ms5 / args.config5_scans,
+            "ms_per_batch": ms5 / len(geo5),
+            "fps_ms": a5["fps/level=1"]["ms"] if "fps/level=1" in a5 else None,
+            "crop_ms": crop5["ms"] if crop5 else None,
+            "crop_frac": (crop5["bytes"] / (crop5["ms"] / 1e3) / 1e9 / hbm_peak_) if crop5 else None,
+            "gpu_launches_per_batch": g5.launches,
+            "features": "stand-in feature maps: one resident set shared by all batches; geometry distinct per scan",
+        }
+        del g5, static5, geo5, alone5
+        torch.cuda.empty_cache()
     clk = clocks.stop() if clocks else None
 
     # the only cross-rank step of the path: the final host gather of the host-consumed results (untimed)
@@ -530,12 +755,15 @@ def run_b200(args):
 
     def roof(o):
         default_cfg = args.batch == 16 and args.points == 16384 and not args.msg_radii
+        traffic, traffic_source = ncu_traffic(o["launch"], hf.build_id()) if default_cfg else (None, "not the default configuration")
         return {"kernel": o["launch"], "bound": o["bound"], "achieved": o["achieved"], "peak": o["peak"],
-                "unit": o["unit"], "frac": o["frac"], "traffic": ncu_traffic(o["launch"]) if default_cfg else None,
+                "unit": o["unit"], "frac": o["frac"], "traffic": traffic, "traffic_source": traffic_source,
                 "ms_per_launch": o["ms"],
                 "ms_per_launch_alone": o["ms_alone"], "frac_alone": o["frac_alone"],
                 "algorithmic_bytes": o["bytes"], "algorithmic_flops": o["flops"],
-                "peak_source": hbm_src if o["bound"] == "hbm" else "derived 148 SM x 128 lanes x 2 x 1.965 GHz (not measured)",
+                "peak_source": hbm_src if o["bound"] == "hbm" else
+                               "measured in this run: hf_fp32_probe, FFMA %.1f / FFMA2 %.1f TFLOP/s (derived 148 SM x 128 lanes x 2 x "
+                               "1.965 GHz = %.1f)" % (fp32["ffma"], fp32["ffma2"], fp32["derived"]),
                 "share_of_step": o["share_of_step"],
                 "note": "frac: this launch inside an overlapped step (issued eagerly right after the timed graph replays), where "
                         "it shares the GPU with the other 12 streams - the crop at the lowest priority; frac_alone: the same "
@@ -555,9 +783,12 @@ def run_b200(args):
         "roofline_ops": [{k: o[k] for k in ("launch", "bound", "ms", "ms_alone", "per_step", "achieved", "unit", "frac",
                                             "frac_alone", "share_of_step")} for o in ops],
         "serial_ms_per_step": serial_step_ms,
+        "fp32_peak": fp32,
+        "config5": config5,
+        "build": hf.version(),
     }
-    if not args.no_cpu_baseline:
-        cb, _ = time_cpu(args, cfg, host_np, 1, 0)
+    if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only
+        cb, _ = time_cpu(args, cfg, 1, 0, single_thread=True)
         line["cpu_baseline"] = cb
     if args.table:
         for o in ops:
@@ -573,31 +804,41 @@ def run_b200(args):
 
 NCU_KERNEL_OF = {  # probe name -> (kernel name fragment, grid) in the committed ncu --set full summary
     "pc_crop_and_sample/c=288": ("crop_kernel", "(8192, 1, 1)"),
-    "fps/level=1": ("fps_multi_ker", None),
+    "fps/level=1": ("fps_", None),
 }
 
 
-def ncu_traffic(launch):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `launch`, from the newest
-    profiles/r*_ncu_full_*_summary.csv (one ncu --set full capture of this same configuration,
-    tools/gpu_pass.sh + tools/ncu_summary.py); None if the kernel is not in it."""
+def ncu_traffic(launch, build_id):
+    """-> (dram__bytes_read.sum + dram__bytes_write.sum of one launch of `launch`, source description).
+
+    The figure comes from one `ncu --set full` capture of this same configuration (tools/gpu_pass.sh +
+    tools/ncu_summary.py -> profiles/r*_ncu_full_*_summary.csv, newest first).  A capture is only used if its first
+    line names the build it was taken from (`build=<id>`, heterofusionrcnn_b200/build.py:source_id) and that is the
+    library running now; otherwise traffic is None and the source says why - a stale figure is never printed next
+    to freshly timed numbers."""
     import csv
     import glob
+    import re
 
     if launch not in NCU_KERNEL_OF:
-        return None
+        return None, "no capture is kept for this launch"
     frag, grid = NCU_KERNEL_OF[launch]
-    import re
 
     def version(path):  # r<round>_ncu_full_v<pass>_summary.csv -> (round, pass): numeric, not lexicographic
         m = re.search(r"r(\d+)_ncu_full_v(\d+)_summary", os.path.basename(path))
         return (int(m.group(1)), int(m.group(2))) if m else (0, 0)
 
-    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_ncu_full_*_summary.csv")),
-                   key=version)
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_*_summary.csv")), key=version)
     if not files:
-        return None
-    rows = list(csv.reader(open(files[-1])))
+        return None, "no capture under profiles/"
+    path = files[-1]
+    rows = list(csv.reader(open(path)))
+    m = re.search(r"build=([0-9a-f]{12})", rows[0][0] if rows and rows[0] else "")
+    name = "profiles/" + os.path.basename(path)
+    if not m:
+        return None, "%s does not name its build (taken before builds carried an id): not used" % name
+    if m.group(1) != build_id:
+        return None, "%s is a capture of build %s, the library is build %s: not used" % (name, m.group(1), build_id)
     hdr, units = rows[1], rows[2]
     ci = {h: i for i, h in enumerate(hdr)}
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
@@ -606,8 +847,8 @@ def ncu_traffic(launch):
             tot = 0.0
             for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                 tot += float(r[ci[k]]) * scale[units[ci[k]]]
-            return tot
-    return None
+            return tot, "%s (ncu --set full of build %s, kernel %s grid %s)" % (name, build_id, r[ci["Kernel Name"]], r[ci["Grid Size"]])
+    return None, "%s holds no launch of %s with grid %s: not used" % (name, frag, grid)
 
 
 def main():

@@ -19,4 +19,14 @@ _os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 from ._lib import HfOpsError, InvalidArgumentError, launch_count, load  # noqa: F401
 
-__version__ = "0.1.0"
+__version__ = "0.2.0"
+
+
+def version():
+    """The native library's version string, e.g. 'hfops-b200 0.2.0 (sm_100a) build 1a2b3c4d5e6f'."""
+    return load().hf_version().decode()
+
+
+def build_id():
+    """The 12-hex-digit hash of the sources libhfops.so was built from (heterofusionrcnn_b200/build.py:source_id)."""
+    return version().rsplit(" ", 1)[-1]

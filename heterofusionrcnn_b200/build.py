@@ -37,11 +37,25 @@ def _stale():
     return any(os.path.getmtime(d) > built for d in deps if os.path.exists(d))
 
 
+def source_id():
+    """12 hex digits over every file the library is built from: hf_version() carries it, so a profile or a
+    measurement can name the exact build it was taken from (bench.py refuses ncu traffic of another build)."""
+    import hashlib
+
+    h = hashlib.sha256()
+    files = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(PKG_DIR, "..", "include", "hfops.h")]
+    for f in files:
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:12]
+
+
 def build(force=False, verbose=False):
     """Compile every CUDA source for sm_100a and link libhfops.so.  Returns the path."""
     if not force and not _stale():
         return LIB_PATH
     nvcc = _nvcc()
+    NVCC_FLAGS = globals()["NVCC_FLAGS"] + ['-DHF_BUILD_ID="%s"' % source_id()]
     objdir = os.path.join(PKG_DIR, "build")
     os.makedirs(objdir, exist_ok=True)
     procs = []

@@ -104,6 +104,64 @@ def to_device_from_pinned(pinned, device):
     return {k: [up(x) for x in v] if isinstance(v, list) else up(v) for k, v in pinned.items()}
 
 
+HOST_ORIGINATED = ("xyz", "intensity", "fg_mask", "crop_boxes", "box_ind", "nms_boxes")
+
+
+class InputArena:
+    """All input tensors of one step packed into ONE pinned host buffer, mirrored by device buffers of the same
+    layout: a step's host->device transfer is one cudaMemcpyAsync instead of one per tensor (14 for the default
+    chain).  The tensors a real caller holds on the host (scans, intensities, masks, boxes: HOST_ORIGINATED,
+    ~8 MB per 16 scans) come first, the stand-ins for the MLP feature maps (which the reference produces on the
+    device, hf/core/models/rcnn_model.py:478-489) after them, so either the whole arena or only the
+    host-originated prefix can be sent with a single copy."""
+
+    ALIGN = 256
+
+    def __init__(self, host, pin=True):
+        items = []
+        for k, v in host.items():
+            for i, a in (enumerate(v) if isinstance(v, list) else [(None, v)]):
+                if a is not None:
+                    items.append((k, i, np.ascontiguousarray(a)))
+        items.sort(key=lambda it: 0 if it[0] in HOST_ORIGINATED else 1)  # stable: host-originated first
+        self.layout, off, self.prefix = [], 0, 0
+        for k, i, a in items:
+            off = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+            self.layout.append((k, i, tuple(a.shape), torch.from_numpy(a[:0].copy() if a.size else a).dtype, off, a.nbytes))
+            off += a.nbytes
+            if k in HOST_ORIGINATED:
+                self.prefix = off
+        self.nbytes = (off + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.prefix = (self.prefix + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        self.lists = {k: len(v) for k, v in host.items() if isinstance(v, list)}
+        self.pinned = torch.empty((self.nbytes,), dtype=torch.uint8)
+        if pin:  # (pin=False: layout tests on a machine without a CUDA driver)
+            self.pinned = self.pinned.pin_memory()
+        flat = self.pinned.numpy()
+        for (k, i, shape, dt, o, nb), (_, _, a) in zip(self.layout, items):
+            flat[o:o + nb] = a.reshape(-1).view(np.uint8)
+
+    def device_buffer(self, device):
+        return torch.empty((self.nbytes,), dtype=torch.uint8, device=device)
+
+    def views(self, buf):
+        """dict of tensors (same structure as make_host_inputs) viewing `buf` (a host or device arena)."""
+        out = {k: [None] * n for k, n in self.lists.items()}
+        for k, i, shape, dt, o, nb in self.layout:
+            t = buf[o:o + nb].view(dt).view(shape)
+            if i is None:
+                out[k] = t
+            else:
+                out[k][i] = t
+        return out
+
+    def upload(self, dev_buf, host_originated_only=False):
+        """ONE asynchronous host->device copy on the current stream; returns the bytes sent."""
+        nb = self.prefix if host_originated_only else self.nbytes
+        dev_buf[:nb].copy_(self.pinned[:nb], non_blocking=True)
+        return nb
+
+
 def host_results(res, cfg):
     """The results of one chain pass that leave the device in the reference pipeline: index
     outputs the host consumes (proposal keep lists, sampled indices, counts, empty-box flags).
@@ -333,14 +391,22 @@ class ChainPipeline:
         self.inflight = [None] * self.depth
         self.k = 0
 
-    def submit(self, dev, probe=None):
-        slot = self.k % self.depth
-        self.k += 1
+    def next_slot(self):
+        return self.k % self.depth
+
+    def release(self, slot):
+        """Host-wait for the pass that used `slot` last and drop its tensors.  Call it before overwriting input
+        buffers that pass was reading (submit() calls it for its own slot)."""
         old = self.inflight[slot]
         if old is not None:
             for e in old[1]["_done"]:
                 e.synchronize()
             self.inflight[slot] = None
+
+    def submit(self, dev, probe=None):
+        slot = self.k % self.depth
+        self.k += 1
+        self.release(slot)
         res = run_chain(dev, self.cfg, probe, overlap=self.overlap, slot=slot, join=not self.overlap or self.depth == 1)
         self.inflight[slot] = (dev, res)  # the inputs stay referenced as long as the pass may read them
         return res

@@ -20,7 +20,10 @@ void set_error(const char *fmt, ...) {
 void count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 }  // namespace hf
 
-extern "C" const char *hf_version(void) { return "hfops-b200 0.1.0 (sm_100a)"; }
+#ifndef HF_BUILD_ID
+#define HF_BUILD_ID "unknown"
+#endif
+extern "C" const char *hf_version(void) { return "hfops-b200 0.2.0 (sm_100a) build " HF_BUILD_ID; }
 extern "C" const char *hf_last_error(void) { return hf::g_err; }
 extern "C" unsigned long long hf_launch_count(void) { return hf::g_launches.load(std::memory_order_relaxed); }
 

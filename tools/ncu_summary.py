@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Summarise an `ncu --set full` report into one CSV row per launch (the table kept under profiles/).
 
-    python tools/ncu_summary.py gpurun_out/v5_full.ncu-rep "comment line" > profiles/r1_ncu_full_v5_summary.csv
+    python tools/ncu_summary.py gpurun_out/v5_full.ncu-rep "comment line; build=<id from gpurun_out/<tag>_build.txt>" > profiles/r1_ncu_full_v5_summary.csv
 """
 import csv
 import io
