@@ -366,6 +366,7 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
         with on(s_fp), probe("three_interpolate", level=lvl + 1, b=b, n=n, m=m, c=c):
             out = three_interpolate(dev["fp_feats"][j], nidx, w)
         res["fp%d" % (lvl + 1)] = (dist, nidx, out)
+        res.setdefault("fp_weights", {})[lvl + 1] = w
     if overlap:
         done = [mark(s) for s in lanes.all()]
         if join:

@@ -74,12 +74,23 @@ def test_bench_chain_graph_matches_reference_kernels(cuda, oracle):
         rd, ri = _refcuda.three_nn(levels[lvl], levels[lvl + 1])
         assert torch.equal(nidx, ri), "three_nn idx level %d" % (lvl + 1)
         assert torch.equal(dist, rd), "three_nn dist level %d" % (lvl + 1)
-        # weights: hf/core/feature_extractors/pointnet_util.py:304-307 in float32 (torch ops on the reference distances)
+        # weights: hf/core/feature_extractors/pointnet_util.py:304-307 in float32 (torch ops on the reference
+        # distances); positive terms only, so 1e-5 relative per element is the north_star bar
         d = torch.clamp(rd, min=1e-10)
         w = (1.0 / d) / (1.0 / d).sum(dim=2, keepdim=True)
+        gw = res["fp_weights"][lvl + 1]
+        assert close(gw, w), "interpolation weights level %d" % (lvl + 1)
+        # interpolation: the reference kernel on the same indices and the same weights.  A row is a signed sum
+        # of three products, so the bound is 1e-5 of the magnitude of its terms (cancellation can leave a result
+        # far smaller than its rounding error); in practice the two kernels agree bit for bit.
         pts = dev["fp_feats"][j]
-        rout = _refcuda.three_interpolate_channel_first(pts.transpose(1, 2).contiguous(), ri, w.contiguous())
-        assert close(out, rout.transpose(1, 2)), "three_interpolate level %d" % (lvl + 1)
+        rout = _refcuda.three_interpolate_channel_first(pts.transpose(1, 2).contiguous(), ri, gw.contiguous())
+        rout = rout.transpose(1, 2)
+        mag = torch.zeros_like(out)
+        for k in range(3):
+            rows = torch.gather(pts, 1, ri[:, :, k].long()[:, :, None].expand(-1, -1, pts.shape[2]))
+            mag += (gw[:, :, k:k + 1] * rows).abs()
+        assert bool(torch.all((out - rout).abs() <= 1e-5 * mag + 1e-12)), "three_interpolate level %d" % (lvl + 1)
 
     # ---- NMS: reference mask kernel + the reference's host sweep, every scene of the batch ----
     keep, num = N(res["nms_keep"]), N(res["nms_num"])
