@@ -154,6 +154,11 @@ def work(name, m):
     """-> (bound, algorithmic bytes, algorithmic flops) of one launch."""
     if name == "fps":
         return "fp32", 12 * m["b"] * m["n"] + 4 * m["b"] * m["m"], 8 * m["b"] * (m["m"] - 1) * m["n"]
+    if name == "fps_pyramid":  # levels n -> ms[0] -> ms[1] ...: the FPS formula per level + the gathered points
+        ns = [m["n"]] + list(m["ms"])
+        by = sum(12 * m["b"] * ns[j] + 4 * m["b"] * ns[j + 1] + 28 * m["b"] * ns[j + 1] for j in range(len(ns) - 1))
+        fl = sum(8 * m["b"] * (ns[j + 1] - 1) * ns[j] for j in range(len(ns) - 1))
+        return "fp32", by, fl
     if name == "gather_point":
         return "hbm", 4 * m["b"] * m["m"] * 7, 0
     if name == "query_ball_point":

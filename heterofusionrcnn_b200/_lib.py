@@ -29,6 +29,8 @@ SIGNATURES = {
     "hf_fp32_probe_flops": (ctypes.c_double, [_c_int, _c_int, _c_int]),
     "hf_fp32_probe": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr]),
     "hf_farthest_point_sample": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
+    "hf_farthest_point_sample_xyz": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "hf_fps_pyramid": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_fps_set_cluster": (None, [_c_int]),
     "hf_fps_set_threads": (None, [_c_int]),
     "hf_fps_set_variant": (None, [_c_int, _c_int, _c_int]),
@@ -56,6 +58,7 @@ SIGNATURES = {
     "hf_three_nn_weights": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_knn_workspace_bytes": (_size_t, [_c_int, _c_int, _c_int]),
     "hf_knn_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_knn_indices_general": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
     "hf_select_top_k": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_boxes3d_to_bev": (_c_int, [ctypes.c_longlong, _ptr, _ptr, _ptr]),
     "hf_boxes3d_to_corners": (_c_int, [ctypes.c_longlong, _ptr, _c_float, _ptr, _ptr]),

@@ -23,7 +23,8 @@ from .bev_iou.bev_iou import oriented_nms_batch
 from .cropping.tf_cropping import pc_crop_and_sample
 from .grouping.tf_grouping import group_point, query_ball_point
 from .interpolate.tf_interpolate import three_interpolate, three_nn_weights
-from .sampling.tf_sampling import farthest_point_sample, gather_point
+from .sampling.tf_sampling import (PYRAMID_MAX_LEVELS, farthest_point_sample, farthest_point_sample_pyramid,
+                                   farthest_point_sample_with_xyz, gather_point)
 
 
 @dataclass
@@ -42,6 +43,9 @@ class ChainConfig:
     post_nms: int = 512
     with_crop: bool = True
     with_nms: bool = True
+    # sampling spine: level 1 = one launch that writes the indices AND the picked points; levels 2-4 = one launch
+    # (fps pyramid).  False = the reference's op sequence, farthest_point_sample + gather_point per level (8 launches).
+    fused_sampling: bool = True
 
     def scaled(self, points):
         """Same chain on a different cloud size (npoint = n/4 per level)."""
@@ -282,14 +286,31 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
     ns = cfg.nsample
 
     def sample_level(l):
+        """Sampling of SA level l (0-based) on the critical lane; returns the event after which xyz[l + 1] exists.
+        With fused_sampling, level 0 is one launch (indices + picked points) and the call for level 1 samples ALL
+        remaining levels in one launch (their events are the same one)."""
         n, m = n_lv[l], n_lv[l + 1]
+        if len(xyz) > l + 1:  # already produced by the pyramid launch of level 1
+            return have_xyz[l - 1]
         with on(crit):
-            with probe("fps", level=l + 1, b=b, n=n, m=m):
-                idx = farthest_point_sample(m, xyz[l])
-            with probe("gather_point", level=l + 1, b=b, n=n, m=m):
-                new_xyz = gather_point(xyz[l], idx)
-        fps_idx.append(idx)
-        xyz.append(new_xyz)
+            if not cfg.fused_sampling:
+                with probe("fps", level=l + 1, b=b, n=n, m=m):
+                    idx = farthest_point_sample(m, xyz[l])
+                with probe("gather_point", level=l + 1, b=b, n=n, m=m):
+                    new_xyz = gather_point(xyz[l], idx)
+                fps_idx.append(idx)
+                xyz.append(new_xyz)
+            elif l == 0 or len(n_lv) - 1 - l > PYRAMID_MAX_LEVELS:
+                with probe("fps", level=l + 1, b=b, n=n, m=m, xyz=1):
+                    idx, new_xyz = farthest_point_sample_with_xyz(m, xyz[l])
+                fps_idx.append(idx)
+                xyz.append(new_xyz)
+            else:
+                ms = n_lv[l + 1:]
+                with probe("fps_pyramid", level=l + 1, b=b, n=n, ms=tuple(ms)):
+                    idxs, pts = farthest_point_sample_pyramid(ms, xyz[l])
+                fps_idx.extend(idxs)
+                xyz.extend(pts)
         return mark(crit)
 
     # The sampling chain is the spine of the step: its first (longest) launch goes out before anything else,
@@ -366,7 +387,7 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
         with on(s_fp), probe("three_interpolate", level=lvl + 1, b=b, n=n, m=m, c=c):
             out = three_interpolate(dev["fp_feats"][j], nidx, w)
         res["fp%d" % (lvl + 1)] = (dist, nidx, out)
-        res.setdefault("fp_weights", {})[lvl + 1] = w
+        res.setdefault("fp_weights", [None] * 4)[lvl] = w
     if overlap:
         done = [mark(s) for s in lanes.all()]
         if join:
@@ -459,4 +480,5 @@ def chain_launches(cfg):
     n_lv = [cfg.points] + list(cfg.npoint)
     use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
     indexed = [use_ix[l] or (l > 0 and use_ix[l - 1]) for l in range(4)] + [use_ix[3]]
-    return 4 * 5 + 4 * 2 + sum(indexed) + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)
+    sampling = 2 if cfg.fused_sampling else 8  # fps+xyz of level 1 and the pyramid of levels 2-4 / fps + gather per level
+    return sampling + 4 * 3 + 4 * 2 + sum(indexed) + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)

@@ -89,29 +89,40 @@ __device__ __forceinline__ uint32_t mp_tie_decode(uint32_t lo) {
 //     PointNet++ stack sample a cloud that is already in FPS order, where the picks are
 //     0, 1, 2, ...; were they in the same warp, its one candidate per round would allow a
 //     single pick per round.
-template <int C, int W, int PTS>
-__global__ void __launch_bounds__(W * 32, 1)
-    fps_multi_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out) {
+// Shared-memory state of one cluster CTA that survives from one FPS level to the next.
+template <int G, int W>
+struct MpShared {
+    uint32_t slots[2][G][MP_SLOT_W];  // {x, y, z, sec | tie word, td bits, -, -}
+    uint64_t bars[2];
+    uint8_t pos[W][8];  // per warp: rank -> slot of the top 8 candidates
+};
+
+// One FPS level (n points -> m picks) run by a whole cluster.  `load(k)` returns point k of the level's cloud
+// (global memory for the first level of a launch, the previous level's picks in shared memory afterwards).
+//   idxs    (m) global: the picked indices                                         [written by CTA 0]
+//   oxyz    (m,3) global or null: the picked points = gather_point(inp, idxs)       [written by CTA 0]
+//   nxt     (m,3) shared or null: the same, a full copy in EVERY CTA (the next level's cloud)
+// `round` is the cluster-wide exchange round counter: it runs on across the levels of one launch, so the two
+// mbarriers keep their phase (each is armed for round + 2 right after it completed for round).
+template <int C, int W, int PTS, class Load>
+__device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__restrict__ idxs,
+                                                float *__restrict__ oxyz, float *nxt, float *sx,
+                                                MpShared<C * W, W> &sh, int &round) {
     constexpr int T = W * 32, TT = C * T, S = TT < 512 ? 512 / TT : 1, R = TT >= 512 ? TT / 512 : 1, Q = PTS / S;
     constexpr int G = C * W, NC = (G + 31) / 32;
     static_assert(PTS % S == 0 && Q >= 1, "PTS must be a multiple of the residues per thread");
+    static_assert(TT % 512 == 0 || 512 % TT == 0, "cluster threads must divide or be a multiple of 512");
     static_assert(G <= 64, "at most 64 warps per scene");
     static_assert(PTS <= 32, "the equal-to-max mask is 32 bits");
     constexpr int CAP = T * PTS;  // points held by one CTA
-
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float *sx = reinterpret_cast<float *>(smem_raw);
     float *sy = sx + CAP;
     float *sz = sy + CAP;
-    __shared__ __align__(16) uint32_t slots[2][G][MP_SLOT_W];  // {x, y, z, sec | tie word, td bits, -, -}
-    __shared__ __align__(8) uint64_t bars[2];
-    __shared__ __align__(8) uint8_t pos[W][8];  // per warp: rank -> slot of the top 8 candidates
+    auto &slots = sh.slots;
+    auto &bars = sh.bars;
+    auto &pos = sh.pos;
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t rank = C > 1 ? mp_ctarank() : 0u;
-    const int scene = blockIdx.x / C;
-    const float *data = inp + (size_t)scene * n * 3;
-    int *idxs = out + (size_t)scene * m;
     const uint32_t grp = rank * W + warp;  // this warp's group = its slot number
     // point held in register p of the thread with slot u
     auto kof = [](uint32_t u, int p) -> uint32_t {
@@ -125,9 +136,10 @@ __global__ void __launch_bounds__(W * 32, 1)
         const int li = p * T + t;  // local copy, conflict free
         const uint32_t k = kof(u, p);
         if (k < (uint32_t)n) {
-            x[p] = data[(size_t)k * 3 + 0];
-            y[p] = data[(size_t)k * 3 + 1];
-            z[p] = data[(size_t)k * 3 + 2];
+            const float3 v = load(k);
+            x[p] = v.x;
+            y[p] = v.y;
+            z[p] = v.z;
             td[p] = 1e38f;  // tf_sampling_g.cu:118
         } else {
             x[p] = y[p] = z[p] = 0.f;
@@ -137,23 +149,30 @@ __global__ void __launch_bounds__(W * 32, 1)
         sy[li] = y[p];
         sz[li] = z[p];
     }
-    for (int i = t; i < 2 * G * MP_SLOT_W; i += T) (&slots[0][0][0])[i] = 0u;
     if (lane < 8) pos[warp][lane] = 0;
+    const float3 first = load(0);  // every thread reads it BEFORE the barrier: `nxt` may alias the cloud `load` reads
     __syncthreads();
     if (t == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
-        mbar_fence_init();
-        mbar_arrive_expect_tx(&bars[0], G * MP_MSG);
-        mbar_arrive_expect_tx(&bars[1], G * MP_MSG);
-        // round 0 reads its single centre (point 0, tf_sampling_g.cu:114-116) like any other round
-        slots[1][0][0] = __float_as_uint(data[0]);
-        slots[1][0][1] = __float_as_uint(data[1]);
-        slots[1][0][2] = __float_as_uint(data[2]);
+        // round 0 of the level reads its single centre (point 0, tf_sampling_g.cu:114-116) like any other round
+        uint32_t *c0 = slots[(round & 1) ^ 1][0];
+        c0[0] = __float_as_uint(first.x);
+        c0[1] = __float_as_uint(first.y);
+        c0[2] = __float_as_uint(first.z);
+        if (nxt) {
+            nxt[0] = first.x;
+            nxt[1] = first.y;
+            nxt[2] = first.z;
+        }
+        if (rank == 0) {
+            idxs[0] = 0;
+            if (oxyz) {
+                oxyz[0] = first.x;
+                oxyz[1] = first.y;
+                oxyz[2] = first.z;
+            }
+        }
     }
-    if (rank == 0 && t == 0) idxs[0] = 0;
-    if (C > 1) mp_cluster_sync();
-    else __syncthreads();
+    __syncthreads();
 
     // lane c < C pushes to CTA c: remote address of this warp's slot (buffer 0) and of barrier 0 there
     const uint32_t rslot = mp_mapa(smem_u32(&slots[0][grp][0]), (uint32_t)(lane % C));
@@ -170,7 +189,7 @@ __global__ void __launch_bounds__(W * 32, 1)
 
     uint64_t posw = 0;  // the 8 bytes of pos[warp]: slot of the candidate of rank 0..7
     int A = 1, done = 1;
-    for (int round = 0; done < m; ++round) {
+    for (; done < m; ++round) {
         const int buf = round & 1;
         const uint32_t(*cs)[MP_SLOT_W] = slots[buf ^ 1];  // centres accepted last round
         // ---- 1. lower td against the A new centres, two at a time (min is exact in any order) ----
@@ -285,22 +304,113 @@ __global__ void __launch_bounds__(W * 32, 1)
             A = vm ? row : MP_K;
             A = min(A, m - done);
         }
-        // ---- 4. emit ----
-        if (rank == 0 && warp == 0 && lane < A)
-            idxs[done + lane] = (int)mp_tie_decode(sl[(uint32_t)(posw >> (8 * lane)) & 0xffu][4]);
+        // ---- 4. emit: index and coordinates (the slot carries them) of the A accepted picks ----
+        if (warp == 0 && lane < A) {
+            const uint32_t *w = sl[(uint32_t)(posw >> (8 * lane)) & 0xffu];
+            if (nxt) {
+                float *o = nxt + 3 * (done + lane);
+                o[0] = __uint_as_float(w[0]);
+                o[1] = __uint_as_float(w[1]);
+                o[2] = __uint_as_float(w[2]);
+            }
+            if (rank == 0) {
+                idxs[done + lane] = (int)mp_tie_decode(w[4]);
+                if (oxyz) {
+                    float *o = oxyz + 3 * (size_t)(done + lane);
+                    o[0] = __uint_as_float(w[0]);
+                    o[1] = __uint_as_float(w[1]);
+                    o[2] = __uint_as_float(w[2]);
+                }
+            }
+        }
         done += A;
+    }
+}
+
+// Set-up shared by the kernels below: slots cleared, both mbarriers armed for their first round.
+template <int C, int W>
+__device__ __forceinline__ void mp_setup(MpShared<C * W, W> &sh) {
+    constexpr int G = C * W, T = W * 32;
+    const int t = threadIdx.x;
+    for (int i = t; i < 2 * G * MP_SLOT_W; i += T) (&sh.slots[0][0][0])[i] = 0u;
+    if (t == 0) {
+        mbar_init(&sh.bars[0], 1);
+        mbar_init(&sh.bars[1], 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(&sh.bars[0], G * MP_MSG);
+        mbar_arrive_expect_tx(&sh.bars[1], G * MP_MSG);
+    }
+    __syncthreads();
+    if (C > 1) mp_cluster_sync();  // nobody pushes into a CTA whose barriers are not armed yet
+}
+
+// One level: farthest_point_sample (+ gather_point when new_xyz != null).
+template <int C, int W, int PTS>
+__global__ void __launch_bounds__(W * 32, 1)
+    fps_multi_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out, float *__restrict__ new_xyz) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ __align__(16) MpShared<C * W, W> sh;
+    const int scene = blockIdx.x / C;
+    const float *data = inp + (size_t)scene * n * 3;
+    mp_setup<C, W>(sh);
+    int round = 0;
+    fps_multi_level<C, W, PTS>(
+        n, m, [data](uint32_t k) { return make_float3(data[(size_t)k * 3], data[(size_t)k * 3 + 1], data[(size_t)k * 3 + 2]); },
+        out + (size_t)scene * m, new_xyz ? new_xyz + (size_t)scene * m * 3 : nullptr, nullptr,
+        reinterpret_cast<float *>(smem_raw), sh, round);
+    if (C > 1) mp_cluster_sync();  // no CTA may exit while peers can still push into it
+}
+
+// The lower levels of a sampling pyramid in ONE launch: level j samples the picks of level j-1, which every CTA of
+// the cluster already holds in shared memory (each accepted centre reaches every CTA through the exchange), so
+// neither the clouds nor the indices go through HBM between levels and the launches + gathers between them
+// disappear (hf/core/feature_extractors/pointnet_util.py:42-44 runs farthest_point_sample + gather_point per
+// SA level; levels 2..4 of the RPN chain are 4096 -> 1024 -> 256 -> 64).  Level j keeps PTS >> 2j points per thread.
+struct PyramidArgs {
+    int levels;     // 1..3
+    int n;          // points of the input cloud
+    int m[3];       // picks per level, m[j] <= points of level j
+    const float *inp;
+    int *idx[3];    // (b, m[j]) each
+    float *xyz[3];  // (b, m[j], 3) each
+};
+
+template <int C, int W, int P0>
+__global__ void __launch_bounds__(W * 32, 1) fps_pyramid_kernel(PyramidArgs a) {
+    constexpr int P1 = P0 >= 4 ? P0 / 4 : 1, P2 = P1 >= 4 ? P1 / 4 : 1;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ __align__(16) MpShared<C * W, W> sh;
+    float *sx = reinterpret_cast<float *>(smem_raw);       // 3 * T * P0 floats: this CTA's part of the level's cloud
+    float *cloud = sx + 3 * W * 32 * P0;                   // 3 * m[0] floats: the picks of the level = the next cloud
+    const int scene = blockIdx.x / C;
+    const float *data = a.inp + (size_t)scene * a.n * 3;
+    mp_setup<C, W>(sh);
+    int round = 0;
+    fps_multi_level<C, W, P0>(
+        a.n, a.m[0], [data](uint32_t k) { return make_float3(data[(size_t)k * 3], data[(size_t)k * 3 + 1], data[(size_t)k * 3 + 2]); },
+        a.idx[0] + (size_t)scene * a.m[0], a.xyz[0] + (size_t)scene * a.m[0] * 3, a.levels > 1 ? cloud : nullptr, sx, sh, round);
+    auto from_smem = [cloud](uint32_t k) { return make_float3(cloud[3 * k], cloud[3 * k + 1], cloud[3 * k + 2]); };
+    if (a.levels > 1) {
+        if (C > 1) mp_cluster_sync();  // every CTA is out of the level: its slots and staging arrays can be reused
+        else __syncthreads();
+        fps_multi_level<C, W, P1>(a.m[0], a.m[1], from_smem, a.idx[1] + (size_t)scene * a.m[1],
+                                  a.xyz[1] + (size_t)scene * a.m[1] * 3, a.levels > 2 ? cloud : nullptr, sx, sh, round);
+    }
+    if (a.levels > 2) {
+        if (C > 1) mp_cluster_sync();
+        else __syncthreads();
+        fps_multi_level<C, W, P2>(a.m[1], a.m[2], from_smem, a.idx[2] + (size_t)scene * a.m[2],
+                                  a.xyz[2] + (size_t)scene * a.m[2] * 3, nullptr, sx, sh, round);
     }
     if (C > 1) mp_cluster_sync();  // no CTA may exit while peers can still push into it
 }
 
-template <int C, int W, int PTS>
-int launch_fps_multi(int b, int n, int m, const float *inp, int *out, cudaStream_t stream) {
-    auto kern = fps_multi_kernel<C, W, PTS>;
-    const size_t smem = (size_t)3 * W * 32 * PTS * sizeof(float);
+template <class Kern, class... Args>
+int launch_cluster(Kern kern, const char *name, int b, int C, int threads, size_t smem, cudaStream_t stream, Args... args) {
     if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)b * C);
-    cfg.blockDim = dim3(W * 32);
+    cfg.blockDim = dim3(threads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -310,32 +420,44 @@ int launch_fps_multi(int b, int n, int m, const float *inp, int *out, cudaStream
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    HF_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, n, m, inp, out));
-    HF_LAUNCH_OK("fps_multi_kernel");
+    HF_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, args...));
+    HF_LAUNCH_OK(name);
     return HF_OK;
 }
 
+template <int C, int W, int PTS>
+int launch_fps_multi(int b, int n, int m, const float *inp, int *out, float *new_xyz, cudaStream_t stream) {
+    return launch_cluster(fps_multi_kernel<C, W, PTS>, "fps_multi_kernel", b, C, W * 32, (size_t)3 * W * 32 * PTS * sizeof(float),
+                          stream, n, m, inp, out, new_xyz);
+}
+
+template <int C, int W, int P0>
+int launch_fps_pyramid(int b, const PyramidArgs &a, cudaStream_t stream) {
+    const size_t smem = ((size_t)3 * W * 32 * P0 + (size_t)3 * a.m[0]) * sizeof(float);
+    return launch_cluster(fps_pyramid_kernel<C, W, P0>, "fps_pyramid_kernel", b, C, W * 32, smem, stream, a);
+}
+
 template <int C>
-int dispatch_multi(int per, int warps, int b, int n, int m, const float *inp, int *out, cudaStream_t s) {
+int dispatch_multi(int per, int warps, int b, int n, int m, const float *inp, int *out, float *oxyz, cudaStream_t s) {
     // warps per CTA: 4 by default (one per scheduler: the shortest latency chain); 8 / 16 put the same
     // number of groups on half / a quarter of the SMs (hf_fps_set_variant(3, warps, 0)).
     if constexpr (C <= 4) {
       if (warps == 8 && per <= 4096) {
-        if (per <= 2048) return launch_fps_multi<C, 8, 8>(b, n, m, inp, out, s);
-        return launch_fps_multi<C, 8, 16>(b, n, m, inp, out, s);
+        if (per <= 2048) return launch_fps_multi<C, 8, 8>(b, n, m, inp, out, oxyz, s);
+        return launch_fps_multi<C, 8, 16>(b, n, m, inp, out, oxyz, s);
       }
     }
     if constexpr (C <= 2) {
       if (warps == 16 && per <= 8192) {
-        if (per <= 4096) return launch_fps_multi<C, 16, 8>(b, n, m, inp, out, s);
-        return launch_fps_multi<C, 16, 16>(b, n, m, inp, out, s);
+        if (per <= 4096) return launch_fps_multi<C, 16, 8>(b, n, m, inp, out, oxyz, s);
+        return launch_fps_multi<C, 16, 16>(b, n, m, inp, out, oxyz, s);
       }
     }
-    if (per <= 512) return launch_fps_multi<C, 4, 4>(b, n, m, inp, out, s);
-    if (per <= 1024) return launch_fps_multi<C, 4, 8>(b, n, m, inp, out, s);
-    if (per <= 2048) return launch_fps_multi<C, 4, 16>(b, n, m, inp, out, s);
-    if (per <= 4096) return launch_fps_multi<C, 4, 32>(b, n, m, inp, out, s);
-    if (per <= 8192) return launch_fps_multi<C, 8, 32>(b, n, m, inp, out, s);
+    if (per <= 512) return launch_fps_multi<C, 4, 4>(b, n, m, inp, out, oxyz, s);
+    if (per <= 1024) return launch_fps_multi<C, 4, 8>(b, n, m, inp, out, oxyz, s);
+    if (per <= 2048) return launch_fps_multi<C, 4, 16>(b, n, m, inp, out, oxyz, s);
+    if (per <= 4096) return launch_fps_multi<C, 4, 32>(b, n, m, inp, out, oxyz, s);
+    if (per <= 8192) return launch_fps_multi<C, 8, 32>(b, n, m, inp, out, oxyz, s);
     return HF_ERR_UNSUPPORTED;
 }
 
@@ -345,7 +467,7 @@ int dispatch_multi(int per, int warps, int b, int n, int m, const float *inp, in
 // 1 CTA up to 512 points, 2 up to 2048, 4 up to 4096, else 8; halved while the batch would not
 // fit the GPU in one wave and a CTA still holds <= 4096 points.  Returns HF_ERR_UNSUPPORTED
 // for clouds beyond 8 x 8192 points.
-int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req, int warps_req) {
+int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *oxyz, cudaStream_t s, int cluster_req, int warps_req) {
     int cluster = 1;
     if (cluster_req == 1 || cluster_req == 2 || cluster_req == 4 || cluster_req == 8) {
         cluster = cluster_req;
@@ -363,13 +485,56 @@ int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStre
             warps_req = 8;
         }
     }
+    // 6 CTAs x 8 warps x 11 points: 16 scans of 16384 points need 96 SMs and 16 clusters of 6 fit the GPCs of a
+    // B200 at one CTA per SM, which 16 clusters of 8 do not (tools/gpc_probe.cu).  Opt-in: hf_fps_set_cluster(6).
+    if (cluster_req == 6) {
+        if (n > 6 * 256 * 11) return HF_ERR_UNSUPPORTED;
+        if (n <= 6 * 256 * 3) return launch_fps_multi<6, 8, 3>(b, n, m, inp, out, oxyz, s);
+        return launch_fps_multi<6, 8, 11>(b, n, m, inp, out, oxyz, s);
+    }
     while (cluster < 8 && (n + cluster - 1) / cluster > 8192) cluster <<= 1;
     const int per = (n + cluster - 1) / cluster;
     switch (cluster) {
-        case 1: return dispatch_multi<1>(per, warps_req, b, n, m, inp, out, s);
-        case 2: return dispatch_multi<2>(per, warps_req, b, n, m, inp, out, s);
-        case 4: return dispatch_multi<4>(per, warps_req, b, n, m, inp, out, s);
-        default: return dispatch_multi<8>(per, warps_req, b, n, m, inp, out, s);
+        case 1: return dispatch_multi<1>(per, warps_req, b, n, m, inp, out, oxyz, s);
+        case 2: return dispatch_multi<2>(per, warps_req, b, n, m, inp, out, oxyz, s);
+        case 4: return dispatch_multi<4>(per, warps_req, b, n, m, inp, out, oxyz, s);
+        default: return dispatch_multi<8>(per, warps_req, b, n, m, inp, out, oxyz, s);
+    }
+}
+
+
+// Levels 2.. of a sampling pyramid in one launch (fps_pyramid_kernel).  HF_ERR_UNSUPPORTED when no instantiation
+// holds the shape: the caller falls back to one launch per level.
+int fps_pyramid_dispatch(int b, int levels, int n, const int *m, const float *inp, int *const *idx, float *const *xyz,
+                         cudaStream_t s) {
+    if (levels < 1 || levels > 3 || n > 16384) return HF_ERR_UNSUPPORTED;
+    PyramidArgs a = {};
+    a.levels = levels;
+    a.n = n;
+    a.inp = inp;
+    for (int j = 0; j < levels; ++j) {
+        a.m[j] = m[j];
+        a.idx[j] = idx[j];
+        a.xyz[j] = xyz[j];
+    }
+    int tt, p0;
+    if (n <= 4096) {
+        tt = 512;
+        p0 = n <= 512 ? 1 : n <= 1024 ? 2 : n <= 2048 ? 4 : 8;
+    } else {
+        tt = 1024;
+        p0 = 16;
+    }
+    const int p1 = p0 >= 4 ? p0 / 4 : 1, p2 = p1 >= 4 ? p1 / 4 : 1;
+    if (levels > 1 && m[0] > tt * p1) return HF_ERR_UNSUPPORTED;
+    if (levels > 2 && m[1] > tt * p2) return HF_ERR_UNSUPPORTED;
+    if (m[0] > 8192) return HF_ERR_UNSUPPORTED;  // the picks of the first level are staged in shared memory
+    if (tt == 1024) return b > 15 ? launch_fps_pyramid<4, 8, 16>(b, a, s) : launch_fps_pyramid<8, 4, 16>(b, a, s);
+    switch (p0) {
+        case 1: return launch_fps_pyramid<4, 4, 1>(b, a, s);
+        case 2: return launch_fps_pyramid<4, 4, 2>(b, a, s);
+        case 4: return launch_fps_pyramid<4, 4, 4>(b, a, s);
+        default: return launch_fps_pyramid<4, 4, 8>(b, a, s);
     }
 }
 

@@ -22,7 +22,9 @@ namespace hf {
 // fps_bucket.cu: the bucket-pruned kernel (default for clouds it covers)
 int fps_bucket_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int w_req, int j_req);
 // fps_multi.cu: the multi-pick kernel (default for clouds of up to 65536 points)
-int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, cudaStream_t s, int cluster_req, int warps_req);
+int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *oxyz, cudaStream_t s, int cluster_req, int warps_req);
+int fps_pyramid_dispatch(int b, int levels, int n, const int *m, const float *inp, int *const *idx, float *const *xyz,
+                         cudaStream_t s);
 
 namespace {
 
@@ -339,9 +341,21 @@ extern "C" void hf_fps_set_variant(int algo, int warps, int buckets_per_warp) {
     hf::g_bucket_j = buckets_per_warp;
 }
 
-extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
-                                        hf_stream_t stream) {
-    using namespace hf;
+namespace hf {
+namespace {
+int gather_point_launch(int b, int n, int m, const float *inp, const int *idx, float *out, cudaStream_t s) {
+    long long total = (long long)b * m;
+    if (total == 0) return HF_OK;
+    int threads = 256;
+    long long blocks = (total + threads - 1) / threads;
+    gather_point_kernel<<<(unsigned)blocks, threads, 0, s>>>(total, n, m, inp, idx, out);
+    HF_LAUNCH_OK("gather_point_kernel");
+    return HF_OK;
+}
+
+// FPS of one level; oxyz (b,m,3) != null also receives the picked points (= gather_point(inp, out)): the
+// multi-pick kernel writes them next to the indices, the other kernels are followed by a gather launch.
+int fps_any(int b, int n, int m, const float *inp, float *temp, int *out, float *oxyz, hf_stream_t stream) {
     HF_REQUIRE(b >= 0 && n >= 1, "FarthestPointSample expects (batch_size,num_points,3) inp shape");
     HF_REQUIRE(m > 0, "FarthestPointSample expects positive npoint");
     HF_REQUIRE(inp && out, "FarthestPointSample: null pointer");
@@ -356,6 +370,7 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
         int rc = fps_bucket_dispatch(b, n, m, inp, out, s, g_bucket_w, g_bucket_j);
         if (rc == HF_ERR_UNSUPPORTED)
             set_error("FarthestPointSample: bucket kernel has no shape for n=%d warps=%d buckets/warp=%d", n, g_bucket_w, g_bucket_j);
+        if (rc == HF_OK && oxyz) rc = gather_point_launch(b, n, m, inp, out, oxyz, s);
         return rc;
     }
 
@@ -363,7 +378,7 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
     // DSMEM exchange.  algo 1 = the one-pick-per-exchange cluster kernel below, which also
     // serves clouds the multi-pick kernel has no shape for.
     if (g_algo == 0 || g_algo == 3) {
-        int rc = fps_multi_dispatch(b, n, m, inp, out, s, g_cluster_override, g_algo == 3 ? g_bucket_w : 0);
+        int rc = fps_multi_dispatch(b, n, m, inp, out, oxyz, s, g_cluster_override, g_algo == 3 ? g_bucket_w : 0);
         if (rc != HF_ERR_UNSUPPORTED) return rc;
         if (g_algo == 3) {
             set_error("FarthestPointSample: multi-pick kernel has no shape for n=%d", n);
@@ -391,7 +406,7 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
         int grid = b < 32 ? b : 32;
         fps_global_kernel<<<grid, 1024, 0, s>>>(b, n, m, inp, temp, out);
         HF_LAUNCH_OK("fps_global_kernel");
-        return HF_OK;
+        return oxyz ? gather_point_launch(b, n, m, inp, out, oxyz, s) : HF_OK;
     }
     int rc;
     switch (cluster) {
@@ -400,7 +415,52 @@ extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, f
         case 4: rc = dispatch_pts<4>(per, b, n, m, inp, out, s); break;
         default: rc = dispatch_pts<8>(per, b, n, m, inp, out, s); break;
     }
+    if (rc == HF_OK && oxyz) rc = gather_point_launch(b, n, m, inp, out, oxyz, s);
     return rc;
+}
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
+                                        hf_stream_t stream) {
+    return hf::fps_any(b, n, m, inp, temp, out, nullptr, stream);
+}
+
+extern "C" int hf_farthest_point_sample_xyz(int b, int n, int m, const float *inp, float *temp, int *out,
+                                            float *new_xyz, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(new_xyz != nullptr, "FarthestPointSample: new_xyz is null");
+    return fps_any(b, n, m, inp, temp, out, new_xyz, stream);
+}
+
+extern "C" int hf_fps_pyramid(int b, int levels, int n, const int *m, const float *inp, int *const *idx,
+                              float *const *new_xyz, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(b >= 0 && n >= 1, "FarthestPointSample expects (batch_size,num_points,3) inp shape");
+    HF_REQUIRE(levels >= 1 && levels <= HF_FPS_PYRAMID_MAX_LEVELS && m && idx && new_xyz, "fps_pyramid: 1..%d levels",
+               HF_FPS_PYRAMID_MAX_LEVELS);
+    HF_REQUIRE(inp != nullptr, "FarthestPointSample: null pointer");
+    for (int j = 0; j < levels; ++j) {
+        HF_REQUIRE(m[j] > 0, "FarthestPointSample expects positive npoint");
+        HF_REQUIRE(idx[j] && new_xyz[j], "fps_pyramid: null output pointer at level %d", j);
+    }
+    if (b == 0) return HF_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (g_algo == 0 || g_algo == 3) {
+        const int rc = fps_pyramid_dispatch(b, levels, n, m, inp, idx, new_xyz, s);
+        if (rc != HF_ERR_UNSUPPORTED) return rc;
+    }
+    // no single-launch shape (or another FPS variant was asked for): level by level, each on the previous level's picks
+    const float *cloud = inp;
+    int pts = n;
+    for (int j = 0; j < levels; ++j) {
+        HF_REQUIRE(pts <= 65536, "fps_pyramid: clouds beyond 65536 points need the temp buffer of hf_farthest_point_sample");
+        const int rc = fps_any(b, pts, m[j], cloud, nullptr, idx[j], new_xyz[j], stream);
+        if (rc != HF_OK) return rc;
+        cloud = new_xyz[j];
+        pts = m[j];
+    }
+    return HF_OK;
 }
 
 extern "C" int hf_gather_point(int b, int n, int m, const float *inp, const int *idx, float *out,
@@ -408,11 +468,5 @@ extern "C" int hf_gather_point(int b, int n, int m, const float *inp, const int 
     using namespace hf;
     HF_REQUIRE(b >= 0 && n >= 1 && m >= 0, "GatherPoint expects (batch_size,num_points,3) inp shape");
     HF_REQUIRE(inp && idx && out, "GatherPoint: null pointer");
-    long long total = (long long)b * m;
-    if (total == 0) return HF_OK;
-    int threads = 256;
-    long long blocks = (total + threads - 1) / threads;
-    gather_point_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(total, n, m, inp, idx, out);
-    HF_LAUNCH_OK("gather_point_kernel");
-    return HF_OK;
+    return gather_point_launch(b, n, m, inp, idx, out, (cudaStream_t)stream);
 }

@@ -592,9 +592,9 @@ template <int R, bool INDEXED>
 __global__ void __launch_bounds__(kSqWarps * 32)
     knn_kernel(int n, int m, int k, int nq, int nbc, const float *__restrict__ xyzQ, const float *__restrict__ xyzC,
                const float4 *__restrict__ sortedQ, const float4 *__restrict__ sortedC, const float4 *__restrict__ boxesC,
-               float *__restrict__ val, int *__restrict__ idx) {
+               float *__restrict__ val, int *__restrict__ idx, int pairs) {
     constexpr unsigned long long kNone = ~0ull;
-    constexpr int kMaxLb = kMaxIndexed / 32 / 32;  // candidate buckets per lane
+    constexpr int kMaxLb = kMaxIndexed / 32 / 32;  // candidate buckets per lane and pass
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int scene = blockIdx.y;
     const int p = blockIdx.x * kSqWarps + warp;  // query slot (curve order when INDEXED)
@@ -649,59 +649,68 @@ __global__ void __launch_bounds__(kSqWarps * 32)
             offer(cx, cy, cz, j < n ? j : -1);
         }
     } else {
-        // exact lower bound of every candidate bucket for this query; visited in ascending order of it
-        float lb[kMaxLb];
+        // exact lower bound of every candidate bucket for this query; visited in ascending order of it.  A cloud of
+        // more than kMaxIndexed points (indexed in parts, see cloud_index_kernel) is searched in passes of
+        // kMaxLb * 32 buckets: within a pass every bucket whose bound can still beat the k-th best is visited, and the
+        // k-th best carries over, so the result is that of one pass over all buckets.
+        for (int base = 0; base < nbc; base += kMaxLb * 32) {
+            float lb[kMaxLb];
 #pragma unroll
-        for (int u = 0; u < kMaxLb; ++u) {
-            const int cb = u * 32 + lane;
-            lb[u] = INFINITY;
-            if (cb < nbc) lb[u] = point_gap2(q, __ldg(&boxesC[cb * 2]), __ldg(&boxesC[cb * 2 + 1]));
-        }
-        for (;;) {
-            float lmin = lb[0];
-            int lu = 0;
-#pragma unroll
-            for (int u = 1; u < kMaxLb; ++u)
-                if (lb[u] < lmin) {
-                    lmin = lb[u];
-                    lu = u;
-                }
-            const unsigned gmin = __reduce_min_sync(0xffffffffu, __float_as_uint(lmin));  // lower bounds are >= 0
-            if (gmin == 0x7F800000u) break;                                             // every bucket visited
-            if ((unsigned)(worst >> 32) < gmin) break;  // '<': an equal distance can still win on the index
-            const int src = __ffs(__ballot_sync(0xffffffffu, __float_as_uint(lmin) == gmin)) - 1;
-            const int cb = __shfl_sync(0xffffffffu, lu, src) * 32 + src;
-            if (lane == src) {
-#pragma unroll
-                for (int u = 0; u < kMaxLb; ++u)
-                    if (u == lu) lb[u] = INFINITY;
+            for (int u = 0; u < kMaxLb; ++u) {
+                const int cb = base + u * 32 + lane;
+                lb[u] = INFINITY;
+                if (cb < nbc) lb[u] = point_gap2(q, __ldg(&boxesC[cb * 2]), __ldg(&boxesC[cb * 2 + 1]));
             }
-            const float4 c = __ldg(&sortedC[(size_t)cb * 32 + lane]);
-            offer(c.x, c.y, c.z, __float_as_int(c.w));
+            for (;;) {
+                float lmin = lb[0];
+                int lu = 0;
+#pragma unroll
+                for (int u = 1; u < kMaxLb; ++u)
+                    if (lb[u] < lmin) {
+                        lmin = lb[u];
+                        lu = u;
+                    }
+                const unsigned gmin = __reduce_min_sync(0xffffffffu, __float_as_uint(lmin));  // lower bounds are >= 0
+                if (gmin == 0x7F800000u) break;                                             // every bucket visited
+                if ((unsigned)(worst >> 32) < gmin) break;  // '<': an equal distance can still win on the index
+                const int src = __ffs(__ballot_sync(0xffffffffu, __float_as_uint(lmin) == gmin)) - 1;
+                const int cb = base + __shfl_sync(0xffffffffu, lu, src) * 32 + src;
+                if (lane == src) {
+#pragma unroll
+                    for (int u = 0; u < kMaxLb; ++u)
+                        if (u == lu) lb[u] = INFINITY;
+                }
+                const float4 c = __ldg(&sortedC[(size_t)cb * 32 + lane]);
+                offer(c.x, c.y, c.z, __float_as_int(c.w));
+            }
         }
     }
     float *vv = val + ((size_t)scene * m + qi) * k;
-    int *ii = idx + ((size_t)scene * m + qi) * k;
+    int *ii = idx + ((size_t)scene * m + qi) * k * (pairs ? 2 : 1);
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const int s2 = r * 32 + lane;
         if (s2 < k) {
             vv[s2] = __uint_as_float((unsigned)(best[r] >> 32));
-            ii[s2] = (int)(unsigned)best[r];
+            if (pairs) {  // (batch index, point index): what tf.gather_nd takes (hf/core/pointfly.py:206-210)
+                *reinterpret_cast<int2 *>(ii + 2 * s2) = make_int2(scene, (int)(unsigned)best[r]);
+            } else {
+                ii[s2] = (int)(unsigned)best[r];
+            }
         }
     }
 }
 
 template <int R>
 int launch_knn(bool indexed, int b, int n, int m, int k, const float *xyz1, const float *xyz2, const CloudDesc *q,
-               const CloudDesc *c, float *val, int *idx, cudaStream_t s) {
+               const CloudDesc *c, float *val, int *idx, int pairs, cudaStream_t s) {
     if (indexed) {
         const int nq = q->npad, nbc = c->npad / 32;
         knn_kernel<R, true><<<dim3((nq + kSqWarps - 1) / kSqWarps, b), kSqWarps * 32, 0, s>>>(
-            n, m, k, nq, nbc, xyz2, xyz1, q->sorted, c->sorted, c->boxes, val, idx);
+            n, m, k, nq, nbc, xyz2, xyz1, q->sorted, c->sorted, c->boxes, val, idx, pairs);
     } else {
         knn_kernel<R, false><<<dim3((m + kSqWarps - 1) / kSqWarps, b), kSqWarps * 32, 0, s>>>(
-            n, m, k, m, 0, xyz2, xyz1, nullptr, nullptr, nullptr, val, idx);
+            n, m, k, m, 0, xyz2, xyz1, nullptr, nullptr, nullptr, val, idx, pairs);
     }
     HF_LAUNCH_OK("knn_kernel");
     return HF_OK;
@@ -723,7 +732,7 @@ bool spatial_applies(int nq, int nc) {
 // knn_point profits from the sort much earlier (tools/knn_bench.py: 4096 x 1024, k = 32: 0.08 vs 0.41 ms).
 bool knn_applies(int nq, int nc) {
     if (g_spatial_mode == 1) return false;
-    if (nq < 1 || nc < 1 || nq > kMaxIndexed || nc > kMaxIndexed) return false;
+    if (nq < 1 || nc < 1 || nq > kMaxCloud || nc > kMaxCloud) return false;
     if (g_spatial_mode == 2) return true;
     return nq >= 64 && nc >= 64 && (long long)nq * nc >= (1ll << 20);
 }
@@ -881,9 +890,10 @@ extern "C" size_t hf_knn_workspace_bytes(int b, int n, int m) {
     return hf::knn_applies(m, n) ? hf_spatial_workspace_bytes(b, n, m) : 0;
 }
 
-extern "C" int hf_knn_point(int b, int n, int m, int k, const float *xyz1, const float *xyz2, float *val, int *idx,
-                            void *workspace, size_t workspace_bytes, hf_stream_t stream) {
-    using namespace hf;
+namespace hf {
+namespace {
+int knn_any(int b, int n, int m, int k, const float *xyz1, const float *xyz2, float *val, int *idx, int pairs,
+            void *workspace, size_t workspace_bytes, hf_stream_t stream) {
     HF_REQUIRE(k > 0, "KnnPoint expects positive k");
     HF_REQUIRE(b >= 0 && n >= 1 && m >= 0, "KnnPoint expects (batch_size, ndataset, 3) xyz1 shape");
     HF_REQUIRE(k <= n, "KnnPoint: k must not exceed ndataset (input must have at least k columns)");
@@ -901,7 +911,20 @@ extern "C" int hf_knn_point(int b, int n, int m, int k, const float *xyz1, const
         int rc = launch_index(b, c, &q, s);
         if (rc != HF_OK) return rc;
     }
-    if (k <= 32) return launch_knn<1>(indexed, b, n, m, k, xyz1, xyz2, &q, &c, val, idx, s);
-    if (k <= 64) return launch_knn<2>(indexed, b, n, m, k, xyz1, xyz2, &q, &c, val, idx, s);
-    return launch_knn<4>(indexed, b, n, m, k, xyz1, xyz2, &q, &c, val, idx, s);
+    if (k <= 32) return launch_knn<1>(indexed, b, n, m, k, xyz1, xyz2, &q, &c, val, idx, pairs, s);
+    if (k <= 64) return launch_knn<2>(indexed, b, n, m, k, xyz1, xyz2, &q, &c, val, idx, pairs, s);
+    return launch_knn<4>(indexed, b, n, m, k, xyz1, xyz2, &q, &c, val, idx, pairs, s);
+}
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_knn_point(int b, int n, int m, int k, const float *xyz1, const float *xyz2, float *val, int *idx,
+                            void *workspace, size_t workspace_bytes, hf_stream_t stream) {
+    return hf::knn_any(b, n, m, k, xyz1, xyz2, val, idx, 0, workspace, workspace_bytes, stream);
+}
+
+extern "C" int hf_knn_indices_general(int b, int p, int n, int k, const float *queries, const float *points,
+                                      float *distances, int *indices, void *workspace, size_t workspace_bytes,
+                                      hf_stream_t stream) {
+    return hf::knn_any(b, n, p, k, points, queries, distances, indices, 1, workspace, workspace_bytes, stream);
 }

@@ -64,6 +64,61 @@ returns:
     return out
 
 
+def farthest_point_sample_with_xyz(npoint, inp):
+    """farthest_point_sample + gather_point of one set-abstraction level in one launch
+    (hf/core/feature_extractors/pointnet_util.py:42-44: `new_xyz = gather_point(xyz, farthest_point_sample(npoint, xyz))`).
+
+    Returns (idx (b,npoint) int32, new_xyz (b,npoint,3) float32); both identical to the two separate ops.
+    """
+    require(isinstance(npoint, int) and npoint > 0, "FarthestPointSample expects positive npoint")
+    inp = dev_tensor(inp, torch.float32, "inp")
+    require(inp.dim() == 3 and inp.shape[2] == 3, "FarthestPointSample expects (batch_size,num_points,3) inp shape")
+    b, n = inp.shape[0], inp.shape[1]
+    out = torch.empty((b, npoint), dtype=torch.int32, device=inp.device)
+    new_xyz = torch.empty((b, npoint, 3), dtype=torch.float32, device=inp.device)
+    temp = torch.empty((32, n), dtype=torch.float32, device=inp.device) if n > _ON_CHIP_POINTS else None
+    with torch.cuda.device(inp.device):
+        rc = _lib.load().hf_farthest_point_sample_xyz(
+            b, n, npoint, inp.data_ptr(), temp.data_ptr() if temp is not None else None, out.data_ptr(),
+            new_xyz.data_ptr(), stream_ptr(inp.device))
+    _lib.check(rc, "farthest_point_sample_xyz")
+    return out, new_xyz
+
+
+PYRAMID_MAX_LEVELS = 3
+
+
+def farthest_point_sample_pyramid(npoints, inp):
+    """Consecutive set-abstraction sampling levels in one launch: level j draws npoints[j] points from the picks of
+    level j-1 (level 0 from inp), i.e. the `farthest_point_sample` + `gather_point` pairs of successive
+    pointnet_sa_module calls (pointnet_util.py:42-44) with nothing else in between.
+
+    npoints: list of 1..3 ints.  Returns ([idx_j (b,npoints[j]) int32], [new_xyz_j (b,npoints[j],3) float32]),
+    identical to calling farthest_point_sample / gather_point level by level.
+    """
+    import ctypes
+
+    npoints = [int(v) for v in npoints]
+    require(1 <= len(npoints) <= PYRAMID_MAX_LEVELS, "fps pyramid takes 1..%d levels" % PYRAMID_MAX_LEVELS)
+    require(all(v > 0 for v in npoints), "FarthestPointSample expects positive npoint")
+    inp = dev_tensor(inp, torch.float32, "inp")
+    require(inp.dim() == 3 and inp.shape[2] == 3, "FarthestPointSample expects (batch_size,num_points,3) inp shape")
+    b, n = inp.shape[0], inp.shape[1]
+    require(n <= _ON_CHIP_POINTS, "fps pyramid: clouds beyond %d points are sampled level by level" % _ON_CHIP_POINTS)
+    idx = [torch.empty((b, m), dtype=torch.int32, device=inp.device) for m in npoints]
+    xyz = [torch.empty((b, m, 3), dtype=torch.float32, device=inp.device) for m in npoints]
+    L = len(npoints)
+    m_arr = (ctypes.c_int * L)(*npoints)
+    idx_arr = (ctypes.c_void_p * L)(*[t.data_ptr() for t in idx])
+    xyz_arr = (ctypes.c_void_p * L)(*[t.data_ptr() for t in xyz])
+    with torch.cuda.device(inp.device):
+        rc = _lib.load().hf_fps_pyramid(b, L, n, ctypes.cast(m_arr, ctypes.c_void_p), inp.data_ptr(),
+                                        ctypes.cast(idx_arr, ctypes.c_void_p), ctypes.cast(xyz_arr, ctypes.c_void_p),
+                                        stream_ptr(inp.device))
+    _lib.check(rc, "fps_pyramid")
+    return idx, xyz
+
+
 def gather_point_grad(inp, idx, out_g):
     """Gradient of gather_point w.r.t. inp (the reference's GatherPointGrad op,
     sampling/tf_sampling.py:54-58, op checks sampling/tf_sampling.cpp:150-179).

@@ -64,7 +64,21 @@ int hf_fp32_probe(int blocks, int iters, int packed, float *out, hf_stream_t str
  * Requires m >= 1 (tf_sampling.cpp:99). */
 int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp, int *out,
                              hf_stream_t stream);
-/* Tuning override for the FPS launch shape (cluster size 1/2/4/8, 0 = heuristic). */
+/* farthest_point_sample + gather_point of one SA level (hf/core/feature_extractors/pointnet_util.py:42-44) in one
+ * launch: out (b,m) as above and new_xyz (b,m,3) = inp[out].  The sampling kernel holds the coordinates of every
+ * pick when it writes the index, so the separate gatherpointLauncher launch (tf_sampling_g.cu:206) disappears. */
+int hf_farthest_point_sample_xyz(int b, int n, int m, const float *inp, float *temp, int *out, float *new_xyz,
+                                 hf_stream_t stream);
+/* `levels` (1..HF_FPS_PYRAMID_MAX_LEVELS) consecutive SA sampling levels in ONE launch: level j samples m[j] points
+ * from the picks of level j-1 (level 0 from inp (b,n,3)), exactly like calling hf_farthest_point_sample_xyz level by
+ * level (pointnet_util.py:42-44 per set-abstraction module).  m: host array of `levels` ints; idx / new_xyz: HOST
+ * arrays of `levels` device pointers, (b,m[j]) int32 and (b,m[j],3) float.  Clouds of up to 16384 points with
+ * m[j+1] <= m[j] run as one cluster kernel that keeps each level's picks in shared memory; other shapes are
+ * issued level by level. */
+#define HF_FPS_PYRAMID_MAX_LEVELS 3
+int hf_fps_pyramid(int b, int levels, int n, const int *m, const float *inp, int *const *idx, float *const *new_xyz,
+                   hf_stream_t stream);
+/* Tuning override for the FPS launch shape (cluster size 1/2/4/6/8, 0 = heuristic). */
 void hf_fps_set_cluster(int cluster);
 /* Tuning override for the FPS CTA size (256 or 512 threads, 0 = heuristic). */
 void hf_fps_set_threads(int threads);
@@ -267,12 +281,20 @@ int hf_pc_crop_and_sample_grad_fts(const int *box_ind, const int *crop_ind,
  * index (tf.nn.top_k's rule).  The reference builds the whole (b,m,n) matrix as r2 - 2*x2.x1^T + r1
  * with a TF matmul and runs top_k on the CPU; here distance and selection are fused and the matrix
  * never exists.  val is the directly computed squared distance (the expanded form's cancellation
- * error, ~1e-7 * |x|^2, is not reproduced).  Requires 1 <= k <= min(n, 128).  workspace =
+ * error, ~1e-7 * |x|^2, is not reproduced; tests pin the op on the reference formula restated in float32 within
+ * that error).  Requires 1 <= k <= min(n, 128); clouds of up to 65536 points take the pruned search.  workspace =
  * hf_knn_workspace_bytes(b, n, m) bytes (0 = the call is too small to profit from sorting) or NULL
  * (then every pair is tested). */
 size_t hf_knn_workspace_bytes(int b, int n, int m);
 int hf_knn_point(int b, int n, int m, int k, const float *xyz1, const float *xyz2, float *val,
                  int *idx, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* knn_indices_general(queries, points, k, sort=True, unique=True) of PointCNN (hf/core/pointfly.py:185-214, called from
+ * hf/core/feature_extractors/pointcnn.py:72): the k nearest `points` (b,n,3) of every query (b,p,3), ascending ->
+ * distances (b,p,k) and indices (b,p,k,2) int32 = (batch index, point index) pairs, the layout tf.gather_nd takes.
+ * `unique` has no effect in the reference (prepare_for_unique_top_k rebinds a local, pointfly.py:162-164).  Same
+ * kernel, workspace (hf_knn_workspace_bytes(b, n, p)) and value definition as hf_knn_point. */
+int hf_knn_indices_general(int b, int p, int n, int k, const float *queries, const float *points, float *distances,
+                           int *indices, void *workspace, size_t workspace_bytes, hf_stream_t stream);
 /* Replaces selectionSortLauncher(b,n,m,k,dist,outi,out), grouping/tf_grouping_g.cu:129: k steps of
  * selection sort on every row of dist (b,m,n) -> outi (b,m,n) int32, out (b,m,n); the first k
  * entries are the k smallest in order, the tail is the permutation the swaps leave (bit-exact,

@@ -243,6 +243,52 @@ def knn_point(k, xyz1, xyz2):
     return val, idx
 
 
+def knn_point_reference_form(k, xyz1, xyz2):
+    """grouping/tf_grouping.py:78-93 restated operation for operation in numpy float32 (TensorFlow is not installable
+    here): r1 = sum(xyz1*xyz1), r2 = sum(xyz2*xyz2), mul = xyz2 @ xyz1^T, dist = r2 - 2*mul + r1^T, then
+    tf.nn.top_k(-dist, k) = the k smallest, equal values in ascending index order.  Returns (val, idx, dist, tol):
+    dist is the whole (b,m,n) matrix and tol (b,m,1) bounds |dist - exact squared distance| — the expanded form
+    cancels, and TF's matmul may add its three products in another order than numpy's, so both the reference's own
+    values and any comparison with them are only defined up to tol = 8 eps (r2 + max r1)."""
+    xyz1, xyz2 = _c(xyz1, np.float32), _c(xyz2, np.float32)
+    r1 = np.sum(xyz1 * xyz1, axis=2, keepdims=True, dtype=np.float32)  # (b,n,1)
+    r2 = np.sum(xyz2 * xyz2, axis=2, keepdims=True, dtype=np.float32)  # (b,m,1)
+    mul = np.matmul(xyz2, np.transpose(xyz1, (0, 2, 1))).astype(np.float32)  # (b,m,n)
+    dist = (r2 - np.float32(2) * mul + np.transpose(r1, (0, 2, 1))).astype(np.float32)
+    order = np.argsort(dist, axis=2, kind="stable")[:, :, :k]
+    val = np.take_along_axis(dist, order, axis=2)
+    tol = (8 * np.finfo(np.float32).eps) * (r2 + r1.max(axis=1, keepdims=True))
+    return val, order.astype(np.int32), dist, tol.astype(np.float32)
+
+
+def check_knn_against_reference_form(k, xyz1, xyz2, val, idx):
+    """The pin of knn_point on the reference's own formula.  (val, idx) = the implementation under test (direct
+    squared distances).  Asserts, per query: every value within tol of the reference-form value of the SAME index;
+    the values ascending; every reference-form neighbour that is missing from idx (and every extra one) lies within
+    2 tol of the k-th distance; and wherever consecutive reference-form distances are more than 2 tol apart on both
+    sides, the index at that rank is the reference's.  Returns the fraction of ranks that were compared exactly."""
+    rv, ri, dist, tol = knn_point_reference_form(k, xyz1, xyz2)
+    val, idx = np.asarray(val), np.asarray(idx).astype(np.int64)
+    same = np.take_along_axis(dist, idx, axis=2)
+    assert np.all(np.abs(same - val) <= tol), "values differ from the reference form by more than its own error"
+    assert np.all(np.diff(val, axis=2) >= 0)
+    n = dist.shape[2]
+    srt = np.sort(dist, axis=2)
+    kth = srt[:, :, k - 1:k]
+    inside = dist <= kth - 2 * tol  # certainly among the k nearest
+    outside = dist >= kth + 2 * tol  # certainly not
+    got = np.zeros(dist.shape, bool)
+    np.put_along_axis(got, idx, True, axis=2)
+    assert not np.any(inside & ~got), "a certain neighbour is missing"
+    assert not np.any(outside & got), "a certain non-neighbour was returned"
+    lo = np.concatenate([np.full_like(srt[:, :, :1], -np.inf), srt[:, :, :k - 1]], axis=2)
+    hi = srt[:, :, 1:k + 1] if n > k else np.concatenate([srt[:, :, 1:k], np.full_like(srt[:, :, :1], np.inf)], axis=2)
+    cur = srt[:, :, :k]
+    decided = (cur - lo > 2 * tol) & (hi - cur > 2 * tol)
+    assert np.array_equal(idx[decided], ri.astype(np.int64)[decided]), "index differs at a rank the reference form decides"
+    return float(decided.mean())
+
+
 def _mangled(so, name):
     out = subprocess.run(["nm", "-D", "--defined-only", so], check=True, stdout=subprocess.PIPE, text=True).stdout
     for line in out.splitlines():

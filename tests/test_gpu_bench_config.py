@@ -78,7 +78,7 @@ def test_bench_chain_graph_matches_reference_kernels(cuda, oracle):
         # distances); positive terms only, so 1e-5 relative per element is the north_star bar
         d = torch.clamp(rd, min=1e-10)
         w = (1.0 / d) / (1.0 / d).sum(dim=2, keepdim=True)
-        gw = res["fp_weights"][lvl + 1]
+        gw = res["fp_weights"][lvl]
         assert close(gw, w), "interpolation weights level %d" % (lvl + 1)
         # interpolation: the reference kernel on the same indices and the same weights.  A row is a signed sum
         # of three products, so the bound is 1e-5 of the magnitude of its terms (cancellation can leave a result

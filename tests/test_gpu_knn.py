@@ -43,6 +43,63 @@ def test_knn_point_matches_oracle(cuda, oracle, b, n, m, k, dup, mode):
     assert np.array_equal(N(val), want_v)
 
 
+@pytest.mark.parametrize("b,n,m,k,mode", [(2, 16384, 1024, 16, 0), (2, 16384, 512, 32, 1), (1, 40000, 256, 32, 2),
+                                          (1, 65536, 300, 16, 0), (2, 20000, 200, 64, 2)])
+def test_knn_point_is_pinned_on_the_reference_formula(cuda, oracle, b, n, m, k, mode):
+    """grouping/tf_grouping.py:78-93 restated in numpy float32 (oracle.knn_point_reference_form): the CUDA result has
+    the reference's neighbours at every rank that formula decides beyond its own rounding error, and its values
+    within that error.  Includes clouds above 16384 points (searched in passes over the parts of the index)."""
+    xyz, _ = synthetic.make_scans(71 + n + k, b, n)
+    x1 = T(xyz, cuda)
+    x2 = gather_point(x1, farthest_point_sample(m, x1))
+    _lib.load().hf_spatial_set_mode(mode)
+    try:
+        val, idx = knn_point(k, x1, x2)
+    finally:
+        _lib.load().hf_spatial_set_mode(0)
+    frac = oracle.check_knn_against_reference_form(k, xyz, N(x2), N(val), N(idx))
+    assert frac > 0.5, frac
+    if n <= 20000:  # and bit-exact against the oracle's direct form (serial: small cases only)
+        want_v, want_i = oracle.knn_point(k, xyz, N(x2))
+        assert np.array_equal(N(idx), want_i) and np.array_equal(N(val), want_v)
+
+
+def test_knn_large_cloud_pruned_equals_every_pair(cuda):
+    """Clouds of 16385..65536 points: the pruned search (index in parts) against the every-pair kernel, bit for bit."""
+    xyz, _ = synthetic.make_scans(13, 2, 50000, duplicate_pad=3000)
+    x1 = T(xyz, cuda)
+    x2 = gather_point(x1, farthest_point_sample(3000, x1))
+    lib = _lib.load()
+    try:
+        lib.hf_spatial_set_mode(1)
+        v1, i1 = knn_point(32, x1, x2)
+        lib.hf_spatial_set_mode(2)
+        v2, i2 = knn_point(32, x1, x2)
+    finally:
+        lib.hf_spatial_set_mode(0)
+    assert torch.equal(i1, i2) and torch.equal(v1, v2)
+
+
+def test_knn_indices_general_matches_knn_point(cuda, oracle):
+    """hf/core/pointfly.py:185-214: (distances, (batch, point) index pairs) of the same search."""
+    from heterofusionrcnn_b200.pointfly import knn_indices_general
+
+    xyz, _ = synthetic.make_scans(5, 3, 3000, duplicate_pad=100)
+    pts = T(xyz, cuda)
+    qrs = gather_point(pts, farthest_point_sample(200, pts))
+    for k in (8, 48):
+        dist, ind = knn_indices_general(qrs, pts, k, True)
+        assert tuple(dist.shape) == (3, 200, k) and tuple(ind.shape) == (3, 200, k, 2) and ind.dtype == torch.int32
+        val, idx = knn_point(k, pts, qrs)
+        assert torch.equal(dist, val) and torch.equal(ind[..., 1], idx)
+        assert torch.equal(ind[..., 0], torch.arange(3, device=cuda, dtype=torch.int32)[:, None, None].expand(-1, 200, k))
+        # tf.gather_nd(points, indices) == the neighbours
+        nb = pts[ind[..., 0].long(), ind[..., 1].long()]
+        d = ((nb - qrs[:, :, None, :]) ** 2).sum(-1)
+        assert torch.allclose(d, dist, rtol=1e-5, atol=1e-6)
+        oracle.check_knn_against_reference_form(k, xyz, N(qrs), N(dist), N(ind[..., 1]))
+
+
 def test_knn_point_rejects_bad_arguments(cuda):
     x = torch.zeros((1, 8, 3), device=cuda)
     with pytest.raises(_lib.InvalidArgumentError):

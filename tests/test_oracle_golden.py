@@ -267,6 +267,27 @@ def test_oracle_knn_point_is_a_stable_top_k_of_the_squared_distances(oracle):
     assert np.allclose(np.sort(exp, axis=2)[:, :, :8], val, atol=1e-4)
 
 
+def test_oracle_knn_point_is_pinned_on_the_reference_formula(oracle):
+    """grouping/tf_grouping.py:78-93 (r2 - 2 x2.x1^T + r1, then top_k) restated in numpy float32 is the pin of
+    knn_point: same neighbours wherever that formula's own rounding error (tol) leaves the rank decided, values
+    within tol.  KITTI-range coordinates (tens of metres), where the cancellation is largest."""
+    from heterofusionrcnn_b200 import synthetic
+
+    xyz, _ = synthetic.make_scans(91, 2, 3000, duplicate_pad=200)
+    q = xyz[:, ::7][:, :300]
+    for k in (1, 8, 32):
+        val, idx = oracle.knn_point(k, xyz, q)
+        frac = oracle.check_knn_against_reference_form(k, xyz, q, val, idx)
+        assert frac > 0.5, frac  # the check is not vacuous
+    # small coordinates: the expanded form is accurate, the neighbour lists must agree outright
+    rng = np.random.default_rng(4)
+    x1 = rng.random((2, 400, 3), dtype=np.float32)
+    x2 = rng.random((2, 50, 3), dtype=np.float32)
+    val, idx = oracle.knn_point(16, x1, x2)
+    rv, ri, _, tol = oracle.knn_point_reference_form(16, x1, x2)
+    assert np.mean(idx == ri) > 0.99 and np.all(np.abs(val - rv) <= tol)
+
+
 def test_oracle_box_8co_matches_the_reference_numpy_encoder(oracle):
     """tests/golden/box8co_ref.npz = hf/core/box_8c_encoder.py:np_box_3d_to_box_8co run on seeded boxes
     (tests/golden/make_golden_box8co.py); the oracle returns the (N,3,8) layout of tf_box_3d_to_box_8co."""
