@@ -66,8 +66,12 @@ SIGNATURES = {
     "hf_box3d_iou": (_c_int, [_c_int, _ptr, _c_int, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
     "hf_oriented_nms_scored_workspace_bytes": (_size_t, [_c_int, _c_int]),
     "hf_oriented_nms_scored": (_c_int, [_ptr, _ptr, _c_int, _c_int, _c_float, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_sb_nms_workspace_bytes": (_size_t, [_c_int, _c_int]),
+    "hf_sb_nms": (_c_int, [_ptr, _ptr, _c_int, _c_int, _c_float, _c_int, _c_int, _ptr, _ptr, _ptr, _size_t, _ptr]),
     "hf_lidar_fov_filter_workspace_bytes": (_size_t, [_c_int, _c_int]),
     "hf_lidar_fov_filter": (_c_int, [_c_int, _c_int, _ptr, _ptr, _c_int, _c_int, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_pc_sample_points": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _c_float, _c_float, _ptr, _ptr, _ptr,
+                                     _ptr]),
     "hf_prob_sample": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_group_point_concat": (_c_int, [_c_int] * 5 + [_ptr] * 6),
     "hf_group_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),

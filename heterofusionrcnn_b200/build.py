@@ -13,7 +13,7 @@ import sys
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libhfops.so")
-SOURCES = ["api.cu", "sampling.cu", "fps_bucket.cu", "fps_multi.cu", "grouping.cu", "spatial.cu", "interpolate.cu", "cropping.cu", "bev_iou.cu", "backward.cu", "topk.cu", "glue.cu", "prob_sample.cu", "lidar_input.cu"]
+SOURCES = ["api.cu", "sampling.cu", "fps_bucket.cu", "fps_multi.cu", "grouping.cu", "spatial.cu", "interpolate.cu", "cropping.cu", "bev_iou.cu", "backward.cu", "topk.cu", "glue.cu", "prob_sample.cu", "lidar_input.cu", "pc_sample.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",

@@ -116,6 +116,23 @@ __global__ void map_keep_kernel(long long total, int per_scene, const int *__res
     }
 }
 
+// sb_nms_fn's tail (hf/core/models/model_util.py:124-142): the first nms_size entries of the keep list, mapped back to
+// the caller's box order; entries from `limit` on are -1, limit = min(nms_size, N) when the duplicate padding of the
+// keep list is kept (fixed_num_proposal_nms) and min(nms_size, kept) when tf.unique removes it (the kept boxes are
+// distinct and the padding repeats keep[0], so unique leaves exactly the kept ones in order).
+__global__ void sb_nms_select_kernel(int scenes, int per_scene, int nms_size, int fixed, const int *__restrict__ order,
+                                     const int *__restrict__ keep_sorted, const int *__restrict__ num_kept,
+                                     int *__restrict__ out, int *__restrict__ out_num) {
+    const long long total = (long long)scenes * nms_size;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int scene = (int)(i / nms_size), j = (int)(i - (long long)scene * nms_size);
+        const int limit = min(nms_size, fixed ? per_scene : num_kept[scene]);
+        const long long base = (long long)scene * per_scene;
+        out[i] = j < limit ? order[base + keep_sorted[base + j]] : -1;
+        if (j == 0) out_num[scene] = limit;
+    }
+}
+
 inline size_t a16(size_t v) { return (v + 15) & ~(size_t)15; }
 inline int grid_for(long long total) {
     long long g = (total + 255) / 256;
@@ -180,14 +197,16 @@ extern "C" size_t hf_oriented_nms_scored_workspace_bytes(int scenes, int boxes_n
     return hf::a16(sn * 4) + hf::a16(sn * 20) + hf::a16(sn * 4) + hf_oriented_nms_workspace_bytes(scenes, boxes_num);
 }
 
-extern "C" int hf_oriented_nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_num, float thresh,
-                                      int *keep, int *num_kept, void *workspace, size_t workspace_bytes,
-                                      hf_stream_t stream) {
-    using namespace hf;
+namespace hf {
+namespace {
+// keep != null: the whole keep list (S,N) mapped back to the caller's order (oriented_nms_tf);
+// sel != null: sb_nms_fn's (S,nms_size) selection with -1 padding and its count.
+int nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_num, float thresh, int *keep, int *num_kept,
+               int nms_size, int fixed, int *sel, int *sel_num, void *workspace, size_t workspace_bytes, hf_stream_t stream) {
     HF_REQUIRE(thresh >= 0, "Need nms_threshold >= 0, got %f", (double)thresh);
     HF_REQUIRE(scenes >= 0 && boxes_num >= 0, "oriented_nms expects (S,N,7) boxes and (S,N) scores");
     if (scenes == 0 || boxes_num == 0) return HF_OK;
-    HF_REQUIRE(boxes3d && scores && keep, "oriented_nms: null pointer");
+    HF_REQUIRE(boxes3d && scores && (keep || (sel && sel_num)), "oriented_nms: null pointer");
     HF_REQUIRE(workspace && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "oriented_nms: null or unaligned workspace");
     if (workspace_bytes < hf_oriented_nms_scored_workspace_bytes(scenes, boxes_num)) {
         set_error("oriented_nms: workspace too small");
@@ -205,7 +224,10 @@ extern "C" int hf_oriented_nms_scored(const float *boxes3d, const float *scores,
     int *order = reinterpret_cast<int *>(w);
     float *bev = reinterpret_cast<float *>(w + a16(sn * 4));
     int *keep_sorted = reinterpret_cast<int *>(w + a16(sn * 4) + a16(sn * 20));
-    void *nms_ws = w + a16(sn * 4) + a16(sn * 20) + a16(sn * 4);
+    unsigned char *nms_ws = w + a16(sn * 4) + a16(sn * 20) + a16(sn * 4);
+    if (!num_kept && sel) {  // the selection needs the count: it lives behind the NMS workspace (hf_sb_nms_workspace_bytes)
+        num_kept = reinterpret_cast<int *>(nms_ws + a16(hf_oriented_nms_workspace_bytes(scenes, boxes_num)));
+    }
     const size_t smem = (size_t)P * 8;
     if (smem > 48 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(score_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     score_order_kernel<<<scenes, kSortThreads, smem, s>>>(boxes_num, P, scores, order);
@@ -215,7 +237,56 @@ extern "C" int hf_oriented_nms_scored(const float *boxes3d, const float *scores,
     int rc = hf_oriented_nms(bev, scenes, boxes_num, thresh, keep_sorted, num_kept, nms_ws,
                              hf_oriented_nms_workspace_bytes(scenes, boxes_num), stream);
     if (rc != HF_OK) return rc;
-    map_keep_kernel<<<grid_for((long long)sn), 256, 0, s>>>((long long)sn, boxes_num, order, keep_sorted, keep);
-    HF_LAUNCH_OK("map_keep_kernel");
+    if (keep) {
+        map_keep_kernel<<<grid_for((long long)sn), 256, 0, s>>>((long long)sn, boxes_num, order, keep_sorted, keep);
+        HF_LAUNCH_OK("map_keep_kernel");
+    }
+    if (sel) {
+        sb_nms_select_kernel<<<grid_for((long long)scenes * nms_size), 256, 0, s>>>(scenes, boxes_num, nms_size, fixed, order,
+                                                                                   keep_sorted, num_kept, sel, sel_num);
+        HF_LAUNCH_OK("sb_nms_select_kernel");
+    }
     return HF_OK;
 }
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_oriented_nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_num, float thresh,
+                                      int *keep, int *num_kept, void *workspace, size_t workspace_bytes,
+                                      hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(scenes == 0 || boxes_num == 0 || keep, "oriented_nms: null pointer");
+    if (workspace_bytes < hf_oriented_nms_scored_workspace_bytes(scenes, boxes_num)) {
+        set_error("oriented_nms: workspace too small");
+        return HF_ERR_WORKSPACE;
+    }
+    return nms_scored(boxes3d, scores, scenes, boxes_num, thresh, keep, num_kept, 0, 0, nullptr, nullptr,
+                      workspace, workspace_bytes, stream);
+}
+
+extern "C" size_t hf_sb_nms_workspace_bytes(int scenes, int boxes_num) {
+    return hf_oriented_nms_scored_workspace_bytes(scenes, boxes_num) + hf::a16((size_t)(scenes > 0 ? scenes : 0) * 4) + 16;
+}
+
+extern "C" int hf_sb_nms(const float *boxes3d, const float *scores, int scenes, int boxes_num, float thresh, int nms_size,
+                         int fixed_num_proposal_nms, int *nms_indices, int *num_selected, void *workspace,
+                         size_t workspace_bytes, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(nms_size >= 0, "sb_nms_fn: nms_size must be >= 0");
+    HF_REQUIRE(scenes >= 0 && boxes_num >= 0, "oriented_nms expects (S,N,7) boxes and (S,N) scores");
+    if (scenes == 0) return HF_OK;
+    HF_REQUIRE(num_selected && (nms_size == 0 || nms_indices), "sb_nms_fn: null pointer");
+    if (workspace_bytes < hf_sb_nms_workspace_bytes(scenes, boxes_num)) {
+        set_error("sb_nms_fn: workspace too small");
+        return HF_ERR_WORKSPACE;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (boxes_num == 0 || nms_size == 0) {  // nothing to select: all padding, zero selected
+        if (nms_size) HF_CUDA_OK(cudaMemsetAsync(nms_indices, 0xff, (size_t)scenes * nms_size * 4, s));
+        HF_CUDA_OK(cudaMemsetAsync(num_selected, 0, (size_t)scenes * 4, s));
+        return HF_OK;
+    }
+    return nms_scored(boxes3d, scores, scenes, boxes_num, thresh, nullptr, nullptr, nms_size, fixed_num_proposal_nms ? 1 : 0,
+                      nms_indices, num_selected, workspace, workspace_bytes, stream);
+}
+

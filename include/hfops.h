@@ -98,6 +98,21 @@ int hf_gather_point(int b, int n, int m, const float *inp, const int *idx, float
 int hf_prob_sample(int b, int n, int m, const float *inp_p, const float *inp_r, float *temp, int *out,
                    hf_stream_t stream);
 
+/* The fixed-size sampling of the KITTI loader (hf/datasets/kitti/kitti_dataset.py:341-371) on the device, fed by
+ * hf_lidar_fov_filter: pts (S,n_cap,4) [x,y,z,intensity] with counts (S) valid rows per scan (device memory: the scan
+ * does not return to the host) -> out (S,num_out,4) [x,y,z,intensity - intensity_shift].  n > num_out: every point
+ * with depth z >= depth_split (40 m) and a draw without replacement from the nearer ones; n < num_out: every point and
+ * num_out - n repeats (without replacement up to 2n, with replacement beyond); then a shuffle.  numpy's RNG stream is
+ * replaced by host-drawn inputs that need no knowledge of the scan:
+ *   keys (S,n_cap) uint32: choice(a, k, replace=False) := the k candidates with the smallest (keys[i], i), ascending i;
+ *   extra (S,num_out) uint32 (may be NULL unless num_out > 2n): choice(a, k, replace=True) := a[extra[e] % len(a)];
+ *   slot_of (S,num_out) int32, a permutation per scan: shuffle(choice) := new[slot_of[j]] = old[j].
+ * choice (S,num_out) int32 (may be NULL) receives the source row of every output row; status (S): 1, or 0 where the
+ * reference raises (empty scan; more far points than num_out) and the rows are zero.  n_cap <= 131072. */
+int hf_pc_sample_points(int scans, int n_cap, int num_out, const float *pts, const int *counts, const unsigned *keys,
+                        const int *slot_of, const unsigned *extra, float depth_split, float intensity_shift, float *out,
+                        int *choice, int *status, hf_stream_t stream);
+
 /* ---- grouping ----------------------------------------------------------- */
 /* Replaces queryBallPointLauncher(b,n,m,radius,nsample,xyz1,xyz2,idx,pts_cnt),
  * grouping/tf_grouping_g.cu:125.  xyz1 (b,n,3) dataset, xyz2 (b,m,3) queries ->
@@ -324,6 +339,15 @@ size_t hf_oriented_nms_scored_workspace_bytes(int scenes, int boxes_num);
 int hf_oriented_nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_num,
                            float nms_overlap_thresh, int *keep, int *num_kept, void *workspace,
                            size_t workspace_bytes, hf_stream_t stream);
+/* sb_nms_fn (hf/core/models/model_util.py:101-142, mapped over the scenes of a batch by rpn_model.py:683): scored
+ * oriented NMS as above, then the first nms_size entries of the keep list; with fixed_num_proposal_nms = 0 the
+ * duplicate padding of the keep list is dropped (tf.unique) and the selection is padded with -1.
+ * nms_indices (S,nms_size) int32 indices into the caller's boxes or -1; num_selected (S) = entries before the -1
+ * padding (min(nms_size, N) when fixed, min(nms_size, kept) otherwise).  workspace: hf_sb_nms_workspace_bytes. */
+size_t hf_sb_nms_workspace_bytes(int scenes, int boxes_num);
+int hf_sb_nms(const float *boxes3d, const float *scores, int scenes, int boxes_num, float thresh, int nms_size,
+              int fixed_num_proposal_nms, int *nms_indices, int *num_selected, void *workspace, size_t workspace_bytes,
+              hf_stream_t stream);
 
 /* ---- input side --------------------------- */
 /* get_lidar_point_cloud with im_size, hf/core/obj_utils.py:221-277 (lidar_to_cam_frame, hf/core/calib_utils.py:

@@ -405,6 +405,58 @@ def oriented_nms_scored(boxes3d, scores, thresh):
     return order[keep_sorted]
 
 
+def pc_sample_points(pts, count, num_out, keys, slot_of, extra=None, depth_split=40.0, intensity_shift=0.5):
+    """hf/datasets/kitti/kitti_dataset.py:341-371 restated for ONE scan with the np.random calls replaced by the
+    host-input definitions of include/hfops.h:hf_pc_sample_points.  pts (n_cap,4) float32 [x,y,z,intensity], count =
+    valid rows.  Returns (sampled (P,4) float32, choice (P) int32, ok); ok = 0 (zeros, -1) where the reference raises."""
+    pts = np.asarray(pts, np.float32)
+    n, P = int(count), int(num_out)
+    keys = np.asarray(keys).astype(np.uint32)[:n]
+
+    def draw(cand, k):  # choice(cand, k, replace=False): k smallest (key, index), ascending index
+        order = np.lexsort((cand, keys[cand]))[:k]
+        return np.sort(cand[order])
+
+    bad = (np.zeros((P, 4), np.float32), np.full((P,), -1, np.int32), 0)
+    if P == 0:
+        return np.zeros((0, 4), np.float32), np.zeros((0,), np.int32), 1
+    if n == 0:
+        return bad
+    idx = np.arange(n)
+    if P < n:
+        near = pts[:n, 2] < np.float32(depth_split)
+        far_idx, near_idx = idx[~near], idx[near]
+        if P - len(far_idx) < 0:
+            return bad
+        choice = np.concatenate([draw(near_idx, P - len(far_idx)), far_idx])
+    else:
+        choice = idx
+        if P > n:
+            if P <= 2 * n:
+                more = draw(idx, P - n)
+            else:
+                more = (np.asarray(extra).astype(np.uint32)[: P - n] % np.uint32(n)).astype(np.int64)
+            choice = np.concatenate([choice, more])
+    shuffled = np.empty_like(choice)
+    shuffled[np.asarray(slot_of, np.int64)] = choice
+    out = pts[shuffled].copy()
+    out[:, 3] = out[:, 3] - np.float32(intensity_shift)
+    return out, shuffled.astype(np.int32), 1
+
+
+def sb_nms_fn(boxes3d, scores, thresh, nms_size, fixed_num_proposal_nms):
+    """hf/core/models/model_util.py:124-142 restated: slice, tf.unique (first occurrences, in order), -1 padding."""
+    idx = oriented_nms_scored(boxes3d, scores, thresh)
+    idx = idx[: min(nms_size, len(idx))]
+    if not fixed_num_proposal_nms:
+        _, first = np.unique(idx, return_index=True)
+        idx = idx[np.sort(first)]
+    num = len(idx)
+    if nms_size > num:
+        idx = np.concatenate([idx, np.full((nms_size - num,), -1, idx.dtype)])
+    return idx.astype(np.int32), num
+
+
 def box_3d_to_box_8co(boxes_3d, expand_length=0.0):
     """hf/core/box_8c_encoder.py:101-184 after the expansion of rcnn_model.py:462-476 -> (N,3,8), float32."""
     b = np.asarray(boxes_3d, np.float32).copy()

@@ -59,6 +59,27 @@ def test_oriented_nms_tf_matches_oracle(cuda, oracle, s, n, thresh, ties):
     assert torch.equal(single, keep[0])
 
 
+@pytest.mark.parametrize("s,n,thresh,nms_size", [(2, 2000, 0.8, 300), (1, 700, 0.3, 512), (3, 1500, 0.01, 1024),
+                                                 (2, 9000, 0.85, 512), (1, 100, 0.5, 300), (1, 64, 0.7, 0)])
+def test_sb_nms_fn_matches_oracle(cuda, oracle, s, n, thresh, nms_size):
+    """hf/core/models/model_util.py:101-142: slice to nms_size, tf.unique when the proposal count is not fixed, -1
+    padding, count before padding; both settings, batched and single-scene calls."""
+    from heterofusionrcnn_b200.model_util import sb_nms_fn
+
+    rng = np.random.default_rng(n + nms_size)
+    boxes = np.stack([clustered_boxes3d(20 + i, n) for i in range(s)])
+    scores = rng.random((s, n)).astype(np.float32)
+    for fixed in (True, False):
+        got, num = sb_nms_fn((T(boxes, cuda), T(scores, cuda)), thresh, nms_size, fixed, None)
+        assert tuple(got.shape) == (s, nms_size) and got.dtype == torch.int32
+        for i in range(s):
+            want, wnum = oracle.sb_nms_fn(boxes[i], scores[i], thresh, nms_size, fixed)
+            assert np.array_equal(N(got[i]), want), (i, fixed)
+            assert int(N(num)[i]) == wnum, (i, fixed)
+        one, onum = sb_nms_fn((T(boxes[0], cuda), T(scores[0], cuda)), thresh, nms_size, fixed, None)
+        assert torch.equal(one, got[0]) and int(onum) == int(num[0])
+
+
 def test_box_3d_to_box_8co_feeds_the_crop(cuda, oracle):
     """tf_box_3d_to_box_8co (+ the proposal expansion) against the oracle, and as the crop's box input."""
     from heterofusionrcnn_b200.box_8c_encoder import tf_box_3d_to_box_8co

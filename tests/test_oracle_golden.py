@@ -288,6 +288,28 @@ def test_oracle_knn_point_is_pinned_on_the_reference_formula(oracle):
     assert np.mean(idx == ri) > 0.99 and np.all(np.abs(val - rv) <= tol)
 
 
+def _pc_sample_cases():
+    g = np.load(os.path.join(os.path.dirname(GOLD), "pc_sample_ref.npz"))
+    names = sorted({k.split(".")[0] for k in g.files}, key=lambda c: int(c[1:]))
+    return [{k.split(".", 1)[1]: g[k] for k in g.files if k.startswith(c + ".")} for c in names]
+
+
+def test_oracle_pc_sample_matches_the_reference_block(oracle):
+    """tests/golden/pc_sample_ref.npz = kitti_dataset.py:341-371 EXECUTED with np.random bound to the host-input
+    definitions (make_golden_pc_sample.py): near/far split, both kinds of draw, the shuffle, the intensity shift, and
+    the two inputs on which the reference raises."""
+    cases = _pc_sample_cases()
+    assert len(cases) >= 10 and any(int(c["ok"]) == 0 for c in cases)
+    for c in cases:
+        pts = np.concatenate([c["pts"], c["inten"]], axis=1).astype(np.float32)
+        out, choice, ok = oracle.pc_sample_points(pts, len(pts), int(c["P"]), c["keys"], c["slot_of"], c["extra"])
+        assert ok == int(c["ok"])
+        if ok:
+            assert np.array_equal(choice, c["choice"])
+            assert np.array_equal(out, c["sampled"].astype(np.float32))  # the reference computes in float64
+            assert np.array_equal(out.astype(np.float64)[:, :3], c["sampled"][:, :3])
+
+
 def test_oracle_box_8co_matches_the_reference_numpy_encoder(oracle):
     """tests/golden/box8co_ref.npz = hf/core/box_8c_encoder.py:np_box_3d_to_box_8co run on seeded boxes
     (tests/golden/make_golden_box8co.py); the oracle returns the (N,3,8) layout of tf_box_3d_to_box_8co."""
