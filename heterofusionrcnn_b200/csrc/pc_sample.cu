@@ -14,7 +14,7 @@
 //   slot_of (S, P) int32        np.random.shuffle(choice)              := new[slot_of[j]] = old[j]  (a permutation)
 // Each is a valid implementation of the numpy call it stands for (uniform keys / a uniform permutation give the
 // same distribution); tests/golden/make_golden_pc_sample.py executes the reference's own lines with np.random
-// replaced by exactly these definitions and the oracle and this kernel reproduce its output.
+// replaced by exactly these definitions; this kernel reproduces that output bit for bit (tests/test_gpu_pc_sample.py).
 //
 // One CTA per scan.  Selecting the k smallest keys is a 4-pass radix select (256-bin shared-memory histograms);
 // "ascending index order" makes every position a prefix count, so there is no sort: three bitmaps by point index
