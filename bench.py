@@ -165,6 +165,9 @@ def work(name, m):
         return "fp32", 12 * m["b"] * (m["n"] + m["m"]) + 4 * m["b"] * m["m"] * (m["ns"] + 1), 9 * m["b"] * m["m"] * m["n"]
     if name == "group_point":
         return "hbm", 4 * (m["b"] * m["m"] * m["ns"] * m["c"] + m["b"] * m["m"] * m["ns"] + m["b"] * m["n"] * m["c"]), 0
+    if name == "group_point_pair":  # xyz (3) and features (c) of the same rows: the group_point formula for 3 + c
+        cc = m["c"] + 3
+        return "hbm", 4 * (m["b"] * m["m"] * m["ns"] * cc + m["b"] * m["m"] * m["ns"] + m["b"] * m["n"] * cc), 0
     if name == "three_nn":
         return "fp32", 12 * m["b"] * (m["n"] + m["m"]) + 24 * m["b"] * m["n"], 8 * m["b"] * m["n"] * m["m"]
     if name == "three_interpolate":

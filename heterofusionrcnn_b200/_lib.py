@@ -35,6 +35,8 @@ SIGNATURES = {
     "hf_fps_set_threads": (None, [_c_int]),
     "hf_fps_set_variant": (None, [_c_int, _c_int, _c_int]),
     "hf_gather_point": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
+    "hf_gather_set_mode": (None, [_c_int]),
+    "hf_group_point_pair": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_query_ball_point": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_spatial_workspace_bytes": (_size_t, [_c_int, _c_int, _c_int]),
     "hf_spatial_set_mode": (None, [_c_int]),

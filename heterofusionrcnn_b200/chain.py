@@ -21,7 +21,7 @@ import torch
 from . import spatial, synthetic
 from .bev_iou.bev_iou import oriented_nms_batch
 from .cropping.tf_cropping import pc_crop_and_sample
-from .grouping.tf_grouping import group_point, query_ball_point
+from .grouping.tf_grouping import group_point, group_point_pair, query_ball_point
 from .interpolate.tf_interpolate import three_interpolate, three_nn_weights
 from .sampling.tf_sampling import (PYRAMID_MAX_LEVELS, farthest_point_sample, farthest_point_sample_pyramid,
                                    farthest_point_sample_with_xyz, gather_point)
@@ -46,6 +46,9 @@ class ChainConfig:
     # sampling spine: level 1 = one launch that writes the indices AND the picked points; levels 2-4 = one launch
     # (fps pyramid).  False = the reference's op sequence, farthest_point_sample + gather_point per level (8 launches).
     fused_sampling: bool = True
+    # grouping: the coordinates and the features of a level's neighbourhoods in one launch (group_point_pair);
+    # False = two group_point launches per level (pointnet_util.py:49,56)
+    fused_grouping: bool = True
 
     def scaled(self, points):
         """Same chain on a different cloud size (npoint = n/4 per level)."""
@@ -359,10 +362,14 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                 after(sg, index_ready[l])
             with probe("query_ball_point", level=l + 1, b=b, n=n, m=m, ns=ns):
                 gidx, cnt = query_ball_point(cfg.radius[l], ns, xyz[l], new_xyz, index1=ix[0], index2=ix[1])
-            with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
-                gxyz = group_point(xyz[l], gidx)
-            with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
-                gfeat = group_point(feats[l], gidx)
+            if cfg.fused_grouping:
+                with probe("group_point_pair", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
+                    gxyz, gfeat = group_point_pair(xyz[l], feats[l], gidx)
+            else:
+                with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=3):
+                    gxyz = group_point(xyz[l], gidx)
+                with probe("group_point", level=l + 1, b=b, n=n, m=m, ns=ns, c=feats[l].shape[2]):
+                    gfeat = group_point(feats[l], gidx)
         # three_nn of FP level l+1 (unknown = level l cloud, known = level l+1 cloud) is geometry only;
         # the interpolation weights (pointnet_util.py:304-307) come out of the same kernel
         sn = s_nn[l]
@@ -481,4 +488,5 @@ def chain_launches(cfg):
     use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
     indexed = [use_ix[l] or (l > 0 and use_ix[l - 1]) for l in range(4)] + [use_ix[3]]
     sampling = 2 if cfg.fused_sampling else 8  # fps+xyz of level 1 and the pyramid of levels 2-4 / fps + gather per level
-    return sampling + 4 * 3 + 4 * 2 + sum(indexed) + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)
+    grouping = 4 * (2 if cfg.fused_grouping else 3)  # ball query + group_point (pair) per level
+    return sampling + grouping + 4 * 2 + sum(indexed) + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)

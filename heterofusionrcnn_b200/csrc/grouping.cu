@@ -120,9 +120,15 @@ constexpr int kGpThreads = 256;
 constexpr int kGpRowsPerWarp = 4;
 
 // c % 4 == 0, 16-byte aligned rows.  grid = (blocks, b).
+// XYZ: the same pass also gathers the (b,n,3) coordinates of the rows into out_xyz (b,rows,3) — sample_and_group calls
+// group_point twice with the same idx (hf/core/feature_extractors/pointnet_util.py:49,56), and the 12-byte rows of the
+// coordinate call are latency-sized work that does not deserve its own launch: lanes 0..11 of the warp copy the 4 x 3
+// floats of its four rows (48 contiguous bytes of out_xyz).
+template <bool XYZ>
 __global__ void __launch_bounds__(kGpThreads)
     group_point_vec4_kernel(int n, int c4, int rows, const float4 *__restrict__ points,
-                            const int *__restrict__ idx, float4 *__restrict__ out) {
+                            const int *__restrict__ idx, float4 *__restrict__ out, const float *__restrict__ xyz,
+                            float *__restrict__ out_xyz) {
     const int scene = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * kGpThreads + threadIdx.x) >> 5;
@@ -134,6 +140,15 @@ __global__ void __launch_bounds__(kGpThreads)
         int src[kGpRowsPerWarp];
 #pragma unroll
         for (int u = 0; u < kGpRowsPerWarp; ++u) src[u] = (r0 + u < rows) ? ind[r0 + u] : -1;
+        if (XYZ && lane < 3 * kGpRowsPerWarp) {
+            const int u = lane / 3, j = lane - 3 * u;
+            int su = src[0];
+#pragma unroll
+            for (int q = 1; q < kGpRowsPerWarp; ++q)
+                if (u == q) su = src[q];
+            if (su >= 0)
+                out_xyz[((size_t)scene * rows + r0 + u) * 3 + j] = __ldg(&xyz[((size_t)scene * n + su) * 3 + j]);
+        }
         for (int v = lane; v < c4; v += 32) {
             float4 val[kGpRowsPerWarp];
 #pragma unroll
@@ -144,6 +159,69 @@ __global__ void __launch_bounds__(kGpThreads)
                 if (src[u] >= 0) stg_cs_f4(&o[(size_t)(r0 + u) * c4 + v], val[u]);
         }
     }
+}
+
+// TMA row mover (c % 4 == 0): the op is a pure copy, so no byte has to pass through a register.  Every WARP runs its
+// own ring of kGbStages shared-memory stages.  A stage holds R consecutive output rows: each lane issues the 1-D bulk
+// copies (cp.async.bulk global -> shared, one per gathered source row) of its rows, all completing on the stage's
+// mbarrier; the R rows are contiguous in `out`, so ONE bulk copy shared -> global writes the whole stage.  Loads of two
+// stages are in flight while the third is being written: the bytes in flight per SM are bounded by its shared memory
+// (4 warps x 3 stages x <= 16 KB), not by registers, and the kernel issues ~2 instructions per row, which leaves the
+// issue slots of the SM to whatever else runs beside it (the sampling clusters).
+constexpr int kGbThreads = 128;
+constexpr int kGbStages = 3;
+constexpr int kGbStageBytes = 16 * 1024;
+
+__global__ void __launch_bounds__(kGbThreads)
+    group_point_bulk_kernel(int n, int rowbytes, int R, long long rows_all, int rows_per_scene,
+                            const unsigned char *__restrict__ points, const int *__restrict__ idx,
+                            unsigned char *__restrict__ out) {
+    extern __shared__ __align__(128) unsigned char gb_smem[];
+    __shared__ __align__(8) uint64_t bars[kGbThreads / 32][kGbStages];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char *ring = gb_smem + (size_t)warp * kGbStages * kGbStageBytes;
+    if (lane == 0) {
+        for (int s = 0; s < kGbStages; ++s) mbar_init(&bars[warp][s], 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+    const long long groups = (rows_all + R - 1) / R;
+    const long long gw = (long long)blockIdx.x * (kGbThreads / 32) + warp, nw = (long long)gridDim.x * (kGbThreads / 32);
+    // a warp's k-th group is g(k) = gw + k * nw
+    auto issue = [&](long long k) {
+        const long long g = gw + k * nw;
+        if (g >= groups) return;
+        const int s = (int)(k % kGbStages);
+        const long long r0 = g * R;
+        const int cnt = (int)((rows_all - r0) < R ? (rows_all - r0) : R);
+        if (lane == 0) mbar_arrive_expect_tx(&bars[warp][s], (uint32_t)cnt * (uint32_t)rowbytes);
+        __syncwarp();
+        for (int u = lane; u < cnt; u += 32) {
+            const long long row = r0 + u;
+            const long long scene = row / rows_per_scene;
+            const unsigned char *src = points + ((size_t)scene * n + (size_t)__ldg(&idx[row])) * rowbytes;
+            tma_load_1d(ring + (size_t)s * kGbStageBytes + (size_t)u * rowbytes, src, (uint32_t)rowbytes, &bars[warp][s]);
+        }
+    };
+    issue(0);
+    issue(1);
+    for (long long k = 0;; ++k) {
+        const long long g = gw + k * nw;
+        if (g >= groups) break;
+        const int s = (int)(k % kGbStages);
+        // stage (k + 2) % 3 was written out as group k - 1: its store must have read the stage before it is refilled
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+        issue(k + 2);
+        mbar_wait(&bars[warp][s], (uint32_t)(k / kGbStages) & 1u);
+        if (lane == 0) {
+            const long long r0 = g * R;
+            const int cnt = (int)((rows_all - r0) < R ? (rows_all - r0) : R);
+            tma_store_1d(out + (size_t)r0 * rowbytes, ring + (size_t)s * kGbStageBytes, (uint32_t)cnt * (uint32_t)rowbytes);
+            tma_store_commit();
+        }
+    }
+    if (lane == 0) tma_store_wait_read<0>();  // shared memory must outlive the last store's read
 }
 
 // any c: flat (row, channel) mapping so stores are coalesced; gathers are 4-byte.
@@ -160,6 +238,29 @@ __global__ void __launch_bounds__(kGpThreads)
         int r = (int)(e / c);
         int l = (int)(e - (long long)r * c);
         o[e] = __ldg(&pts[(size_t)ind[r] * c + l]);
+    }
+}
+
+// Rows of a few floats (xyz = 3, intensity = 1): one THREAD per output row, CX + CP floats per row gathered from two
+// sources that share the index (CP = 0: one source).  Consecutive threads write consecutive rows, so the stores of a
+// warp are one contiguous run; the flat (element / c) mapping of the scalar kernel above costs a division per float.
+template <int CX, int CP>
+__global__ void __launch_bounds__(kGpThreads)
+    group_point_small_kernel(int n, int rows, const float *__restrict__ a, const float *__restrict__ bsrc,
+                             const int *__restrict__ idx, float *__restrict__ out_a, float *__restrict__ out_b) {
+    const int scene = blockIdx.y;
+    const int *ind = idx + (size_t)scene * rows;
+    for (int r = blockIdx.x * kGpThreads + threadIdx.x; r < rows; r += gridDim.x * kGpThreads) {
+        const size_t src = (size_t)scene * n + ind[r], dst = (size_t)scene * rows + r;
+        float va[CX], vb[CP > 0 ? CP : 1];
+#pragma unroll
+        for (int j = 0; j < CX; ++j) va[j] = __ldg(&a[src * CX + j]);
+#pragma unroll
+        for (int j = 0; j < CP; ++j) vb[j] = __ldg(&bsrc[src * CP + j]);
+#pragma unroll
+        for (int j = 0; j < CX; ++j) out_a[dst * CX + j] = va[j];
+#pragma unroll
+        for (int j = 0; j < CP; ++j) out_b[dst * CP + j] = vb[j];
     }
 }
 
@@ -216,6 +317,11 @@ float ball_threshold(float radius) {
 
 }  // namespace hf
 
+namespace hf {
+thread_local int g_gather_bulk = 0;  // hf_gather_set_mode: 1 = TMA row mover where it applies, 0 = register kernels (faster: profiles/r2_gather_bench_tma_rows.txt)
+}
+extern "C" void hf_gather_set_mode(int bulk) { hf::g_gather_bulk = bulk; }
+
 extern "C" int hf_query_ball_point(int b, int n, int m, float radius, int nsample, const float *xyz1,
                                    const float *xyz2, int *idx, int *pts_cnt, hf_stream_t stream) {
     using namespace hf;
@@ -241,30 +347,79 @@ extern "C" int hf_query_ball_point(int b, int n, int m, float radius, int nsampl
     return HF_OK;
 }
 
-extern "C" int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,
-                              float *out, hf_stream_t stream) {
-    using namespace hf;
+namespace hf {
+namespace {
+// group_point of `points` (b,n,c) and, when xyz != null, of the coordinates (b,n,3) with the same idx, in one launch
+// where a kernel covers the pair (c % 4 == 0 with aligned rows, or c <= 4); otherwise one launch each.
+int group_point_any(int b, int n, int c, int m, int nsample, const float *points, const int *idx, float *out,
+                    const float *xyz, float *out_xyz, cudaStream_t s) {
     HF_REQUIRE(b >= 0 && n >= 1 && c >= 1 && m >= 0 && nsample >= 0,
                "GroupPoint expects (batch_size, num_points, channel) points shape");
-    HF_REQUIRE(points && idx && out, "GroupPoint: null pointer");
+    HF_REQUIRE(points && idx && out && (!xyz || out_xyz), "GroupPoint: null pointer");
     HF_REQUIRE(b <= 65535, "GroupPoint: batch_size > 65535 not supported");
     HF_REQUIRE((long long)m * nsample < (1ll << 31), "GroupPoint: npoint*nsample must fit int32");
     const int rows = m * nsample;
     if (b == 0 || rows == 0) return HF_OK;
-    cudaStream_t s = (cudaStream_t)stream;
     const int sms = num_sms();
-    bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(points) & 15) == 0) &&
-               ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    const bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(points) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    const int rowbytes = c * 4;
+    if (vec && g_gather_bulk && rowbytes <= kGbStageBytes && !xyz) {
+        int R = kGbStageBytes / rowbytes;
+        if (R > 32) R = 32;
+        const long long rows_all = (long long)b * rows;
+        const long long groups = (rows_all + R - 1) / R;
+        const size_t smem = (size_t)(kGbThreads / 32) * kGbStages * kGbStageBytes;
+        HF_CUDA_OK(cudaFuncSetAttribute(group_point_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        long long blocks = (groups + (kGbThreads / 32) - 1) / (kGbThreads / 32);
+        if (blocks > sms) blocks = sms;
+        group_point_bulk_kernel<<<(unsigned)blocks, kGbThreads, smem, s>>>(
+            n, rowbytes, R, rows_all, rows, reinterpret_cast<const unsigned char *>(points), idx,
+            reinterpret_cast<unsigned char *>(out));
+        HF_LAUNCH_OK("group_point_bulk_kernel");
+        return HF_OK;
+    }
     if (vec) {
         int warps_needed = (rows + kGpRowsPerWarp - 1) / kGpRowsPerWarp;
         int blocks = (warps_needed + (kGpThreads / 32) - 1) / (kGpThreads / 32);
         int cap = (sms * 8 + b - 1) / b;  // ~8 resident CTAs per SM over the whole grid
         if (blocks > cap) blocks = cap;
         if (blocks < 1) blocks = 1;
-        group_point_vec4_kernel<<<dim3(blocks, b), kGpThreads, 0, s>>>(
-            n, c / 4, rows, reinterpret_cast<const float4 *>(points), idx, reinterpret_cast<float4 *>(out));
+        if (xyz)
+            group_point_vec4_kernel<true><<<dim3(blocks, b), kGpThreads, 0, s>>>(
+                n, c / 4, rows, reinterpret_cast<const float4 *>(points), idx, reinterpret_cast<float4 *>(out), xyz, out_xyz);
+        else
+            group_point_vec4_kernel<false><<<dim3(blocks, b), kGpThreads, 0, s>>>(
+                n, c / 4, rows, reinterpret_cast<const float4 *>(points), idx, reinterpret_cast<float4 *>(out), nullptr, nullptr);
         HF_LAUNCH_OK("group_point_vec4_kernel");
-    } else {
+        return HF_OK;
+    }
+    if (c <= 4) {  // thread per row; with xyz: (3 + c) floats per row from the two sources
+        int blocks = (rows + kGpThreads - 1) / kGpThreads;
+        const int cap = (sms * 8 + b - 1) / b;
+        if (blocks > cap) blocks = cap;
+        const dim3 grid(blocks, b);
+#define HF_GP_SMALL(CX, CP, A, B, OA, OB) group_point_small_kernel<CX, CP><<<grid, kGpThreads, 0, s>>>(n, rows, A, B, idx, OA, OB)
+        if (xyz) {
+            switch (c) {
+                case 1: HF_GP_SMALL(3, 1, xyz, points, out_xyz, out); break;
+                case 2: HF_GP_SMALL(3, 2, xyz, points, out_xyz, out); break;
+                case 3: HF_GP_SMALL(3, 3, xyz, points, out_xyz, out); break;
+                default: HF_GP_SMALL(3, 4, xyz, points, out_xyz, out); break;
+            }
+        } else {
+            switch (c) {
+                case 1: HF_GP_SMALL(1, 0, points, nullptr, out, nullptr); break;
+                case 2: HF_GP_SMALL(2, 0, points, nullptr, out, nullptr); break;
+                case 3: HF_GP_SMALL(3, 0, points, nullptr, out, nullptr); break;
+                default: HF_GP_SMALL(4, 0, points, nullptr, out, nullptr); break;
+            }
+        }
+#undef HF_GP_SMALL
+        HF_LAUNCH_OK("group_point_small_kernel");
+        return HF_OK;
+    }
+    {
         long long total = (long long)rows * c;
         long long blocks = (total + kGpThreads - 1) / kGpThreads;
         long long cap = ((long long)sms * 8 + b - 1) / b;
@@ -273,7 +428,22 @@ extern "C" int hf_group_point(int b, int n, int c, int m, int nsample, const flo
         group_point_scalar_kernel<<<dim3((unsigned)blocks, b), kGpThreads, 0, s>>>(n, c, rows, points, idx, out);
         HF_LAUNCH_OK("group_point_scalar_kernel");
     }
+    if (xyz) return group_point_any(b, n, 3, m, nsample, xyz, idx, out_xyz, nullptr, nullptr, s);
     return HF_OK;
+}
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,
+                              float *out, hf_stream_t stream) {
+    return hf::group_point_any(b, n, c, m, nsample, points, idx, out, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int hf_group_point_pair(int b, int n, int c, int m, int nsample, const float *xyz, const float *points,
+                                   const int *idx, float *out_xyz, float *out_points, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(xyz && out_xyz, "GroupPoint: null pointer");
+    return group_point_any(b, n, c, m, nsample, points, idx, out_points, xyz, out_xyz, (cudaStream_t)stream);
 }
 
 extern "C" int hf_group_point_concat(int b, int n, int c, int m, int nsample, const float *xyz, const float *points,

@@ -96,73 +96,82 @@ __device__ __forceinline__ float tap3(float w0, float p0, float w1, float p1, fl
 
 constexpr int kTiThreads = 256;
 
-// channel-last, c % 4 == 0: points (b,m,c4) float4 -> out (b,n,c4).  grid = (blocks, b)
-// A warp takes U consecutive rows per step: their 3U indices and weights are one coalesced load by
-// lanes 0..3U-1, issued one step AHEAD (the gathers depend on them: without the prefetch every step is
-// two dependent memory round trips and the kernel is latency bound at ~0.5 of the HBM peak), and the
-// 3U gathered 128-bit loads of a channel chunk are all in flight before the first FMA.
-// The grid is one-dimensional and exactly as large as the GPU holds at once (rows of all scenes are one
-// list): these launches last 15-50 us, a partial last wave is a visible fraction of that.
-constexpr int kTiRows = 4;
-__global__ void __launch_bounds__(kTiThreads)
-    three_interpolate_nlc_vec4_kernel(int m, int c4, int n, long long rows_all, const float4 *__restrict__ points,
+// channel-last, c % 4 == 0: points (b,m,c4) float4 -> out (b,n,c4).  grid = (blocks per scene, b).
+// A warp takes U consecutive rows per round: their 3U indices and weights are one coalesced load by lanes 0..3U-1,
+// issued one round AHEAD (the gathers depend on them: without the prefetch every round is two dependent memory round
+// trips), and the 3U gathered 128-bit loads of a channel chunk are all in flight before the first FMA.
+// ncu (profiles/r2_three_interpolate_ncu.md): the kernel is bound by memory LATENCY per round, not by L2 or DRAM
+// throughput (both < 40 %), so what counts is how soon a warp is back at its next batch of loads: the scene is a grid
+// dimension and every index is 32-bit inside it (no 64-bit division or multiply per row; round 1 spent 80 instructions
+// per row, this kernel ~30), and U = 2 rows per warp at 4 CTAs/SM overlaps the phases of twice as many warps as U = 4
+// at 2 CTAs/SM (47.6 vs 51.8 us at c = 128, 37.3 vs 39.9 us at c = 512 for 16 scans).
+// Measured alternatives that lost and are not in the tree: cp.async (LDGSTS) staging of the rows in shared memory,
+// 4 rounds in flight per warp: 127 us (c = 128) / 56 us (c = 512); rows visited along the Hilbert curve of the
+// unknown cloud for L1 reuse: 64 us / 42 us (same file).
+constexpr int kTiRows = 2;
+template <int U>
+__global__ void __launch_bounds__(kTiThreads, 8 / U)
+    three_interpolate_nlc_vec4_kernel(int m, int c4, int n, const float4 *__restrict__ points,
                                       const int *__restrict__ idx, const float *__restrict__ weight,
                                       float4 *__restrict__ out) {
-    constexpr int U = kTiRows;
     const int lane = threadIdx.x & 31;
-    const long long warp = ((long long)blockIdx.x * kTiThreads + threadIdx.x) >> 5;
-    const long long nwarps = ((long long)gridDim.x * kTiThreads) >> 5;
-    const long long e_all = rows_all * 3;
-    // lane < 3U: source row (in the batch-flattened points array) and weight of tap lane % 3 of row r0 + lane / 3
-    auto fetch = [&](long long r0, long long &src, float &ww) {
-        const long long e = r0 * 3 + lane;
-        const bool ok = lane < 3 * U && e < e_all;
-        src = 0;
+    const int scene = blockIdx.y;
+    const int warp = (blockIdx.x * kTiThreads + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * kTiThreads) >> 5;
+    points += (size_t)scene * m * c4;
+    idx += (size_t)scene * n * 3;
+    weight += (size_t)scene * n * 3;
+    out += (size_t)scene * n * c4;
+    const int e_all = n * 3;
+    // lane < 3U: float4 offset of the tap's source row in the scene's points, and its weight
+    auto fetch = [&](int r0, unsigned &off, float &ww) {
+        const int e = r0 * 3 + lane;
+        off = 0u;
         ww = 0.f;
-        if (ok) {
-            const long long scene = (e / 3) / n;
-            src = scene * m + __ldg(&idx[e]);
+        if (lane < 3 * U && e < e_all) {
+            off = (unsigned)__ldg(&idx[e]) * (unsigned)c4;
             ww = __ldg(&weight[e]);
         }
     };
-    long long r0 = warp * U;
-    long long cur_i, nxt_i = 0;
+    int r0 = warp * U;
+    unsigned cur_o, nxt_o = 0u;
     float cur_w, nxt_w = 0.f;
-    fetch(r0, cur_i, cur_w);
-    for (; r0 < rows_all; r0 += nwarps * U) {
-        fetch(r0 + nwarps * U, nxt_i, nxt_w);
-        const float4 *p0[U], *p1[U], *p2[U];
+    fetch(r0, cur_o, cur_w);
+    for (; r0 < n; r0 += nwarps * U) {
+        fetch(r0 + nwarps * U, nxt_o, nxt_w);
+        unsigned p0[U], p1[U], p2[U];
         float w0[U], w1[U], w2[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            p0[u] = points + __shfl_sync(0xffffffffu, cur_i, 3 * u) * c4;
-            p1[u] = points + __shfl_sync(0xffffffffu, cur_i, 3 * u + 1) * c4;
-            p2[u] = points + __shfl_sync(0xffffffffu, cur_i, 3 * u + 2) * c4;
+            p0[u] = __shfl_sync(0xffffffffu, cur_o, 3 * u) + lane;
+            p1[u] = __shfl_sync(0xffffffffu, cur_o, 3 * u + 1) + lane;
+            p2[u] = __shfl_sync(0xffffffffu, cur_o, 3 * u + 2) + lane;
             w0[u] = __shfl_sync(0xffffffffu, cur_w, 3 * u);
             w1[u] = __shfl_sync(0xffffffffu, cur_w, 3 * u + 1);
             w2[u] = __shfl_sync(0xffffffffu, cur_w, 3 * u + 2);
         }
-        for (int v = lane; v < c4; v += 32) {
+        float4 *o = out + (size_t)r0 * c4;
+        for (int v = lane, vo = 0; v < c4; v += 32, vo += 32) {
             float4 a[U], b[U], c[U];
 #pragma unroll
             for (int u = 0; u < U; ++u) {  // rows past the end carry source row 0: valid memory, never stored
-                a[u] = __ldg(p0[u] + v);
-                b[u] = __ldg(p1[u] + v);
-                c[u] = __ldg(p2[u] + v);
+                a[u] = __ldg(points + (p0[u] + vo));
+                b[u] = __ldg(points + (p1[u] + vo));
+                c[u] = __ldg(points + (p2[u] + vo));
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                if (r0 + u < rows_all) {
+                if (r0 + u < n) {
                     float4 r;
                     r.x = tap3(w0[u], a[u].x, w1[u], b[u].x, w2[u], c[u].x);
                     r.y = tap3(w0[u], a[u].y, w1[u], b[u].y, w2[u], c[u].y);
                     r.z = tap3(w0[u], a[u].z, w1[u], b[u].z, w2[u], c[u].z);
                     r.w = tap3(w0[u], a[u].w, w1[u], b[u].w, w2[u], c[u].w);
-                    stg_cs_f4(&out[(size_t)(r0 + u) * c4 + v], r);
+                    stg_cs_f4(o + u * c4 + v, r);
                 }
             }
         }
-        cur_i = nxt_i;
+        cur_o = nxt_o;
         cur_w = nxt_w;
     }
 }
@@ -239,17 +248,20 @@ extern "C" int hf_three_interpolate_nlc(int b, int m, int c, int n, const float 
     const int sms = num_sms();
     bool vec = (c % 4 == 0) && ((reinterpret_cast<uintptr_t>(points) & 15) == 0) &&
                ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
-    if (vec) {
-        const long long rows_all = (long long)b * n;
-        static int per_sm = 0;
-        if (per_sm == 0) {
-            HF_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, three_interpolate_nlc_vec4_kernel, kTiThreads, 0));
-            if (per_sm < 1) per_sm = 1;
-        }
-        long long blocks = (rows_all + (long long)kTiRows * (kTiThreads / 32) - 1) / ((long long)kTiRows * (kTiThreads / 32));
-        if (blocks > (long long)sms * per_sm) blocks = (long long)sms * per_sm;
-        three_interpolate_nlc_vec4_kernel<<<(unsigned)blocks, kTiThreads, 0, s>>>(
-            m, c / 4, n, rows_all, reinterpret_cast<const float4 *>(points), idx, weight, reinterpret_cast<float4 *>(out));
+    // 32-bit offsets inside a scene: m * c4 float4 of points
+    if (vec && (long long)m * (c / 4) < (1ll << 31)) {
+        auto kern = three_interpolate_nlc_vec4_kernel<kTiRows>;
+        int per_sm = 0;  // occupancy on the current device: a cheap runtime query, not cached (re-entrant, any device)
+        HF_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kTiThreads, 0));
+        if (per_sm < 1) per_sm = 1;
+        // exactly as many CTAs as the GPU holds at once: these launches last 15-50 us, a partial last wave is a visible
+        // fraction of that
+        long long blocks = ((long long)n + (long long)kTiRows * (kTiThreads / 32) - 1) / ((long long)kTiRows * (kTiThreads / 32));
+        const long long cap = ((long long)sms * per_sm) / b;  // rounded down: never a second, nearly empty wave
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        kern<<<dim3((unsigned)blocks, b), kTiThreads, 0, s>>>(m, c / 4, n, reinterpret_cast<const float4 *>(points), idx, weight,
+                                                             reinterpret_cast<float4 *>(out));
         HF_LAUNCH_OK("three_interpolate_nlc_vec4_kernel");
     } else {
         long long total = (long long)n * c;

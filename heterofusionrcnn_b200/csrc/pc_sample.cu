@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kPsThreads)
         bool c = valid;
         if (caseA && valid) c = pts[i].z < split;  // pts_near_flag = pts_depth < 40.0 (NaN depth counts as far)
         const unsigned b = __ballot_sync(0xffffffffu, c);
-        if (lane == 0) wcand[i >> 5] = b;
+        if (lane == 0 && (i >> 5) < words) wcand[i >> 5] = b;  // the last round of the loop runs past `words`
     }
     __syncthreads();
     // pfar <- prefix of the far bitmap (valid & ~cand); borrow wlt as its scratch
@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(kPsThreads)
             eq = key == T;
         }
         const unsigned bl = __ballot_sync(0xffffffffu, lt), be = __ballot_sync(0xffffffffu, eq);
-        if (lane == 0) {
+        if (lane == 0 && (i >> 5) < words) {
             wlt[i >> 5] = bl;
             weq[i >> 5] = be;
         }

@@ -77,6 +77,31 @@ def group_point(points, idx):
     return out
 
 
+def group_point_pair(xyz, points, idx):
+    """The two group_point calls of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49,56) in one pass:
+
+        grouped_xyz, grouped_points = group_point(xyz, idx), group_point(points, idx)
+
+    xyz (b,n,3), points (b,n,c), idx (b,m,nsample) int32 -> (b,m,nsample,3), (b,m,nsample,c); identical results.
+    """
+    xyz = dev_tensor(xyz, torch.float32, "xyz")
+    points = dev_tensor(points, torch.float32, "points")
+    idx = dev_tensor(idx, torch.int32, "idx")
+    require(xyz.dim() == 3 and xyz.shape[2] == 3, "GroupPoint expects (batch_size, num_points, 3) xyz shape")
+    require(points.dim() == 3 and points.shape[0] == xyz.shape[0] and points.shape[1] == xyz.shape[1],
+            "GroupPoint expects (batch_size, num_points, channel) points shape")
+    b, n, c = points.shape
+    require(idx.dim() == 3 and idx.shape[0] == b, "GroupPoint expects (batch_size, npoints, nsample) idx shape")
+    m, nsample = idx.shape[1], idx.shape[2]
+    out_xyz = torch.empty((b, m, nsample, 3), dtype=torch.float32, device=points.device)
+    out = torch.empty((b, m, nsample, c), dtype=torch.float32, device=points.device)
+    with torch.cuda.device(points.device):
+        rc = _lib.load().hf_group_point_pair(b, n, c, m, nsample, xyz.data_ptr(), points.data_ptr(), idx.data_ptr(),
+                                             out_xyz.data_ptr(), out.data_ptr(), stream_ptr(points.device))
+    _lib.check(rc, "group_point")
+    return out_xyz, out
+
+
 def group_point_grad(points, idx, grad_out):
     """Gradient of group_point w.r.t. points (the reference's GroupPointGrad op,
     grouping/tf_grouping.py:55-59, op checks grouping/tf_grouping.cpp:173-208).

@@ -166,6 +166,16 @@ int hf_three_nn_weights(int b, int n, int m, const float *unknown, const float *
  * points (b,n,c), idx (b,m,nsample) -> out (b,m,nsample,c). */
 int hf_group_point(int b, int n, int c, int m, int nsample, const float *points, const int *idx,
                    float *out, hf_stream_t stream);
+/* The two group_point calls of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49,56 — the
+ * coordinates and the features of the same neighbourhoods) in one pass over idx: xyz (b,n,3) -> out_xyz (b,m,nsample,3)
+ * and points (b,n,c) -> out_points (b,m,nsample,c).  Identical to two hf_group_point calls. */
+int hf_group_point_pair(int b, int n, int c, int m, int nsample, const float *xyz, const float *points, const int *idx,
+                        float *out_xyz, float *out_points, hf_stream_t stream);
+/* Tuning override (per calling thread): 1 = group_point with c % 4 == 0 moves its rows with TMA bulk copies
+ * (cp.async.bulk global -> shared per gathered row, one bulk copy shared -> global per stage of rows); 0 (default) =
+ * the register-path kernel, which measures faster for rows of 0.4-2 KB (profiles/r2_gather_bench_tma_rows.txt).
+ * Results are identical. */
+void hf_gather_set_mode(int bulk);
 /* The tail of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49-60) in one pass:
  * out (b,m,nsample,3+c) = concat(xyz[idx] - new_xyz (translation normalisation), points[idx]); c = 0 (points
  * NULL) gives the translated grouped_xyz alone.  Replaces two group_point calls, a tile + subtract and a concat. */
@@ -191,6 +201,7 @@ int hf_three_interpolate(int b, int c, int m, int n, const float *points, const 
  * points (b,m,c), idx/weight (b,n,3) -> out (b,n,c). */
 int hf_three_interpolate_nlc(int b, int m, int c, int n, const float *points, const int *idx,
                              const float *weight, float *out, hf_stream_t stream);
+
 
 /* ---- cropping ----------------------------------------------------------- */
 /* Replaces pccropandsample_gpu(...), cropping/tf_cropping_g.cu:152 together with the

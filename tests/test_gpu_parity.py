@@ -330,6 +330,41 @@ def test_group_point(cuda, oracle, c):
     assert np.array_equal(N(got), oracle.group_point(pts, idx))
 
 
+@pytest.mark.parametrize("c", [1, 2, 3, 4, 7, 96, 130, 256, 512])
+@pytest.mark.parametrize("b,n,m,ns", [(2, 500, 37, 9), (17, 300, 64, 32), (1, 5, 3, 1)])
+def test_group_point_pair(cuda, oracle, c, b, n, m, ns):
+    """The coordinates and the features of the same neighbourhoods in one launch (pointnet_util.py:49,56): every kernel
+    behind the entry — 128-bit rows with the coordinates on 12 lanes, thread-per-row for c <= 4, two launches otherwise."""
+    from heterofusionrcnn_b200.grouping.tf_grouping import group_point_pair
+
+    rng = np.random.default_rng(c + n)
+    xyz = rng.standard_normal((b, n, 3)).astype(np.float32)
+    pts = rng.standard_normal((b, n, c)).astype(np.float32)
+    idx = rng.integers(0, n, (b, m, ns)).astype(np.int32)
+    gx, gp = group_point_pair(T(xyz, cuda), T(pts, cuda), T(idx, cuda))
+    assert tuple(gx.shape) == (b, m, ns, 3) and tuple(gp.shape) == (b, m, ns, c)
+    assert np.array_equal(N(gx), oracle.group_point(xyz, idx))
+    assert np.array_equal(N(gp), oracle.group_point(pts, idx))
+
+
+@pytest.mark.parametrize("c", [4, 96, 256, 512, 1024, 4096, 8192])
+def test_group_point_tma_row_mover(cuda, oracle, c):
+    """hf_gather_set_mode(1): rows moved by cp.async.bulk (global -> shared per gathered row, one bulk copy shared ->
+    global per stage).  Opt-in (slower than the register kernel for these row sizes); rows beyond a stage (16 KB) take
+    the register kernel."""
+    from heterofusionrcnn_b200 import _lib
+
+    rng = np.random.default_rng(c)
+    pts = rng.standard_normal((3, 700, c)).astype(np.float32)
+    idx = rng.integers(0, 700, (3, 41, 13)).astype(np.int32)
+    _lib.load().hf_gather_set_mode(1)
+    try:
+        got = group_point(T(pts, cuda), T(idx, cuda))
+    finally:
+        _lib.load().hf_gather_set_mode(0)
+    assert np.array_equal(N(got), oracle.group_point(pts, idx))
+
+
 # ---------------------------------------------------------------- three_nn / interpolate
 @pytest.mark.parametrize("b,n,m", [(2, 16384, 4096), (2, 4096, 1024), (3, 1024, 256), (2, 256, 64), (2, 333, 1027),
                                    (1, 10, 2), (1, 5, 1)])
@@ -372,6 +407,26 @@ def test_three_interpolate(cuda, oracle, c):
     assert close(got, want) and np.array_equal(got, want)
     cf = N(three_interpolate_channel_first(T(pts.transpose(0, 2, 1), cuda), T(idx, cuda), T(w, cuda)))
     assert np.array_equal(cf.transpose(0, 2, 1), want)
+
+
+@pytest.mark.parametrize("b,n,m,c", [(2, 16384, 4096, 128), (3, 4096, 1024, 512), (2, 701, 300, 132), (1, 33, 7, 4),
+                                     (2, 5000, 1000, 3), (2, 1000, 256, 260), (2, 300, 64, 1024), (1, 1, 5, 8),
+                                     (17, 300, 100, 64)])
+def test_three_interpolate_on_three_nn_geometry(cuda, oracle, b, n, m, c):
+    """Real three_nn indices and weights (neighbouring rows share sources), ragged sizes, more scenes than one CTA row of
+    the grid covers, and the reference kernel's own output in its channel-first layout."""
+    from heterofusionrcnn_b200.interpolate.tf_interpolate import three_nn_weights
+
+    xyz, _ = synthetic.make_scans(50 + n, b, n)
+    unk = T(xyz, cuda)
+    kn = gather_point(unk, farthest_point_sample(m, unk))
+    _, nidx, w = three_nn_weights(unk, kn)
+    pts = torch.randn((b, m, c), device=cuda)
+    got = three_interpolate(pts, nidx, w)
+    assert np.array_equal(N(got), oracle.three_interpolate(N(pts), N(nidx), N(w)))
+    if _refcuda.available():
+        ref = _refcuda.three_interpolate_channel_first(pts.transpose(1, 2).contiguous(), nidx, w)
+        assert torch.equal(got, ref.transpose(1, 2))
 
 
 # ---------------------------------------------------------------- crop
