@@ -104,7 +104,13 @@ struct MpShared {
 //   nxt     (m,3) shared or null: the same, a full copy in EVERY CTA (the next level's cloud)
 // `round` is the cluster-wide exchange round counter: it runs on across the levels of one launch, so the two
 // mbarriers keep their phase (each is armed for round + 2 right after it completed for round).
-template <int C, int W, int PTS, class Load>
+// CH = 0: the coordinates of a thread's PTS points stay in registers.  CH > 0: only the running distances do; the
+// coordinates are re-read from the CTA's shared-memory copy every round, CH points at a time (3 conflict-free LDS per
+// point and round against 6.5 FP32 instructions per point and accepted centre: hidden behind the arithmetic).  That
+// halves the registers per point, so a CTA holds 16384 points (512 threads x 32) instead of 8192 and a 65536-point
+// cloud needs 4 SMs instead of 8: 16 scans run in one wave where the register shape needs two (a B200 co-schedules 15
+// clusters of 8, tools/gpc_probe.cu).
+template <int C, int W, int PTS, int CH = 0, class Load>
 __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__restrict__ idxs,
                                                 float *__restrict__ oxyz, float *nxt, float *sx,
                                                 MpShared<C * W, W> &sh, int &round) {
@@ -130,24 +136,27 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
     };
     const uint32_t u = grp + (uint32_t)G * lane;
 
-    float x[PTS], y[PTS], z[PTS], td[PTS];
+    constexpr int XR = CH > 0 ? CH : PTS;  // coordinates held in registers at a time
+    static_assert(CH == 0 || PTS % CH == 0, "the chunk must divide the points per thread");
+    float x[XR], y[XR], z[XR], td[PTS];
 #pragma unroll
     for (int p = 0; p < PTS; ++p) {
         const int li = p * T + t;  // local copy, conflict free
         const uint32_t k = kof(u, p);
+        float3 v = make_float3(0.f, 0.f, 0.f);
+        td[p] = -1.f;  // padding: never a candidate
         if (k < (uint32_t)n) {
-            const float3 v = load(k);
+            v = load(k);
+            td[p] = 1e38f;  // tf_sampling_g.cu:118
+        }
+        if (CH == 0) {
             x[p] = v.x;
             y[p] = v.y;
             z[p] = v.z;
-            td[p] = 1e38f;  // tf_sampling_g.cu:118
-        } else {
-            x[p] = y[p] = z[p] = 0.f;
-            td[p] = -1.f;  // padding: never a candidate
         }
-        sx[li] = x[p];
-        sy[li] = y[p];
-        sz[li] = z[p];
+        sx[li] = v.x;
+        sy[li] = v.y;
+        sz[li] = v.z;
     }
     if (lane < 8) pos[warp][lane] = 0;
     const float3 first = load(0);  // every thread reads it BEFORE the barrier: `nxt` may alias the cloud `load` reads
@@ -193,7 +202,33 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
         const int buf = round & 1;
         const uint32_t(*cs)[MP_SLOT_W] = slots[buf ^ 1];  // centres accepted last round
         // ---- 1. lower td against the A new centres, two at a time (min is exact in any order) ----
-        {
+        if constexpr (CH > 0) {
+#pragma unroll
+            for (int c0 = 0; c0 < PTS; c0 += CH) {
+#pragma unroll
+                for (int q = 0; q < CH; ++q) {
+                    const int li = (c0 + q) * T + t;
+                    x[q] = sx[li];
+                    y[q] = sy[li];
+                    z[q] = sz[li];
+                }
+                int i = 0;
+                for (; i + 2 <= A; i += 2) {
+                    const float4 a = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * i)) & 0xffu]);
+                    const float4 b2 = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * (i + 1))) & 0xffu]);
+#pragma unroll
+                    for (int q = 0; q < CH; ++q)
+                        td[c0 + q] = fminf(fminf(sqdist(x[q] - a.x, y[q] - a.y, z[q] - a.z),
+                                                 sqdist(x[q] - b2.x, y[q] - b2.y, z[q] - b2.z)),
+                                           td[c0 + q]);
+                }
+                if (i < A) {
+                    const float4 a = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * i)) & 0xffu]);
+#pragma unroll
+                    for (int q = 0; q < CH; ++q) td[c0 + q] = fminf(sqdist(x[q] - a.x, y[q] - a.y, z[q] - a.z), td[c0 + q]);
+                }
+            }
+        } else {
             int i = 0;
             float4 c0 = *reinterpret_cast<const float4 *>(cs[(uint32_t)posw & 0xffu]);
             float4 c1 = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> 8) & 0xffu]);
@@ -345,7 +380,7 @@ __device__ __forceinline__ void mp_setup(MpShared<C * W, W> &sh) {
 }
 
 // One level: farthest_point_sample (+ gather_point when new_xyz != null).
-template <int C, int W, int PTS>
+template <int C, int W, int PTS, int CH = 0>
 __global__ void __launch_bounds__(W * 32, 1)
     fps_multi_kernel(int n, int m, const float *__restrict__ inp, int *__restrict__ out, float *__restrict__ new_xyz) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -354,7 +389,7 @@ __global__ void __launch_bounds__(W * 32, 1)
     const float *data = inp + (size_t)scene * n * 3;
     mp_setup<C, W>(sh);
     int round = 0;
-    fps_multi_level<C, W, PTS>(
+    fps_multi_level<C, W, PTS, CH>(
         n, m, [data](uint32_t k) { return make_float3(data[(size_t)k * 3], data[(size_t)k * 3 + 1], data[(size_t)k * 3 + 2]); },
         out + (size_t)scene * m, new_xyz ? new_xyz + (size_t)scene * m * 3 : nullptr, nullptr,
         reinterpret_cast<float *>(smem_raw), sh, round);
@@ -425,9 +460,9 @@ int launch_cluster(Kern kern, const char *name, int b, int C, int threads, size_
     return HF_OK;
 }
 
-template <int C, int W, int PTS>
+template <int C, int W, int PTS, int CH = 0>
 int launch_fps_multi(int b, int n, int m, const float *inp, int *out, float *new_xyz, cudaStream_t stream) {
-    return launch_cluster(fps_multi_kernel<C, W, PTS>, "fps_multi_kernel", b, C, W * 32, (size_t)3 * W * 32 * PTS * sizeof(float),
+    return launch_cluster(fps_multi_kernel<C, W, PTS, CH>, "fps_multi_kernel", b, C, W * 32, (size_t)3 * W * 32 * PTS * sizeof(float),
                           stream, n, m, inp, out, new_xyz);
 }
 
@@ -492,6 +527,15 @@ int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *o
         if (n <= 6 * 256 * 3) return launch_fps_multi<6, 8, 3>(b, n, m, inp, out, oxyz, s);
         return launch_fps_multi<6, 8, 11>(b, n, m, inp, out, oxyz, s);
     }
+    // Clouds of 16385..65536 points, more than 15 scans: 4 CTAs x 16 warps x 32 points with the coordinates in shared
+    // memory (196 KB per CTA), 4 SMs per scan.  The register shape (8 CTAs x 8 warps x 32 points) is twice as fast per
+    // scan (8.8 vs 16.4 ms for 65536 -> 16384: 16 warps per SM rank the 64 candidates redundantly and share the FP32
+    // pipe) but a B200 holds only 15 clusters of 8, so the 16th scan costs a second wave (16.5 ms): the same time on
+    // 64 SMs instead of all of them, the rest stays free for the kernels that run beside the sampling chain
+    // (profiles/r2_fps_65536_shapes.txt).  warps_req = 16 / 8 force the shared-memory / register shape.
+    if (n > 4 * 4096 && n <= 4 * 16384 && (cluster_req == 0 || cluster_req == 4) &&
+        (warps_req == 16 || (warps_req == 0 && b > 15)))
+        return launch_fps_multi<4, 16, 32, 8>(b, n, m, inp, out, oxyz, s);
     while (cluster < 8 && (n + cluster - 1) / cluster > 8192) cluster <<= 1;
     const int per = (n + cluster - 1) / cluster;
     switch (cluster) {

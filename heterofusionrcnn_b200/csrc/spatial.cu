@@ -726,7 +726,9 @@ bool spatial_applies(int nq, int nc) {
     if (g_spatial_mode == 1) return false;
     if (nq < 1 || nc < 1 || nq > kMaxCloud || nc > kMaxCloud) return false;
     if (g_spatial_mode == 2) return true;
-    return nq >= 64 && nc >= 64 && (long long)nq * nc >= (1ll << 24);  // measured: tools/spatial_bench.py
+    // measured (tools/spatial_bench.py, profiles/r2_spatial_bench.txt): 1024 queries in 4096 points, 16 scans: ball query
+    // 92 -> 58 us including both sorts (33 us with the indices prebuilt), three_nn 84 -> 71 (45) us; 256 in 1024: no gain
+    return nq >= 64 && nc >= 64 && (long long)nq * nc >= (1ll << 22);
 }
 
 // knn_point profits from the sort much earlier (tools/knn_bench.py: 4096 x 1024, k = 32: 0.08 vs 0.41 ms).

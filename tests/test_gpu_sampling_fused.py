@@ -72,6 +72,22 @@ def test_fps_cluster_of_six(cuda, oracle):
         assert np.array_equal(N(got), want), (n, m)
 
 
+@pytest.mark.parametrize("b,n,m,dup", [(2, 65536, 700, 9000), (1, 20000, 300, 0), (2, 40000, 512, 3000), (1, 16385, 64, 0)])
+def test_fps_shared_memory_shape(cuda, oracle, b, n, m, dup):
+    """Clouds of 16385..65536 points with the coordinates in shared memory (4 CTAs x 16 warps, the shape batches of more
+    than 15 scans take): forced here for small batches, against the oracle."""
+    xyz, _ = synthetic.make_scans(401 + n + m, b, n, duplicate_pad=dup)
+    want = oracle.farthest_point_sample(m, xyz)
+    lib = _lib.load()
+    lib.hf_fps_set_variant(3, 16, 0)
+    try:
+        idx, pts = farthest_point_sample_with_xyz(m, T(xyz, cuda))
+    finally:
+        lib.hf_fps_set_variant(0, 0, 0)
+    assert np.array_equal(N(idx), want)
+    assert np.array_equal(N(pts), oracle.gather_point(xyz, want))
+
+
 def _level_by_level(x, ms):
     idxs, pts = [], []
     for m in ms:

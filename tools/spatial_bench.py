@@ -48,6 +48,20 @@ def main():
                 print("level %d  ball      n=%5d m=%5d r=%4.1f     %-10s %8.4f ms  (mean cnt %.1f)" % (
                     lvl + 1, a.shape[1], q.shape[1], r, name, ms, cnt))
             sys.stdout.flush()
+    lib.hf_spatial_set_mode(2)
+    # prebuilt indices (what chain.run_chain does): build time per cloud, then the pruned kernels alone
+    from heterofusionrcnn_b200 import spatial
+    from heterofusionrcnn_b200.interpolate.tf_interpolate import three_nn_weights
+    ix = [spatial.build_cloud_index(c) for c in x]
+    for lvl, c in enumerate(x):
+        ms = timeit(lambda: spatial.build_cloud_index(c))
+        print("cloud_index level %d n=%5d  %8.4f ms" % (lvl, c.shape[1], ms))
+    for lvl, r in [(0, 0.1), (1, 0.2), (2, 0.4)]:
+        a, q = x[lvl], x[lvl + 1]
+        ms = timeit(lambda: three_nn_weights(a, q, index1=ix[lvl], index2=ix[lvl + 1]))
+        print("level %d  three_nn  n=%5d m=%5d            prebuilt   %8.4f ms" % (lvl + 1, a.shape[1], q.shape[1], ms))
+        ms = timeit(lambda: query_ball_point(r, 32, a, q, index1=ix[lvl], index2=ix[lvl + 1]))
+        print("level %d  ball      n=%5d m=%5d r=%4.1f     prebuilt   %8.4f ms" % (lvl + 1, a.shape[1], q.shape[1], r, ms))
     lib.hf_spatial_set_mode(0)
 
 
