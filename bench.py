@@ -181,6 +181,34 @@ def work(name, m):
     return "other", 0, 0
 
 
+def count_pair_evals(torch, hf, chain, resident, cfg):
+    """-> {launch key: (query, candidate) distance evaluations executed by that launch}; 0 entries for launches that
+    took an every-pair kernel (they execute the full count)."""
+    counter = torch.zeros((1,), dtype=torch.int64, device=resident["xyz"].device)
+    lib = hf.load()
+    found = {}
+
+    @contextlib.contextmanager
+    def probe(name, **meta):
+        if name not in ("three_nn", "query_ball_point"):
+            yield
+            return
+        torch.cuda.synchronize()
+        before = int(counter.item())
+        yield
+        torch.cuda.synchronize()
+        key = name + "".join("/%s=%s" % (k, meta[k]) for k in ("level", "c") if k in meta)
+        found[key] = int(counter.item()) - before
+
+    lib.hf_spatial_set_pair_counter(counter.data_ptr())
+    try:
+        chain.run_chain(resident, cfg, probe, overlap=False)
+        torch.cuda.synchronize()
+    finally:
+        lib.hf_spatial_set_pair_counter(None)
+    return found
+
+
 class EventProbe:
     """Brackets every op of chain.run_chain with CUDA events on the launching (current) stream."""
 
@@ -213,7 +241,7 @@ class EventProbe:
             bound, nbytes, flops = work(a["name"], a["meta"])
             avg = a["ms"] / a["n"]
             out.append({"launch": key, "bound": bound, "ms": round(avg, 5), "per_step": a["n"] // max(steps, 1),
-                        "bytes": nbytes, "flops": flops})
+                        "bytes": nbytes, "flops": flops, "meta": a["meta"]})
         return out
 
 
@@ -584,6 +612,9 @@ def run_b200(args):
     torch.cuda.synchronize()
     alone_ms = {o["launch"]: o["ms"] for o in alone.summarise(min(args.steps, 5))}
     serial_step_ms = sum(o["ms"] * o["per_step"] for o in alone.summarise(min(args.steps, 5)))
+    # distance evaluations the pruned ball query / three_nn launches EXECUTE (the kernels count them when a device
+    # counter is set): one more serial pass, outside every timed region
+    pair_evals = count_pair_evals(torch, hf, chain, resident, cfg)
 
     # ---- end to end: host buffers in, host-consumed results out, through the public op API ----
     e2e = None
@@ -754,6 +785,17 @@ def run_b200(args):
         o["frac_alone"] = (a / o["peak"]) if a and o["peak"] else None
         # share of the serial (one-stream) step: with overlap the in-region durations add up to more than the step
         o["share_of_step"] = (o["ms_alone"] or o["ms"]) * o["per_step"] / serial_step_ms
+        # pruned launches: `frac` above divides the EVERY-PAIR flop count of SURVEY 8d by the pruned kernel's time (an
+        # equivalent rate: it can exceed 1); frac_executed divides the evaluations the kernel really ran
+        ex = pair_evals.get(o["launch"], 0)
+        o["pair_evals_executed"] = ex or None
+        o["pair_evals_every_pair"] = (o["meta"]["b"] * o["meta"]["n"] * o["meta"]["m"]) if ex else None
+        if ex and o["flops"] and o["ms_alone"]:
+            per_pair = o["flops"] / o["pair_evals_every_pair"]
+            o["frac_equivalent"], o["frac_alone_equivalent"] = o["frac"], o["frac_alone"]
+            o["frac"] = per_pair * ex / (o["ms"] / 1e3) / 1e12 / FP32_PEAK_TFLOPS
+            o["frac_alone"] = per_pair * ex / (o["ms_alone"] / 1e3) / 1e12 / FP32_PEAK_TFLOPS
+            o["achieved"] = per_pair * ex / (o["ms"] / 1e3) / 1e12
     ops.sort(key=lambda o: -(o["ms_alone"] or o["ms"]) * o["per_step"])
     own = [o for o in ops if o["bound"] != "other"]
     top_fps = max((o for o in own if o["launch"].startswith("fps/")), key=lambda o: o["ms"])
@@ -788,8 +830,10 @@ def run_b200(args):
         # the whole step against the HBM roofline: algorithmic bytes of every launch of the step / step time
         "roofline_step": {"bound": "hbm", "algorithmic_bytes": step_bytes, "achieved": step_bytes / (ms / args.steps) / 1e6,
                           "peak": hbm_peak, "unit": "GB/s", "frac": step_bytes / (ms / args.steps) / 1e6 / hbm_peak},
-        "roofline_ops": [{k: o[k] for k in ("launch", "bound", "ms", "ms_alone", "per_step", "achieved", "unit", "frac",
-                                            "frac_alone", "share_of_step")} for o in ops],
+        "roofline_ops": [{k: o.get(k) for k in ("launch", "bound", "ms", "ms_alone", "per_step", "achieved", "unit", "frac",
+                                                "frac_alone", "share_of_step", "pair_evals_executed", "pair_evals_every_pair",
+                                                "frac_equivalent", "frac_alone_equivalent")
+                          if o.get(k) is not None or k in ("frac", "frac_alone", "achieved", "unit")} for o in ops],
         "serial_ms_per_step": serial_step_ms,
         "fp32_peak": fp32,
         "config5": config5,
@@ -812,7 +856,7 @@ def run_b200(args):
 
 NCU_KERNEL_OF = {  # probe name -> (kernel name fragment, grid) in the committed ncu --set full summary
     "pc_crop_and_sample/c=288": ("crop_kernel", "(8192, 1, 1)"),
-    "fps/level=1": ("fps_", None),
+    "fps/level=1": ("fps_multi_kernel", None),
 }
 
 
@@ -832,21 +876,22 @@ def ncu_traffic(launch, build_id):
         return None, "no capture is kept for this launch"
     frag, grid = NCU_KERNEL_OF[launch]
 
-    def version(path):  # r<round>_ncu_full_v<pass>_summary.csv -> (round, pass): numeric, not lexicographic
-        m = re.search(r"r(\d+)_ncu_full_v(\d+)_summary", os.path.basename(path))
-        return (int(m.group(1)), int(m.group(2))) if m else (0, 0)
-
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_*_summary.csv")), key=version)
+    # every committed summary names the build it was taken from in its first line; use the one of THIS build
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full_*_summary.csv")), key=os.path.getmtime)
     if not files:
         return None, "no capture under profiles/"
-    path = files[-1]
+    path, rows, seen = None, None, []
+    for f in files:
+        first = open(f).readline()
+        m = re.search(r"build=([0-9a-f]{12})", first)
+        seen.append(m.group(1) if m else "-")
+        if m and m.group(1) == build_id:
+            path = f
+    if path is None:
+        return None, "no committed ncu --set full summary was taken from build %s (captures of builds %s): not used" % (
+            build_id, ", ".join(sorted(set(seen))))
     rows = list(csv.reader(open(path)))
-    m = re.search(r"build=([0-9a-f]{12})", rows[0][0] if rows and rows[0] else "")
     name = "profiles/" + os.path.basename(path)
-    if not m:
-        return None, "%s does not name its build (taken before builds carried an id): not used" % name
-    if m.group(1) != build_id:
-        return None, "%s is a capture of build %s, the library is build %s: not used" % (name, m.group(1), build_id)
     hdr, units = rows[1], rows[2]
     ci = {h: i for i, h in enumerate(hdr)}
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}

@@ -40,6 +40,7 @@ SIGNATURES = {
     "hf_query_ball_point": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_spatial_workspace_bytes": (_size_t, [_c_int, _c_int, _c_int]),
     "hf_spatial_set_mode": (None, [_c_int]),
+    "hf_spatial_set_pair_counter": (None, [_ptr]),
     "hf_query_ball_point_ws": (_c_int, [_c_int, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t,
                                         _ptr]),
     "hf_three_nn_ws": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),

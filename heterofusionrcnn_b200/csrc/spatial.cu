@@ -324,7 +324,8 @@ __device__ __forceinline__ float point_gap2(const float4 &q, const float4 &clo, 
 __global__ void __launch_bounds__(kSqWarps * 32)
     ball_query_indexed_kernel(int m, int nsample, float thr2, int nbq, int nbc, const float4 *__restrict__ sortedQ,
                               const float4 *__restrict__ boxesQ, const float4 *__restrict__ sortedC,
-                              const float4 *__restrict__ boxesC, int *__restrict__ idx, int *__restrict__ pts_cnt) {
+                              const float4 *__restrict__ boxesC, int *__restrict__ idx, int *__restrict__ pts_cnt,
+                              unsigned long long *__restrict__ pair_counter) {
     extern __shared__ __align__(16) unsigned char sq_smem[];
     __shared__ int cnts[kSqWarps + 1][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -377,7 +378,9 @@ __global__ void __launch_bounds__(kSqWarps * 32)
     int cur = next();
     float4 vcur = make_float4(0.f, 0.f, 0.f, 0.f);
     if (cur >= 0) vcur = __ldg(&sortedC[(size_t)cur * 32 + lane]);
+    unsigned visited = 0;  // buckets of 32 candidates this warp tested against its 32 queries
     while (cur >= 0) {
+        ++visited;
         const int nxt = next();  // its candidates are in flight while the current bucket is tested
         float4 vnxt = vcur;
         if (nxt >= 0) vnxt = __ldg(&sortedC[(size_t)nxt * 32 + lane]);
@@ -407,6 +410,7 @@ __global__ void __launch_bounds__(kSqWarps * 32)
         cur = nxt;
         vcur = vnxt;
     }
+    if (pair_counter && lane == 0 && visited) atomicAdd(pair_counter, (unsigned long long)visited * 1024ull);
     // ascending index order (insertion sort of this lane's <= nsample hits)
     for (int a = 1; a < cnt; ++a) {
         const int v = rows[a * 33 + lane];
@@ -464,7 +468,7 @@ __global__ void __launch_bounds__(kSqWarps * 32)
     three_nn_indexed_kernel(int n, int nbq, int nbc, const float4 *__restrict__ sortedQ,
                             const float4 *__restrict__ boxesQ, const float4 *__restrict__ sortedC,
                             const float4 *__restrict__ boxesC, float *__restrict__ dist2, int *__restrict__ idx,
-                            float *__restrict__ weight) {
+                            float *__restrict__ weight, unsigned long long *__restrict__ pair_counter) {
     __shared__ __align__(16) float4 tiles[kSqWarps * 32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int scene = blockIdx.y;
@@ -483,7 +487,9 @@ __global__ void __launch_bounds__(kSqWarps * 32)
     float b1 = INFINITY, b2 = INFINITY, b3 = INFINITY;
     int i1 = 0, i2 = 0, i3 = 0;
 
+    unsigned visited = 0;  // buckets of 32 candidates this warp tested against its 32 queries
     auto visit = [&](int cb) {
+        ++visited;
         stage_bucket(tile, sortedC, cb, lane);
 #pragma unroll 8
         for (int j = 0; j < 32; ++j) {
@@ -540,6 +546,7 @@ __global__ void __launch_bounds__(kSqWarps * 32)
             thr = threshold();
         }
     }
+    if (pair_counter && lane == 0) atomicAdd(pair_counter, (unsigned long long)visited * 1024ull);
     if (qi >= 0) {
         float *dd = dist2 + ((size_t)scene * n + qi) * 3;
         int *ii = idx + ((size_t)scene * n + qi) * 3;
@@ -763,6 +770,10 @@ int launch_index(int b, const CloudDesc &a, const CloudDesc *second, cudaStream_
     return HF_OK;
 }
 
+// hf_spatial_set_pair_counter: device counter the pruned ball query / three_nn add their executed (query, candidate)
+// distance evaluations to (measurement aid; per calling thread, NULL = off)
+thread_local unsigned long long *g_pair_counter = nullptr;
+
 int launch_ball_query(int b, int m, float radius, int nsample, const CloudDesc &q, const CloudDesc &c, int *idx,
                       int *pts_cnt, cudaStream_t s) {
     const size_t rowbytes = (size_t)kSqWarps * 32 * sizeof(float4) + (size_t)(kSqWarps + 1) * nsample * 33 * sizeof(int);
@@ -770,7 +781,8 @@ int launch_ball_query(int b, int m, float radius, int nsample, const CloudDesc &
     if (rowbytes > 48 * 1024)
         HF_CUDA_OK(cudaFuncSetAttribute(ball_query_indexed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rowbytes));
     ball_query_indexed_kernel<<<dim3(nbq, b), kSqWarps * 32, rowbytes, s>>>(m, nsample, ball_threshold(radius), nbq, nbc,
-                                                                           q.sorted, q.boxes, c.sorted, c.boxes, idx, pts_cnt);
+                                                                           q.sorted, q.boxes, c.sorted, c.boxes, idx, pts_cnt,
+                                                                           g_pair_counter);
     HF_LAUNCH_OK("ball_query_indexed_kernel");
     return HF_OK;
 }
@@ -779,7 +791,7 @@ int launch_three_nn(int b, int n, const CloudDesc &q, const CloudDesc &c, float 
                     cudaStream_t s) {
     const int nbq = q.npad / 32, nbc = c.npad / 32;
     three_nn_indexed_kernel<<<dim3((nbq + kSqWarps - 1) / kSqWarps, b), kSqWarps * 32, 0, s>>>(
-        n, nbq, nbc, q.sorted, q.boxes, c.sorted, c.boxes, dist2, idx, weight);
+        n, nbq, nbc, q.sorted, q.boxes, c.sorted, c.boxes, dist2, idx, weight, g_pair_counter);
     HF_LAUNCH_OK("three_nn_indexed_kernel");
     return HF_OK;
 }
@@ -790,6 +802,7 @@ inline bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 }  // namespace hf
 
 extern "C" void hf_spatial_set_mode(int mode) { hf::g_spatial_mode = mode; }
+extern "C" void hf_spatial_set_pair_counter(unsigned long long *device_counter) { hf::g_pair_counter = device_counter; }
 extern "C" int hf_spatial_applies(int nq, int nc) { return hf::spatial_applies(nq, nc) ? 1 : 0; }
 
 extern "C" size_t hf_cloud_index_bytes(int b, int n) {

@@ -132,6 +132,11 @@ int hf_query_ball_point(int b, int n, int m, float radius, int nsample, const fl
  * hf_spatial_set_mode: 0 = auto, 1 = never pruned, 2 = pruned whenever a shape exists (tests). */
 size_t hf_spatial_workspace_bytes(int b, int n, int m);
 void hf_spatial_set_mode(int mode);
+/* Measurement aid (per calling thread): while device_counter != NULL the pruned ball query / three_nn kernels launched
+ * by this thread add the (query, candidate) distance evaluations they actually execute to *device_counter (one
+ * atomicAdd per warp; 1024 per visited bucket of 32 candidates x 32 queries).  bench.py divides them, not the
+ * every-pair count, by the launch time for the FP32 fraction of these kernels. */
+void hf_spatial_set_pair_counter(unsigned long long *device_counter);
 int hf_query_ball_point_ws(int b, int n, int m, float radius, int nsample, const float *xyz1,
                            const float *xyz2, int *idx, int *pts_cnt, void *workspace,
                            size_t workspace_bytes, hf_stream_t stream);

@@ -535,9 +535,15 @@ def test_bev_iou_known_answers_and_oracle(cuda, oracle):
     wo, wi = oracle.compute_bev_iou(boxes[:300], boxes[300:])
     go, gi = compute_bev_iou(T(boxes[:300], cuda), T(boxes[300:], cuda))
     assert (wo > 0).mean() > 0.05
-    # libdevice vs glibc sin/cos/atan2 differ in the last ulps: float tolerance, and exact zeros agree
-    assert np.allclose(N(go), wo, rtol=1e-4, atol=1e-5) and np.allclose(N(gi), wi, rtol=1e-4, atol=1e-5)
+    # libdevice vs glibc sinf/cosf/atan2f differ in the last ulps (the oracle runs on the host): each side is within
+    # north_star's 1e-5 of the reference kernel (test_bev_iou_matches_reference_kernel, test_oracle_golden.py), so the
+    # two are within 2e-5 of each other; the observed maximum over these 120 000 pairs is printed (pytest -s)
     assert np.array_equal(N(go) == 0, wo == 0)
+    for name, got, want in (("overlap", N(go), wo), ("iou", N(gi), wi)):
+        nz = want != 0
+        rel = np.abs(got[nz].astype(np.float64) - want[nz]) / np.abs(want[nz])
+        print("bev_iou %s: %d non-zero pairs, max relative difference CUDA vs host oracle %.3g" % (name, nz.sum(), rel.max()))
+        assert np.allclose(got, want, rtol=2e-5, atol=1e-6), (name, rel.max())
 
 
 @needs_ref

@@ -96,8 +96,10 @@ def test_iou_oracle_close_to_reference_kernel(oracle, gold):
     ov, iou = oracle.compute_bev_iou(inp["a"], inp["b"])
     assert (gold["iou_a.overlap"] > 0).mean() > 0.1
     assert np.array_equal(ov == 0, gold["iou_a.overlap"] == 0)
-    assert np.allclose(ov, gold["iou_a.overlap"], rtol=1e-4, atol=1e-5)  # glibc vs libdevice sin/cos/atan2
-    assert np.allclose(iou, gold["iou_a.iou"], rtol=1e-4, atol=1e-5)
+    # north_star's bar for float outputs: 1e-5 relative.  The host oracle (glibc sinf/cosf/atan2f) against the
+    # reference kernel's output captured on a B200 (libdevice): observed maxima 8.4e-6 (overlap) / 9.97e-6 (iou)
+    assert np.allclose(ov, gold["iou_a.overlap"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(iou, gold["iou_a.iou"], rtol=1e-5, atol=1e-6)
 
 
 def test_nms_mask_oracle_equals_reference_kernel(oracle, gold):
