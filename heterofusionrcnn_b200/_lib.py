@@ -30,6 +30,7 @@ SIGNATURES = {
     "hf_fp32_probe": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr]),
     "hf_farthest_point_sample": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_farthest_point_sample_xyz": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "hf_farthest_point_sample_indexed": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_fps_pyramid": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_fps_set_cluster": (None, [_c_int]),
     "hf_fps_set_threads": (None, [_c_int]),

@@ -49,6 +49,10 @@ class ChainConfig:
     # grouping: the coordinates and the features of a level's neighbourhoods in one launch (group_point_pair);
     # False = two group_point launches per level (pointnet_util.py:49,56)
     fused_grouping: bool = True
+    # level-1 FPS over the input's spatial index (warps skip the centres that cannot reach them): None = where it
+    # pays, i.e. clouds above 16384 points (65536: 8.8 -> 6.3 ms per launch; at 16384 points the wait for the index
+    # costs what the skipping saves, profiles/r2_fps_sorted_probe.txt)
+    sorted_fps: object = None
 
     def scaled(self, points):
         """Same chain on a different cloud size (npoint = n/4 per level)."""
@@ -304,8 +308,11 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                 fps_idx.append(idx)
                 xyz.append(new_xyz)
             elif l == 0 or len(n_lv) - 1 - l > PYRAMID_MAX_LEVELS:
+                ix = index[0] if (l == 0 and sorted_fps) else None
+                if ix is not None:
+                    after(crit, index_ready[0])
                 with probe("fps", level=l + 1, b=b, n=n, m=m, xyz=1):
-                    idx, new_xyz = farthest_point_sample_with_xyz(m, xyz[l])
+                    idx, new_xyz = farthest_point_sample_with_xyz(m, xyz[l], index=ix)
                 fps_idx.append(idx)
                 xyz.append(new_xyz)
             else:
@@ -320,17 +327,20 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
     # so its clusters take their SMs while the GPU is still empty.  In program order (overlap=False) the
     # independent branches keep the reference's order instead.
     have_xyz = [None] * 4
-    if overlap:
-        have_xyz[0] = sample_level(0)
     # spatial index of each level's cloud, built once and shared by ball query and three_nn of the
     # two levels that search it (only where the calls are large enough to take the pruned kernels).
     # The input's index needs whole SMs (1024-thread CTAs): it goes out before the crop floods the GPU.
     use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
     index, index_ready = [None] * 5, [None] * 5
+    sorted_fps = use_ix[0] and (cfg.sorted_fps if cfg.sorted_fps is not None else cfg.points > 16384)
+    if overlap and not sorted_fps:
+        have_xyz[0] = sample_level(0)
     if use_ix[0]:
         with on(s_group[0]), probe("cloud_index", level=0, b=b, n=n_lv[0]):
             index[0] = spatial.build_cloud_index(xyz[0])  # needs only the input: overlaps FPS level 1
         index_ready[0] = mark(s_group[0])
+    if overlap and sorted_fps:  # the level-1 FPS reads the cloud through its index: right behind it
+        have_xyz[0] = sample_level(0)
     if cfg.with_nms:
         with on(s_nms), probe("oriented_nms", b=b, nb=cfg.nms_boxes):
             keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)

@@ -110,7 +110,16 @@ struct MpShared {
 // halves the registers per point, so a CTA holds 16384 points (512 threads x 32) instead of 8192 and a 65536-point
 // cloud needs 4 SMs instead of 8: 16 scans run in one wave where the register shape needs two (a B200 co-schedules 15
 // clusters of 8, tools/gpc_probe.cu).
-template <int C, int W, int PTS, int CH = 0, class Load>
+//
+// SORTED: the cloud arrives in the order of its spatial index (spatial.cu: Hilbert-sorted {x, y, z, original index}
+// records, `load(s)` = record s, `load.first()` = original point 0) and a WARP holds 32 * PTS consecutive records, i.e.
+// a compact region of space with a bounding box.  A centre whose exact lower-bound distance to that box (same operation
+// sequence as sqdist, so LB <= fl(d) for every point inside) is not below the warp's current maximum td cannot lower any
+// td of the warp (fminf(d, td) == td): the warp skips it.  After the first few hundred picks four centres out of five
+// are skipped, and the distance update is the largest part of this kernel's instructions.  The picks are unchanged:
+// every candidate carries its ORIGINAL index in the key (shared-memory array behind the coordinates), and ties inside a
+// thread or a warp are resolved on that key instead of on the register order.
+template <int C, int W, int PTS, int CH = 0, bool SORTED = false, class Load>
 __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__restrict__ idxs,
                                                 float *__restrict__ oxyz, float *nxt, float *sx,
                                                 MpShared<C * W, W> &sh, int &round) {
@@ -121,8 +130,10 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
     static_assert(G <= 64, "at most 64 warps per scene");
     static_assert(PTS <= 32, "the equal-to-max mask is 32 bits");
     constexpr int CAP = T * PTS;  // points held by one CTA
+    static_assert(!SORTED || CH == 0, "the sorted shape keeps its coordinates in registers");
     float *sy = sx + CAP;
     float *sz = sy + CAP;
+    uint32_t *sorig = reinterpret_cast<uint32_t *>(sz + CAP);  // SORTED: original index of every point of this CTA
     auto &slots = sh.slots;
     auto &bars = sh.bars;
     auto &pos = sh.pos;
@@ -139,15 +150,32 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
     constexpr int XR = CH > 0 ? CH : PTS;  // coordinates held in registers at a time
     static_assert(CH == 0 || PTS % CH == 0, "the chunk must divide the points per thread");
     float x[XR], y[XR], z[XR], td[PTS];
+    float blx = INFINITY, bly = INFINITY, blz = INFINITY, bhx = -INFINITY, bhy = -INFINITY, bhz = -INFINITY;  // SORTED: warp box
 #pragma unroll
     for (int p = 0; p < PTS; ++p) {
         const int li = p * T + t;  // local copy, conflict free
-        const uint32_t k = kof(u, p);
         float3 v = make_float3(0.f, 0.f, 0.f);
         td[p] = -1.f;  // padding: never a candidate
-        if (k < (uint32_t)n) {
-            v = load(k);
-            td[p] = 1e38f;  // tf_sampling_g.cu:118
+        if constexpr (SORTED) {
+            const uint32_t s_ = grp * (32u * PTS) + (uint32_t)p * 32u + lane;  // a warp = 32 * PTS consecutive records
+            uint32_t orig = 0u;
+            if (s_ < (uint32_t)n) {
+                const float4 r = load(s_);
+                if (__float_as_int(r.w) >= 0) {
+                    v = make_float3(r.x, r.y, r.z);
+                    orig = (uint32_t)__float_as_int(r.w);
+                    td[p] = 1e38f;
+                    blx = fminf(blx, v.x); bly = fminf(bly, v.y); blz = fminf(blz, v.z);
+                    bhx = fmaxf(bhx, v.x); bhy = fmaxf(bhy, v.y); bhz = fmaxf(bhz, v.z);
+                }
+            }
+            sorig[li] = orig;
+        } else {
+            const uint32_t k = kof(u, p);
+            if (k < (uint32_t)n) {
+                v = load(k);
+                td[p] = 1e38f;  // tf_sampling_g.cu:118
+            }
         }
         if (CH == 0) {
             x[p] = v.x;
@@ -158,8 +186,24 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
         sy[li] = v.y;
         sz[li] = v.z;
     }
+    if constexpr (SORTED) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            blx = fminf(blx, __shfl_xor_sync(0xffffffffu, blx, o)); bly = fminf(bly, __shfl_xor_sync(0xffffffffu, bly, o));
+            blz = fminf(blz, __shfl_xor_sync(0xffffffffu, blz, o)); bhx = fmaxf(bhx, __shfl_xor_sync(0xffffffffu, bhx, o));
+            bhy = fmaxf(bhy, __shfl_xor_sync(0xffffffffu, bhy, o)); bhz = fmaxf(bhz, __shfl_xor_sync(0xffffffffu, bhz, o));
+        }
+    }
+    // original index of the point in register p of lane l_ of this warp (tie words are built from it)
+    auto orig_of = [&](int l_, int p) -> uint32_t {
+        if constexpr (SORTED) return sorig[p * T + warp * 32 + l_];
+        else return kof(grp + (uint32_t)G * (uint32_t)l_, p);
+    };
+    uint32_t wmax_prev = 0x7F800000u;  // SORTED: bits of the warp's maximum td after the previous round
     if (lane < 8) pos[warp][lane] = 0;
-    const float3 first = load(0);  // every thread reads it BEFORE the barrier: `nxt` may alias the cloud `load` reads
+    float3 first;  // every thread reads it BEFORE the barrier: `nxt` may alias the cloud `load` reads
+    if constexpr (SORTED) first = load.first();
+    else first = load(0);
     __syncthreads();
     if (t == 0) {
         // round 0 of the level reads its single centre (point 0, tf_sampling_g.cu:114-116) like any other round
@@ -202,7 +246,20 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
         const int buf = round & 1;
         const uint32_t(*cs)[MP_SLOT_W] = slots[buf ^ 1];  // centres accepted last round
         // ---- 1. lower td against the A new centres, two at a time (min is exact in any order) ----
-        if constexpr (CH > 0) {
+        if constexpr (SORTED) {
+            const float wmaxf = __uint_as_float(wmax_prev);
+            for (int i = 0; i < A; ++i) {
+                const float4 a = *reinterpret_cast<const float4 *>(cs[(uint32_t)(posw >> (8 * i)) & 0xffu]);
+                // exact lower bound of sqdist(point - a) over the warp's box (same operation sequence as sqdist)
+                const float gx = fmaxf(0.f, fmaxf(blx - a.x, a.x - bhx));
+                const float gy = fmaxf(0.f, fmaxf(bly - a.y, a.y - bhy));
+                const float gz = fmaxf(0.f, fmaxf(blz - a.z, a.z - bhz));
+                if (sqdist(gx, gy, gz) < wmaxf) {  // warp uniform
+#pragma unroll
+                    for (int p = 0; p < PTS; ++p) td[p] = fminf(sqdist(x[p] - a.x, y[p] - a.y, z[p] - a.z), td[p]);
+                }
+            }
+        } else if constexpr (CH > 0) {
 #pragma unroll
             for (int c0 = 0; c0 < PTS; c0 += CH) {
 #pragma unroll
@@ -255,6 +312,7 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
         const bool have = m1 >= 0.f;  // false: only padding here
         const uint32_t hi = have ? __float_as_uint(m1) : 0u;
         const uint32_t wm = __reduce_max_sync(0xffffffffu, hi);  // warp maximum (in flight during the scan below)
+        wmax_prev = wm;
         uint32_t eqm = 0u;
         float m2a = -1.f, m2b = -1.f;
 #pragma unroll
@@ -266,7 +324,20 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
         }
         float m2 = fmaxf(m2a, m2b);
         if (eqm & (eqm - 1u)) m2 = m1;  // two points share the maximum
-        const int bp = __ffs(eqm) - 1;  // first in the reference's tie order
+        int bp = __ffs(eqm) - 1;  // first in the reference's tie order (registers ascend in it unless SORTED)
+        if constexpr (SORTED) {
+            if (eqm & (eqm - 1u)) {  // rare (duplicate points): the reference's order is on the ORIGINAL index
+                uint32_t best = 0u;
+                for (uint32_t rest = eqm; rest; rest &= rest - 1u) {
+                    const int p = __ffs(rest) - 1;
+                    const uint32_t w_ = mp_tie_word(sorig[p * T + t]);
+                    if (w_ >= best) {
+                        best = w_;
+                        bp = p;
+                    }
+                }
+            }
+        }
         const uint32_t h2 = m2 >= 0.f ? __float_as_uint(m2) : 0u;
         const bool top = have && hi == wm;
         const unsigned eq = __ballot_sync(0xffffffffu, top);
@@ -274,7 +345,7 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
         int L = __ffs(eq) - 1;
         if (eq & (eq - 1u)) {  // several lanes hold the warp maximum (duplicate points): rare, warp-uniform
             ws = wm;
-            const uint32_t mylo = mp_tie_word(kof(u, bp));
+            const uint32_t mylo = mp_tie_word(orig_of(lane, bp));
             const uint32_t wl = __reduce_max_sync(0xffffffffu, top ? mylo : 0u);
             L = __ffs(__ballot_sync(0xffffffffu, top && mylo == wl)) - 1;
         }
@@ -289,7 +360,7 @@ __device__ __forceinline__ void fps_multi_level(int n, int m, Load load, int *__
                     mx = __float_as_uint(sx[wli]);
                     my = __float_as_uint(sy[wli]);
                     mz = __float_as_uint(sz[wli]);
-                    mlo = mp_tie_word(kof(grp + (uint32_t)G * wl_, wbp));
+                    mlo = mp_tie_word(orig_of(wl_, wbp));
                     mhi = wm;
                 }
                 const uint32_t so = (uint32_t)buf * (G * MP_SLOT_W * 4), bo = (uint32_t)buf * 8;
@@ -396,6 +467,30 @@ __global__ void __launch_bounds__(W * 32, 1)
     if (C > 1) mp_cluster_sync();  // no CTA may exit while peers can still push into it
 }
 
+// One level over a cloud that comes with its spatial index (SORTED mode of fps_multi_level).
+struct SortedLoad {
+    const float4 *rec;  // the scene's Hilbert-sorted records {x, y, z, original index | -1 = padding}
+    const float *data;  // the scene's points in original order (the first centre is original point 0)
+    __device__ __forceinline__ float4 operator()(uint32_t s) const { return __ldg(&rec[s]); }
+    __device__ __forceinline__ float3 first() const { return make_float3(data[0], data[1], data[2]); }
+};
+
+template <int C, int W, int PTS>
+__global__ void __launch_bounds__(W * 32, 1)
+    fps_multi_sorted_kernel(int n, int npad, int m, const float *__restrict__ inp, const float4 *__restrict__ sorted,
+                            int *__restrict__ out, float *__restrict__ new_xyz) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ __align__(16) MpShared<C * W, W> sh;
+    const int scene = blockIdx.x / C;
+    mp_setup<C, W>(sh);
+    int round = 0;
+    SortedLoad load{sorted + (size_t)scene * npad, inp + (size_t)scene * n * 3};
+    fps_multi_level<C, W, PTS, 0, true>(npad, m, load, out + (size_t)scene * m,
+                                        new_xyz ? new_xyz + (size_t)scene * m * 3 : nullptr, nullptr,
+                                        reinterpret_cast<float *>(smem_raw), sh, round);
+    if (C > 1) mp_cluster_sync();  // no CTA may exit while peers can still push into it
+}
+
 // The lower levels of a sampling pyramid in ONE launch: level j samples the picks of level j-1, which every CTA of
 // the cluster already holds in shared memory (each accepted centre reaches every CTA through the exchange), so
 // neither the clouds nor the indices go through HBM between levels and the launches + gathers between them
@@ -464,6 +559,13 @@ template <int C, int W, int PTS, int CH = 0>
 int launch_fps_multi(int b, int n, int m, const float *inp, int *out, float *new_xyz, cudaStream_t stream) {
     return launch_cluster(fps_multi_kernel<C, W, PTS, CH>, "fps_multi_kernel", b, C, W * 32, (size_t)3 * W * 32 * PTS * sizeof(float),
                           stream, n, m, inp, out, new_xyz);
+}
+
+template <int C, int W, int PTS>
+int launch_fps_sorted(int b, int n, int npad, int m, const float *inp, const float4 *sorted, int *out, float *new_xyz,
+                      cudaStream_t stream) {
+    return launch_cluster(fps_multi_sorted_kernel<C, W, PTS>, "fps_multi_sorted_kernel", b, C, W * 32,
+                          (size_t)4 * W * 32 * PTS * sizeof(float), stream, n, npad, m, inp, sorted, out, new_xyz);
 }
 
 template <int C, int W, int P0>
@@ -546,6 +648,21 @@ int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *o
     }
 }
 
+
+// FPS over a cloud with its spatial index (hf_cloud_index_build): same picks, warps skip the centres that cannot
+// reach them.  HF_ERR_UNSUPPORTED when no shape holds the cloud: the caller falls back to the unsorted kernel.
+int fps_sorted_dispatch(int b, int n, int m, const float *inp, const void *index, int *out, float *oxyz, cudaStream_t s,
+                        int warps_req) {
+    const int npad = (n + 31) & ~31;
+    const float4 *sorted = reinterpret_cast<const float4 *>(index);
+    if (npad <= 4096) return HF_ERR_UNSUPPORTED;  // small clouds: the exchange, not the update, is the cost
+    if (npad <= 16384) {
+        if (warps_req == 4 || (warps_req == 0 && b <= 15)) return launch_fps_sorted<8, 4, 16>(b, n, npad, m, inp, sorted, out, oxyz, s);
+        return launch_fps_sorted<4, 8, 16>(b, n, npad, m, inp, sorted, out, oxyz, s);
+    }
+    if (npad <= 65536) return launch_fps_sorted<8, 8, 32>(b, n, npad, m, inp, sorted, out, oxyz, s);
+    return HF_ERR_UNSUPPORTED;
+}
 
 // Levels 2.. of a sampling pyramid in one launch (fps_pyramid_kernel).  HF_ERR_UNSUPPORTED when no instantiation
 // holds the shape: the caller falls back to one launch per level.

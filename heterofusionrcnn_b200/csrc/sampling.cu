@@ -25,6 +25,8 @@ int fps_bucket_dispatch(int b, int n, int m, const float *inp, int *out, cudaStr
 int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *oxyz, cudaStream_t s, int cluster_req, int warps_req);
 int fps_pyramid_dispatch(int b, int levels, int n, const int *m, const float *inp, int *const *idx, float *const *xyz,
                          cudaStream_t s);
+int fps_sorted_dispatch(int b, int n, int m, const float *inp, const void *index, int *out, float *oxyz, cudaStream_t s,
+                        int warps_req);
 
 namespace {
 
@@ -431,6 +433,20 @@ extern "C" int hf_farthest_point_sample_xyz(int b, int n, int m, const float *in
     using namespace hf;
     HF_REQUIRE(new_xyz != nullptr, "FarthestPointSample: new_xyz is null");
     return fps_any(b, n, m, inp, temp, out, new_xyz, stream);
+}
+
+extern "C" int hf_farthest_point_sample_indexed(int b, int n, int m, const float *inp, const void *index, int *out,
+                                                float *new_xyz, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(b >= 0 && n >= 1, "FarthestPointSample expects (batch_size,num_points,3) inp shape");
+    HF_REQUIRE(m > 0, "FarthestPointSample expects positive npoint");
+    HF_REQUIRE(inp && out, "FarthestPointSample: null pointer");
+    if (b == 0) return HF_OK;
+    if (index && (reinterpret_cast<uintptr_t>(index) & 15) == 0 && (g_algo == 0 || g_algo == 3)) {
+        const int rc = fps_sorted_dispatch(b, n, m, inp, index, out, new_xyz, (cudaStream_t)stream, g_algo == 3 ? g_bucket_w : 0);
+        if (rc != HF_ERR_UNSUPPORTED) return rc;
+    }
+    return fps_any(b, n, m, inp, nullptr, out, new_xyz, stream);
 }
 
 extern "C" int hf_fps_pyramid(int b, int levels, int n, const int *m, const float *inp, int *const *idx,

@@ -64,10 +64,12 @@ returns:
     return out
 
 
-def farthest_point_sample_with_xyz(npoint, inp):
+def farthest_point_sample_with_xyz(npoint, inp, index=None):
     """farthest_point_sample + gather_point of one set-abstraction level in one launch
     (hf/core/feature_extractors/pointnet_util.py:42-44: `new_xyz = gather_point(xyz, farthest_point_sample(npoint, xyz))`).
 
+    index: optional spatial.CloudIndex of `inp` (the one ball query / three_nn / the crop of the level use anyway): the
+    kernel then skips, warp by warp, the accepted centres that cannot reach the warp's region of the cloud.
     Returns (idx (b,npoint) int32, new_xyz (b,npoint,3) float32); both identical to the two separate ops.
     """
     require(isinstance(npoint, int) and npoint > 0, "FarthestPointSample expects positive npoint")
@@ -76,6 +78,13 @@ def farthest_point_sample_with_xyz(npoint, inp):
     b, n = inp.shape[0], inp.shape[1]
     out = torch.empty((b, npoint), dtype=torch.int32, device=inp.device)
     new_xyz = torch.empty((b, npoint, 3), dtype=torch.float32, device=inp.device)
+    ix = index.ptr_for(inp) if index is not None else None
+    if ix is not None and n <= _ON_CHIP_POINTS:
+        with torch.cuda.device(inp.device):
+            rc = _lib.load().hf_farthest_point_sample_indexed(b, n, npoint, inp.data_ptr(), ix, out.data_ptr(),
+                                                              new_xyz.data_ptr(), stream_ptr(inp.device))
+        _lib.check(rc, "farthest_point_sample_indexed")
+        return out, new_xyz
     temp = torch.empty((32, n), dtype=torch.float32, device=inp.device) if n > _ON_CHIP_POINTS else None
     with torch.cuda.device(inp.device):
         rc = _lib.load().hf_farthest_point_sample_xyz(

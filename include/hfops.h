@@ -69,6 +69,12 @@ int hf_farthest_point_sample(int b, int n, int m, const float *inp, float *temp,
  * pick when it writes the index, so the separate gatherpointLauncher launch (tf_sampling_g.cu:206) disappears. */
 int hf_farthest_point_sample_xyz(int b, int n, int m, const float *inp, float *temp, int *out, float *new_xyz,
                                  hf_stream_t stream);
+/* The same with the cloud's spatial index (hf_cloud_index_build over inp; NULL = none): the kernel reads the cloud in
+ * curve order, a warp holds a compact region of it and skips every accepted centre whose exact lower-bound distance
+ * to that region cannot lower any of its running distances.  Indices and points are identical to
+ * hf_farthest_point_sample_xyz (new_xyz may be NULL); clouds of 4097..65536 points, others take the plain kernel. */
+int hf_farthest_point_sample_indexed(int b, int n, int m, const float *inp, const void *index, int *out, float *new_xyz,
+                                     hf_stream_t stream);
 /* `levels` (1..HF_FPS_PYRAMID_MAX_LEVELS) consecutive SA sampling levels in ONE launch: level j samples m[j] points
  * from the picks of level j-1 (level 0 from inp (b,n,3)), exactly like calling hf_farthest_point_sample_xyz level by
  * level (pointnet_util.py:42-44 per set-abstraction module).  m: host array of `levels` ints; idx / new_xyz: HOST

@@ -658,6 +658,37 @@ def test_chain_on_streams_equals_chain_in_program_order(cuda):
             assert ka == kb and torch.equal(ta, tb), ka
 
 
+@pytest.mark.parametrize("points,batch", [(8192, 3), (16384, 2), (20000, 2)])
+def test_chain_fused_entries_equal_the_reference_op_sequence(cuda, points, batch):
+    """The chain as bench.py issues it (fused sampling spine, group_point pairs, FPS over the input's index) against the
+    same chain issued op by op like the reference's Python (farthest_point_sample + gather_point per level, two
+    group_point calls per level, plain FPS): every output identical."""
+    from heterofusionrcnn_b200 import chain
+
+    cfg = chain.ChainConfig().scaled(points)
+    cfg.crop_boxes, cfg.crop_resize, cfg.crop_channels, cfg.nms_boxes = 32, 128, 32, 1200
+    dev = chain.to_device(chain.make_host_inputs(cfg, batch=batch, seed=9), cuda)
+    plain = chain.ChainConfig(**{**cfg.__dict__})
+    plain.fused_sampling, plain.fused_grouping, plain.sorted_fps = False, False, False
+    fused = chain.ChainConfig(**{**cfg.__dict__})
+    fused.sorted_fps = True
+    a = chain.run_chain(dev, plain, overlap=False)
+    for overlap in (False, True):
+        b = chain.run_chain(dev, fused, overlap=overlap)
+        torch.cuda.synchronize()
+        for l in range(4):
+            assert torch.equal(a["fps_idx"][l], b["fps_idx"][l]), l
+            assert torch.equal(a["xyz_levels"][l + 1], b["xyz_levels"][l + 1]), l
+            for x, y in zip(a["sa%d" % (l + 1)], b["sa%d" % (l + 1)]):
+                assert torch.equal(x, y), l
+            for x, y in zip(a["fp%d" % (l + 1)], b["fp%d" % (l + 1)]):
+                assert torch.equal(x, y), l
+        for x, y in zip(a["crop"], b["crop"]):
+            assert torch.equal(x, y)
+        assert torch.equal(a["nms_keep"], b["nms_keep"]) and torch.equal(a["nms_num"], b["nms_num"])
+    assert chain.chain_launches(plain) - chain.chain_launches(fused) == 6 + 4
+
+
 # ---------------------------------------------------------------- three_nn fused with the FP weights
 @pytest.mark.parametrize("b,n,m,indexed", [(2, 16384, 4096, True), (2, 16384, 4096, False), (3, 1024, 256, False),
                                            (2, 300, 2, False), (1, 64, 3, False)])

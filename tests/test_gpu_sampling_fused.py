@@ -88,6 +88,44 @@ def test_fps_shared_memory_shape(cuda, oracle, b, n, m, dup):
     assert np.array_equal(N(pts), oracle.gather_point(xyz, want))
 
 
+@pytest.mark.parametrize("b,n,m,dup,warps", [(2, 16384, 1024, 4000, 0), (16, 16384, 200, 0, 0), (3, 5000, 300, 100, 0),
+                                             (2, 4097, 200, 0, 0), (2, 16000, 500, 0, 4), (2, 16384, 300, 2000, 8),
+                                             (2, 40000, 300, 3000, 0), (1, 65536, 256, 8000, 0), (2, 3000, 64, 0, 0),
+                                             (1, 33000, 2000, 0, 0)])
+def test_fps_over_a_spatial_index(cuda, oracle, b, n, m, dup, warps):
+    """index= : the cloud is read in curve order and warps skip the centres that cannot reach their region.  Same picks
+    (the tie-break runs on the original indices): against the oracle, duplicate-padded clouds included, every shape
+    (8 x 4 and 4 x 8 warps at <= 16384 points, 8 x 8 beyond, clouds indexed in parts, the fallback below 4097 points)."""
+    from heterofusionrcnn_b200 import spatial
+
+    xyz, _ = synthetic.make_scans(501 + n + m, b, n, duplicate_pad=dup)
+    x = T(xyz, cuda)
+    ix = spatial.build_cloud_index(x)
+    want = oracle.farthest_point_sample(m, xyz)
+    lib = _lib.load()
+    if warps:
+        lib.hf_fps_set_variant(3, warps, 0)
+    try:
+        idx, pts = farthest_point_sample_with_xyz(m, x, index=ix)
+    finally:
+        lib.hf_fps_set_variant(0, 0, 0)
+    assert np.array_equal(N(idx), want)
+    assert np.array_equal(N(pts), oracle.gather_point(xyz, want))
+
+
+@pytest.mark.parametrize("b,n,m", [(16, 16384, 4096), (4, 65536, 16384), (15, 16384, 4096)])
+def test_fps_over_a_spatial_index_full_size(cuda, b, n, m):
+    """BASELINE config 2 / config 5 sizes: identical to the kernel without the index (itself pinned on the reference
+    kernel at these sizes, test_gpu_bench_config.py)."""
+    from heterofusionrcnn_b200 import spatial
+
+    xyz, _ = synthetic.make_scans(79, b, n, duplicate_pad=n // 8)
+    x = T(xyz, cuda)
+    i0, p0 = farthest_point_sample_with_xyz(m, x)
+    i1, p1 = farthest_point_sample_with_xyz(m, x, index=spatial.build_cloud_index(x))
+    assert torch.equal(i0, i1) and torch.equal(p0, p1)
+
+
 def _level_by_level(x, ms):
     idxs, pts = [], []
     for m in ms:
