@@ -499,4 +499,5 @@ def chain_launches(cfg):
     indexed = [use_ix[l] or (l > 0 and use_ix[l - 1]) for l in range(4)] + [use_ix[3]]
     sampling = 2 if cfg.fused_sampling else 8  # fps+xyz of level 1 and the pyramid of levels 2-4 / fps + gather per level
     grouping = 4 * (2 if cfg.fused_grouping else 3)  # ball query + group_point (pair) per level
-    return sampling + grouping + 4 * 2 + sum(indexed) + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)
+    second_level = sum(1 for l in range(5) if indexed[l] and n_lv[l] > 16384)  # cloud_super_kernel of a large cloud
+    return sampling + grouping + 4 * 2 + sum(indexed) + second_level + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)

@@ -45,12 +45,13 @@ __global__ void __launch_bounds__(kCropThreads)
                 int channel, int ichannel, float *__restrict__ crop_pts, float *__restrict__ crop_fts,
                 float *__restrict__ crop_int, uint8_t *__restrict__ crop_mask, int *__restrict__ crop_ind,
                 uint8_t *__restrict__ non_empty, const float4 *__restrict__ ix_sorted, const float4 *__restrict__ ix_boxes,
-                int npad) {
+                int npad, const float4 *__restrict__ ix_super, int nsuper) {
     extern __shared__ int smem_i[];
     int *sel = smem_i;                // [resize] final source index per slot
     int *wlist = smem_i + resize;     // [kCropWarps][resize] per-warp ordered hits
     __shared__ int wcount[kCropWarps];
     __shared__ int hcount;
+    __shared__ int slist[64], scount;  // super-boxes (groups of 32 buckets) the RoI's bounding box touches
 
     const int b = blockIdx.x;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -90,8 +91,23 @@ __global__ void __launch_bounds__(kCropThreads)
         const int nb = npad >> 5;
         const float4 *srt = ix_sorted + (size_t)bch * npad;
         const float4 *bxs = ix_boxes + (size_t)bch * nb * 2;
+        // large clouds carry a second box level (spatial.cu:cloud_super_kernel): only the groups of 32 buckets whose
+        // super-box the RoI touches are looked at, instead of every bucket box of the scan (2048 at 65536 points)
+        int ngroups = (nb + 31) >> 5;
+        const bool two_level = ix_super != nullptr && nsuper <= 64;
+        if (two_level) {
+            if (t == 0) scount = 0;
+            __syncthreads();
+            if (t < nsuper) {
+                const float4 slo = __ldg(&ix_super[((size_t)bch * nsuper + t) * 2]), shi = __ldg(&ix_super[((size_t)bch * nsuper + t) * 2 + 1]);
+                if (slo.x <= hix && shi.x >= lox && slo.y <= hiy && shi.y >= loy && slo.z <= hiz && shi.z >= loz)
+                    slist[atomicAdd(&scount, 1)] = t;
+            }
+        }
         __syncthreads();
-        for (int g0 = warp * 32; g0 < nb; g0 += kCropWarps * 32) {
+        if (two_level) ngroups = scount;
+        for (int gi = warp; gi < ngroups; gi += kCropWarps) {
+            const int g0 = (two_level ? slist[gi] : gi) * 32;
             const int cb = g0 + lane;
             bool touch = false;
             if (cb < nb) {
@@ -274,12 +290,13 @@ template <bool VEC4, bool INDEXED>
 int launch_crop(size_t smem, cudaStream_t s, const float *pts, const float *fts, const float *intensities, const uint8_t *mask,
                 const float *boxes, const int *box_ind, int num_boxes, int npts, int resize, int channel,
                 int intensity_channel, float *crop_pts, float *crop_fts, float *crop_intensities, uint8_t *crop_mask,
-                int *crop_ind, uint8_t *non_empty_box, const float4 *ix_sorted, const float4 *ix_boxes, int npad) {
+                int *crop_ind, uint8_t *non_empty_box, const float4 *ix_sorted, const float4 *ix_boxes, int npad,
+                const float4 *ix_super, int nsuper) {
     auto kern = crop_kernel<VEC4, INDEXED>;
     if (smem > 40 * 1024) HF_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<num_boxes, kCropThreads, smem, s>>>(pts, fts, intensities, mask, boxes, box_ind, npts, resize, channel,
                                                intensity_channel, crop_pts, crop_fts, crop_intensities, crop_mask, crop_ind,
-                                               non_empty_box, ix_sorted, ix_boxes, npad);
+                                               non_empty_box, ix_sorted, ix_boxes, npad, ix_super, nsuper);
     HF_LAUNCH_OK("crop_kernel");
     return HF_OK;
 }
@@ -310,14 +327,17 @@ extern "C" int hf_pc_crop_and_sample_indexed(const float *pts, const float *fts,
     const bool vec = (channel % 4 == 0) && ((reinterpret_cast<uintptr_t>(fts) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(crop_fts) & 15) == 0);
     // cloud index layout (spatial.cu:carve_index): [sorted: batch x npad float4][boxes: batch x npad/32 x 2 float4]
+    // [super: batch x nsuper x 2 float4, clouds above 16384 points only]
     const bool indexed = pts_index && (reinterpret_cast<uintptr_t>(pts_index) & 15) == 0 && hf_cloud_index_bytes(batch, npts) != 0;
     const int npad = (npts + 31) & ~31;
     const float4 *ix_sorted = static_cast<const float4 *>(pts_index);
     const float4 *ix_boxes = indexed ? ix_sorted + (size_t)batch * npad : nullptr;
+    const int nsuper = npad > 16384 ? (npad / 32 + 31) / 32 : 0;
+    const float4 *ix_super = (indexed && nsuper) ? ix_boxes + (size_t)batch * (npad / 32) * 2 : nullptr;
     cudaStream_t s = (cudaStream_t)stream;
 #define HF_CROP_ARGS                                                                                                     \
     smem, s, pts, fts, intensities, mask, boxes, box_ind, num_boxes, npts, resize, channel, intensity_channel, crop_pts, \
-        crop_fts, crop_intensities, crop_mask, crop_ind, non_empty_box, ix_sorted, ix_boxes, npad
+        crop_fts, crop_intensities, crop_mask, crop_ind, non_empty_box, ix_sorted, ix_boxes, npad, ix_super, nsuper
     if (vec) return indexed ? launch_crop<true, true>(HF_CROP_ARGS) : launch_crop<true, false>(HF_CROP_ARGS);
     return indexed ? launch_crop<false, true>(HF_CROP_ARGS) : launch_crop<false, false>(HF_CROP_ARGS);
 #undef HF_CROP_ARGS

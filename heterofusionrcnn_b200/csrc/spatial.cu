@@ -82,6 +82,8 @@ struct CloudDesc {
     const float *xyz;  // (b, n, 3)
     float4 *sorted;    // (b, npad) {x, y, z, original index as int bits}; padding = {NaN, NaN, NaN, -1}
     float4 *boxes;     // (b, npad/32, 2) {lo.xyz, smallest original index in the bucket}, {hi.xyz, -}
+    float4 *super;     // (b, nsuper, 2) boxes of 32 consecutive buckets, clouds above kMaxIndexed points only
+    int nsuper;
     int n, npad, per_thread;  // points, rounded up to 32, sort elements per thread = ceil(part_n / 1024)
     int parts, part_n;        // the cloud is sorted in `parts` runs of part_n (a multiple of 32) consecutive points
 };
@@ -726,7 +728,9 @@ int launch_knn(bool indexed, int b, int n, int m, int k, const float *xyz1, cons
 thread_local int g_spatial_mode = 0;  // 0 = auto, 1 = never (every-pair kernels), 2 = whenever a shape exists
 
 inline int round32(int v) { return (v + 31) & ~31; }
-inline size_t cloud_bytes(int b, int n) { return (size_t)b * round32(n) * 17; }  // 16 B/point + 32 B/bucket
+// 16 B/point + 32 B/bucket (+ 32 B per 32 buckets for clouds above kMaxIndexed points: the second box level)
+inline int super_count(int n) { return round32(n) > kMaxIndexed ? (round32(n) / 32 + 31) / 32 : 0; }
+inline size_t cloud_bytes(int b, int n) { return (size_t)b * ((size_t)round32(n) * 17 + (size_t)super_count(n) * 32); }
 
 // Is the pruned path used for a call whose query cloud has nq points and candidate cloud nc?
 bool spatial_applies(int nq, int nc) {
@@ -758,7 +762,38 @@ CloudDesc carve_index(int b, int n, const float *xyz, void *mem) {
     d.per_thread = (d.part_n + kIdxThreads - 1) / kIdxThreads;
     d.sorted = reinterpret_cast<float4 *>(w);
     d.boxes = reinterpret_cast<float4 *>(w + (size_t)b * d.npad * 16);
+    d.nsuper = super_count(n);
+    d.super = d.nsuper ? reinterpret_cast<float4 *>(w + (size_t)b * d.npad * 17) : nullptr;
     return d;
+}
+
+// Second box level of a large cloud: super-box j = bounding box of buckets 32j .. 32j+31 (one warp each).  The RoI crop
+// tests 64 of these instead of the 2048 bucket boxes of a 65536-point scan before it looks at buckets at all.
+__global__ void __launch_bounds__(256) cloud_super_kernel(int nb, int nsuper, const float4 *__restrict__ boxes,
+                                                          float4 *__restrict__ super) {
+    const int lane = threadIdx.x & 31;
+    const int sb = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int scene = blockIdx.y;
+    if (sb >= nsuper) return;
+    const int bk = sb * 32 + lane;
+    float lx = INFINITY, ly = INFINITY, lz = INFINITY, hx = -INFINITY, hy = -INFINITY, hz = -INFINITY;
+    if (bk < nb) {
+        const float4 lo = boxes[((size_t)scene * nb + bk) * 2], hi = boxes[((size_t)scene * nb + bk) * 2 + 1];
+        if (__float_as_int(lo.w) != INT_MAX) {  // the bucket holds a real point
+            lx = lo.x; ly = lo.y; lz = lo.z;
+            hx = hi.x; hy = hi.y; hz = hi.z;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lx = fminf(lx, __shfl_xor_sync(0xffffffffu, lx, o)); ly = fminf(ly, __shfl_xor_sync(0xffffffffu, ly, o));
+        lz = fminf(lz, __shfl_xor_sync(0xffffffffu, lz, o)); hx = fmaxf(hx, __shfl_xor_sync(0xffffffffu, hx, o));
+        hy = fmaxf(hy, __shfl_xor_sync(0xffffffffu, hy, o)); hz = fmaxf(hz, __shfl_xor_sync(0xffffffffu, hz, o));
+    }
+    if (lane == 0) {
+        super[((size_t)scene * nsuper + sb) * 2] = make_float4(lx, ly, lz, 0.f);
+        super[((size_t)scene * nsuper + sb) * 2 + 1] = make_float4(hx, hy, hz, 0.f);
+    }
 }
 
 // Sort one cloud (or the two clouds of a call, in one launch) into their index memory.
@@ -767,6 +802,11 @@ int launch_index(int b, const CloudDesc &a, const CloudDesc *second, cudaStream_
     const int gparts = second && second->parts > a.parts ? second->parts : a.parts;
     cloud_index_kernel<<<dim3(b * gparts, second ? 2 : 1), kIdxThreads, kIdxSmem, s>>>(a, second ? *second : a, gparts);
     HF_LAUNCH_OK("cloud_index_kernel");
+    for (const CloudDesc *d : {&a, second}) {
+        if (!d || !d->nsuper) continue;
+        cloud_super_kernel<<<dim3((d->nsuper + 7) / 8, b), 256, 0, s>>>(d->npad / 32, d->nsuper, d->boxes, d->super);
+        HF_LAUNCH_OK("cloud_super_kernel");
+    }
     return HF_OK;
 }
 

@@ -456,10 +456,12 @@ def test_crop_matches_oracle(cuda, oracle, C, R):
 
 
 @pytest.mark.parametrize("C,R,P,nbox", [(288, 512, 16384, 40), (7, 64, 16384, 40), (4, 16, 16384, 40), (8, 128, 5000, 25),
-                                        (4, 32, 40000, 12), (12, 8, 70000, 6)])
+                                        (4, 32, 40000, 12), (12, 8, 70000, 6), (8, 256, 65536, 48), (4, 64, 16416, 20),
+                                        (4, 128, 33000, 30)])
 def test_crop_with_cloud_index_matches_oracle(cuda, oracle, C, R, P, nbox):
     """The index only prunes the point-in-box scan: identical outputs, incl. boxes with more hits than the hit
-    list holds (R = 16 / 8: falls back to the ordered scan), clouds indexed in parts (40000) and clouds too
+    list holds (R = 16 / 8: falls back to the ordered scan), clouds indexed in parts with the second box level
+    (16416 .. 65536 points: only the groups of 32 buckets whose super-box the RoI touches are tested) and clouds too
     large to index (70000: plain path)."""
     from heterofusionrcnn_b200 import spatial
 
