@@ -209,6 +209,46 @@ def count_pair_evals(torch, hf, chain, resident, cfg):
     return found
 
 
+def back_to_back(torch, chain, resident, cfg, reps=20):
+    """The HBM-bound gathers of the chain re-issued `reps` times back to back between ONE pair of CUDA events (L2 flushed
+    first): the per-launch event pair of the `alone` leg costs ~5 us on launches of 15-60 us.  Same tensors, same calls
+    as chain.run_chain.  -> {launch key: ms per launch}"""
+    from heterofusionrcnn_b200.grouping.tf_grouping import group_point_pair
+    from heterofusionrcnn_b200.interpolate.tf_interpolate import three_interpolate
+
+    res = chain.run_chain(resident, cfg, None, overlap=False)
+    torch.cuda.synchronize()
+    dev = resident["xyz"].device
+    flush = torch.empty(512 * 1024 * 1024 // 4, device=dev)
+    feats = [resident["intensity"]] + list(resident["sa_feats"][1:])
+    calls = {}
+    for l in range(4):
+        gidx = res["sa%d" % (l + 1)][0]
+        if cfg.fused_grouping:
+            calls["group_point_pair/level=%d/c=%d" % (l + 1, feats[l].shape[2])] = (
+                lambda l=l, gidx=gidx: group_point_pair(res["xyz_levels"][l], feats[l], gidx))
+    for j in range(4):
+        lvl = 3 - j
+        pts, nidx, w = resident["fp_feats"][j], res["fp%d" % (lvl + 1)][1], res["fp_weights"][lvl]
+        calls["three_interpolate/level=%d/c=%d" % (lvl + 1, pts.shape[2])] = (
+            lambda pts=pts, nidx=nidx, w=w: three_interpolate(pts, nidx, w))
+    out = {}
+    for key, fn in calls.items():
+        for _ in range(3):
+            fn()
+        flush.zero_()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        out[key] = e0.elapsed_time(e1) / reps
+    del flush
+    return out
+
+
 class EventProbe:
     """Brackets every op of chain.run_chain with CUDA events on the launching (current) stream."""
 
@@ -615,6 +655,7 @@ def run_b200(args):
     # distance evaluations the pruned ball query / three_nn launches EXECUTE (the kernels count them when a device
     # counter is set): one more serial pass, outside every timed region
     pair_evals = count_pair_evals(torch, hf, chain, resident, cfg)
+    b2b_ms = back_to_back(torch, chain, resident, cfg)
 
     # ---- end to end: host buffers in, host-consumed results out, through the public op API ----
     e2e = None
@@ -785,6 +826,9 @@ def run_b200(args):
         o["frac_alone"] = (a / o["peak"]) if a and o["peak"] else None
         # share of the serial (one-stream) step: with overlap the in-region durations add up to more than the step
         o["share_of_step"] = (o["ms_alone"] or o["ms"]) * o["per_step"] / serial_step_ms
+        o["ms_back_to_back"] = b2b_ms.get(o["launch"])
+        if o["ms_back_to_back"] and o["bound"] == "hbm":
+            o["frac_back_to_back"] = o["bytes"] / (o["ms_back_to_back"] / 1e3) / 1e9 / hbm_peak
         # pruned launches: `frac` above divides the EVERY-PAIR flop count of SURVEY 8d by the pruned kernel's time (an
         # equivalent rate: it can exceed 1); frac_executed divides the evaluations the kernel really ran
         ex = pair_evals.get(o["launch"], 0)
@@ -832,7 +876,8 @@ def run_b200(args):
                           "peak": hbm_peak, "unit": "GB/s", "frac": step_bytes / (ms / args.steps) / 1e6 / hbm_peak},
         "roofline_ops": [{k: o.get(k) for k in ("launch", "bound", "ms", "ms_alone", "per_step", "achieved", "unit", "frac",
                                                 "frac_alone", "share_of_step", "pair_evals_executed", "pair_evals_every_pair",
-                                                "frac_equivalent", "frac_alone_equivalent")
+                                                "frac_equivalent", "frac_alone_equivalent", "ms_back_to_back",
+                                                "frac_back_to_back")
                           if o.get(k) is not None or k in ("frac", "frac_alone", "achieved", "unit")} for o in ops],
         "serial_ms_per_step": serial_step_ms,
         "fp32_peak": fp32,
