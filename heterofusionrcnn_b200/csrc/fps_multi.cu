@@ -658,6 +658,9 @@ int fps_sorted_dispatch(int b, int n, int m, const float *inp, const void *index
     if (npad <= 4096) return HF_ERR_UNSUPPORTED;  // small clouds: the exchange, not the update, is the cost
     if (npad <= 16384) {
         if (warps_req == 4 || (warps_req == 0 && b <= 15)) return launch_fps_sorted<8, 4, 16>(b, n, npad, m, inp, sorted, out, oxyz, s);
+        // more than 15 scans: 4 CTAs x 8 warps (1.16 ms for 16 x 16384 -> 4096 against 1.25 without the index).  6 CTAs
+        // x 8 warps x 11 records (warps_req = 6; 22 such clusters are co-resident) measured 1.49 ms: not the default.
+        if (warps_req == 6) return launch_fps_sorted<6, 8, 11>(b, n, npad, m, inp, sorted, out, oxyz, s);
         return launch_fps_sorted<4, 8, 16>(b, n, npad, m, inp, sorted, out, oxyz, s);
     }
     if (npad <= 65536) return launch_fps_sorted<8, 8, 32>(b, n, npad, m, inp, sorted, out, oxyz, s);

@@ -89,7 +89,7 @@ def test_fps_shared_memory_shape(cuda, oracle, b, n, m, dup):
 
 
 @pytest.mark.parametrize("b,n,m,dup,warps", [(2, 16384, 1024, 4000, 0), (16, 16384, 200, 0, 0), (3, 5000, 300, 100, 0),
-                                             (2, 4097, 200, 0, 0), (2, 16000, 500, 0, 4), (2, 16384, 300, 2000, 8),
+                                             (2, 4097, 200, 0, 0), (2, 16000, 500, 0, 4), (2, 16384, 300, 2000, 8), (2, 16384, 400, 3000, 6), (3, 9000, 256, 0, 6),
                                              (2, 40000, 300, 3000, 0), (1, 65536, 256, 8000, 0), (2, 3000, 64, 0, 0),
                                              (1, 33000, 2000, 0, 0)])
 def test_fps_over_a_spatial_index(cuda, oracle, b, n, m, dup, warps):

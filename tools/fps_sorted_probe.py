@@ -30,6 +30,16 @@ def main():
             t1 = timeit(lambda: farthest_point_sample_with_xyz(m, xb, index=ix), reps=3)
             print("n=%5d m=%5d b=%2d  plain %8.3f ms   with index %8.3f ms (+ index build %6.3f ms)  same=%s" % (
                 n, m, b, t0, t1, t_ix, bool(torch.equal(ref, out))))
+            if n <= 16384:
+                lib = hf.load()
+                for w, name in ((4, "8 CTAs x 4 warps x 16"), (8, "4 CTAs x 8 warps x 16"), (6, "6 CTAs x 8 warps x 11")):
+                    lib.hf_fps_set_variant(3, w, 0)
+                    try:
+                        o2 = farthest_point_sample_with_xyz(m, xb, index=ix)[0]
+                        t2 = timeit(lambda: farthest_point_sample_with_xyz(m, xb, index=ix), reps=3)
+                    finally:
+                        lib.hf_fps_set_variant(0, 0, 0)
+                    print("        with index, %-24s %8.3f ms  same=%s" % (name, t2, bool(torch.equal(ref, o2))))
             sys.stdout.flush()
 
 
