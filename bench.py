@@ -827,6 +827,8 @@ def run_b200(args):
         # share of the serial (one-stream) step: with overlap the in-region durations add up to more than the step
         o["share_of_step"] = (o["ms_alone"] or o["ms"]) * o["per_step"] / serial_step_ms
         o["ms_back_to_back"] = b2b_ms.get(o["launch"])
+        if o["ms_back_to_back"] and o["ms_alone"] and o["ms_back_to_back"] >= o["ms_alone"]:
+            o["ms_back_to_back"] = None  # launches of ~15 us: the host cannot issue them back to back, nothing to report
         if o["ms_back_to_back"] and o["bound"] == "hbm":
             o["frac_back_to_back"] = o["bytes"] / (o["ms_back_to_back"] / 1e3) / 1e9 / hbm_peak
         # pruned launches: `frac` above divides the EVERY-PAIR flop count of SURVEY 8d by the pruned kernel's time (an
