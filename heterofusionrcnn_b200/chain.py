@@ -46,6 +46,11 @@ class ChainConfig:
     # sampling spine: level 1 = one launch that writes the indices AND the picked points; levels 2-4 = one launch
     # (fps pyramid).  False = the reference's op sequence, farthest_point_sample + gather_point per level (8 launches).
     fused_sampling: bool = True
+    # first level (0-based) whose sampling goes into the pyramid launch together with every deeper level.  1 = levels 2-4
+    # in one launch (default).  2 = levels 3-4: level 2 gets its own launch, its points exist 0.06 ms earlier and its ball
+    # query / three_nn (the longest branch behind the spine) start sooner: 1.696 vs 1.714 ms for the SA/FP chain alone,
+    # but 2.026 vs 1.997 ms for the whole step (tools/ablation_probe.py)
+    pyramid_from: int = 1
     # grouping: the coordinates and the features of a level's neighbourhoods in one launch (group_point_pair);
     # False = two group_point launches per level (pointnet_util.py:49,56)
     fused_grouping: bool = True
@@ -307,7 +312,7 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                     new_xyz = gather_point(xyz[l], idx)
                 fps_idx.append(idx)
                 xyz.append(new_xyz)
-            elif l == 0 or len(n_lv) - 1 - l > PYRAMID_MAX_LEVELS:
+            elif l < cfg.pyramid_from or len(n_lv) - 1 - l > PYRAMID_MAX_LEVELS:
                 ix = index[0] if (l == 0 and sorted_fps) else None
                 if ix is not None:
                     after(crit, index_ready[0])
@@ -497,7 +502,8 @@ def chain_launches(cfg):
     n_lv = [cfg.points] + list(cfg.npoint)
     use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
     indexed = [use_ix[l] or (l > 0 and use_ix[l - 1]) for l in range(4)] + [use_ix[3]]
-    sampling = 2 if cfg.fused_sampling else 8  # fps+xyz of level 1 and the pyramid of levels 2-4 / fps + gather per level
+    # fps+xyz per level below pyramid_from and one pyramid launch for the rest / fps + gather per level
+    sampling = (min(max(cfg.pyramid_from, 1), 4) + (1 if cfg.pyramid_from < 4 else 0)) if cfg.fused_sampling else 8
     grouping = 4 * (2 if cfg.fused_grouping else 3)  # ball query + group_point (pair) per level
     second_level = sum(1 for l in range(5) if indexed[l] and n_lv[l] > 16384)  # cloud_super_kernel of a large cloud
     return sampling + grouping + 4 * 2 + sum(indexed) + second_level + (1 if cfg.with_crop else 0) + (5 if cfg.with_nms else 0)
