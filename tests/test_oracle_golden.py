@@ -290,6 +290,20 @@ def test_oracle_knn_point_is_pinned_on_the_reference_formula(oracle):
     assert np.mean(idx == ri) > 0.99 and np.all(np.abs(val - rv) <= tol)
 
 
+def test_oracle_box3d_iou_matches_the_reference_module(oracle):
+    """tests/golden/box3d_iou_ref.npz = hf/core/compute_iou.py:box3d_iou_tf itself (the module imported unmodified, with
+    a numpy shim for its 9 TensorFlow calls and the reference's own BEV math compiled for the host behind
+    bev_iou.compute_bev_iou: tests/golden/make_golden_box3d_iou.py).  Pins the BEV conversion, the height overlap, the
+    volumes and the clipped union of the restatement; identical footprints at three height offsets included."""
+    g = np.load(os.path.join(os.path.dirname(GOLD), "box3d_iou_ref.npz"))
+    iou3d, iou2d = oracle.box3d_iou(g["boxes_a"], g["boxes_b"])
+    assert (g["iou_3d"] > 0).sum() > 100
+    assert np.array_equal(iou3d == 0, g["iou_3d"] == 0)
+    assert np.allclose(iou2d, g["iou_2d"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(iou3d, g["iou_3d"], rtol=1e-5, atol=1e-6)
+    assert np.allclose(np.diag(iou3d)[:5], 1.0, atol=1e-5) and iou3d[6, 6] == 0 and 0.3 < iou3d[5, 5] < 0.8
+
+
 def _pc_sample_cases():
     g = np.load(os.path.join(os.path.dirname(GOLD), "pc_sample_ref.npz"))
     names = sorted({k.split(".")[0] for k in g.files}, key=lambda c: int(c[1:]))
