@@ -80,6 +80,22 @@ def test_sb_nms_fn_matches_oracle(cuda, oracle, s, n, thresh, nms_size):
         assert torch.equal(one, got[0]) and int(onum) == int(num[0])
 
 
+def test_sb_nms_fn_matches_the_reference_modules(cuda):
+    """The CUDA path against tests/golden/sb_nms_ref.npz, the output of the reference's own model_util.sb_nms_fn /
+    compute_iou.oriented_nms_tf (tests/golden/make_golden_sb_nms.py)."""
+    import os
+
+    from heterofusionrcnn_b200.model_util import sb_nms_fn
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sb_nms_ref.npz"))
+    for c in sorted({k.split(".")[0] for k in g.files}):
+        boxes, scores = T(g[c + ".boxes"], cuda), T(g[c + ".scores"], cuda)
+        for fixed, tag in ((True, "fixed"), (False, "unique")):
+            idx, num = sb_nms_fn((boxes, scores), float(g[c + ".thresh"]), int(g[c + ".nms_size"]), fixed, None)
+            assert int(num) == int(g[c + ".num_" + tag]), (c, tag)
+            assert np.array_equal(N(idx), g[c + ".idx_" + tag]), (c, tag)
+
+
 def test_box_3d_to_box_8co_feeds_the_crop(cuda, oracle):
     """tf_box_3d_to_box_8co (+ the proposal expansion) against the oracle, and as the crop's box input."""
     from heterofusionrcnn_b200.box_8c_encoder import tf_box_3d_to_box_8co

@@ -304,6 +304,26 @@ def test_oracle_box3d_iou_matches_the_reference_module(oracle):
     assert np.allclose(np.diag(iou3d)[:5], 1.0, atol=1e-5) and iou3d[6, 6] == 0 and 0.3 < iou3d[5, 5] < 0.8
 
 
+def _sb_nms_cases():
+    g = np.load(os.path.join(os.path.dirname(GOLD), "sb_nms_ref.npz"))
+    names = sorted({k.split(".")[0] for k in g.files}, key=lambda c: int(c[1:]))
+    return [{k.split(".", 1)[1]: g[k] for k in g.files if k.startswith(c + ".")} for c in names]
+
+
+def test_oracle_sb_nms_fn_matches_the_reference_modules(oracle):
+    """tests/golden/sb_nms_ref.npz = hf/core/models/model_util.py:sb_nms_fn -> hf/core/compute_iou.py:oriented_nms_tf, the
+    reference's modules imported unmodified (numpy shim for their TF calls, the reference's host-compiled iou_bev + the
+    sweep restatement behind bev_iou.oriented_nms: tests/golden/make_golden_sb_nms.py): the score sort with its tie
+    rule, the slice, tf.unique, the -1 padding and the count, both settings of fixed_num_proposal_nms."""
+    cases = _sb_nms_cases()
+    assert len(cases) == 5
+    for c in cases:
+        for fixed, tag in ((True, "fixed"), (False, "unique")):
+            idx, num = oracle.sb_nms_fn(c["boxes"], c["scores"], float(c["thresh"]), int(c["nms_size"]), fixed)
+            assert num == int(c["num_" + tag])
+            assert np.array_equal(idx, c["idx_" + tag])
+
+
 def _pc_sample_cases():
     g = np.load(os.path.join(os.path.dirname(GOLD), "pc_sample_ref.npz"))
     names = sorted({k.split(".")[0] for k in g.files}, key=lambda c: int(c[1:]))
