@@ -304,6 +304,22 @@ def test_oracle_box3d_iou_matches_the_reference_module(oracle):
     assert np.allclose(np.diag(iou3d)[:5], 1.0, atol=1e-5) and iou3d[6, 6] == 0 and 0.3 < iou3d[5, 5] < 0.8
 
 
+def test_knn_reference_form_is_the_reference_code(oracle):
+    """tests/golden/knn_pointfly_ref.npz = hf/core/pointfly.py:knn_indices_general (module imported unmodified) and the
+    formula lines grouping/tf_grouping.py:82-93 executed as they stand, both with a numpy float32 shim for their TF calls
+    (tests/golden/make_golden_knn_pointfly.py).  The oracle's knn_point_reference_form — the pin of knn_point — is those
+    lines: identical values and indices; and the direct-form oracle passes the pin's check on these clouds."""
+    g = np.load(os.path.join(os.path.dirname(GOLD), "knn_pointfly_ref.npz"))
+    k = int(g["k"])
+    rv, ri, _, _ = oracle.knn_point_reference_form(k, g["points"], g["queries"])
+    assert np.array_equal(rv, g["knn_point_val"]) and np.array_equal(ri, g["knn_point_idx"])
+    assert np.array_equal(rv, g["pointfly_dist"]) and np.array_equal(ri, g["pointfly_ind"][..., 1])
+    b, p = g["queries"].shape[:2]
+    assert np.array_equal(g["pointfly_ind"][..., 0], np.broadcast_to(np.arange(b, dtype=np.int32)[:, None, None], (b, p, k)))
+    val, idx = oracle.knn_point(k, g["points"], g["queries"])
+    assert oracle.check_knn_against_reference_form(k, g["points"], g["queries"], val, idx) > 0.5
+
+
 def _sb_nms_cases():
     g = np.load(os.path.join(os.path.dirname(GOLD), "sb_nms_ref.npz"))
     names = sorted({k.split(".")[0] for k in g.files}, key=lambda c: int(c[1:]))
