@@ -320,6 +320,17 @@ def test_knn_reference_form_is_the_reference_code(oracle):
     assert oracle.check_knn_against_reference_form(k, g["points"], g["queries"], val, idx) > 0.5
 
 
+def test_fp_weights_restatement_is_the_reference_code():
+    """tests/golden/fp_weights_ref.npz = pointnet_util.py:304-307 executed as they stand (numpy float32 shim for tf.maximum /
+    reduce_sum / tile, make_golden_fp_weights.py).  synthetic.fp_weights — what the three_nn_weights kernel is checked
+    against — reproduces them bit for bit, zero distances and sub-clamp distances included."""
+    from heterofusionrcnn_b200 import synthetic
+
+    g = np.load(os.path.join(os.path.dirname(GOLD), "fp_weights_ref.npz"))
+    assert np.array_equal(synthetic.fp_weights(g["dist"]), g["weight"])
+    assert np.allclose(g["weight"].sum(axis=2), 1.0, atol=1e-6)
+
+
 def _sb_nms_cases():
     g = np.load(os.path.join(os.path.dirname(GOLD), "sb_nms_ref.npz"))
     names = sorted({k.split(".")[0] for k in g.files}, key=lambda c: int(c[1:]))
