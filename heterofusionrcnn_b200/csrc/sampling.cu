@@ -26,7 +26,7 @@ int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *o
 int fps_pyramid_dispatch(int b, int levels, int n, const int *m, const float *inp, int *const *idx, float *const *xyz,
                          cudaStream_t s);
 int fps_sorted_dispatch(int b, int n, int m, const float *inp, const void *index, int *out, float *oxyz, cudaStream_t s,
-                        int warps_req);
+                        int warps_req, int mode_req);
 
 namespace {
 
@@ -443,7 +443,8 @@ extern "C" int hf_farthest_point_sample_indexed(int b, int n, int m, const float
     HF_REQUIRE(inp && out, "FarthestPointSample: null pointer");
     if (b == 0) return HF_OK;
     if (index && (reinterpret_cast<uintptr_t>(index) & 15) == 0 && (g_algo == 0 || g_algo == 3)) {
-        const int rc = fps_sorted_dispatch(b, n, m, inp, index, out, new_xyz, (cudaStream_t)stream, g_algo == 3 ? g_bucket_w : 0);
+        const int rc = fps_sorted_dispatch(b, n, m, inp, index, out, new_xyz, (cudaStream_t)stream, g_algo == 3 ? g_bucket_w : 0,
+                                           g_algo == 3 ? g_bucket_j : 0);
         if (rc != HF_ERR_UNSUPPORTED) return rc;
     }
     return fps_any(b, n, m, inp, nullptr, out, new_xyz, stream);

@@ -93,7 +93,8 @@ def test_fps_shared_memory_shape(cuda, oracle, b, n, m, dup):
                                              (2, 40000, 300, 3000, 0), (1, 65536, 256, 8000, 0), (2, 3000, 64, 0, 0),
                                              (1, 33000, 2000, 0, 0)])
 def test_fps_over_a_spatial_index(cuda, oracle, b, n, m, dup, warps):
-    """index= : the cloud is read in curve order and warps skip the centres that cannot reach their region.  Same picks
+    """index= : the cloud is read in curve order and threads (or warps) skip the centres that cannot reach their part
+    of it.  Same picks
     (the tie-break runs on the original indices): against the oracle, duplicate-padded clouds included, every shape
     (8 x 4 and 4 x 8 warps at <= 16384 points, 8 x 8 beyond, clouds indexed in parts, the fallback below 4097 points)."""
     from heterofusionrcnn_b200 import spatial
@@ -103,14 +104,15 @@ def test_fps_over_a_spatial_index(cuda, oracle, b, n, m, dup, warps):
     ix = spatial.build_cloud_index(x)
     want = oracle.farthest_point_sample(m, xyz)
     lib = _lib.load()
-    if warps:
-        lib.hf_fps_set_variant(3, warps, 0)
-    try:
-        idx, pts = farthest_point_sample_with_xyz(m, x, index=ix)
-    finally:
-        lib.hf_fps_set_variant(0, 0, 0)
-    assert np.array_equal(N(idx), want)
-    assert np.array_equal(N(pts), oracle.gather_point(xyz, want))
+    for mode in (0, 1, 2):  # default (= compact threads) / compact warps / compact threads
+        if warps or mode:
+            lib.hf_fps_set_variant(3, warps, mode)
+        try:
+            idx, pts = farthest_point_sample_with_xyz(m, x, index=ix)
+        finally:
+            lib.hf_fps_set_variant(0, 0, 0)
+        assert np.array_equal(N(idx), want), mode
+        assert np.array_equal(N(pts), oracle.gather_point(xyz, want)), mode
 
 
 @pytest.mark.parametrize("b,n,m", [(16, 16384, 4096), (4, 65536, 16384), (15, 16384, 4096)])

@@ -32,14 +32,25 @@ def main():
                 n, m, b, t0, t1, t_ix, bool(torch.equal(ref, out))))
             if n <= 16384:
                 lib = hf.load()
-                for w, name in ((4, "8 CTAs x 4 warps x 16"), (8, "4 CTAs x 8 warps x 16"), (6, "6 CTAs x 8 warps x 11")):
-                    lib.hf_fps_set_variant(3, w, 0)
+                for w, mode, name in ((4, 1, "warps: 8 CTAs x 4 warps x 16"), (8, 1, "warps: 4 CTAs x 8 warps x 16"),
+                                      (4, 2, "threads: 8 CTAs x 4 warps x 16"), (8, 2, "threads: 4 CTAs x 8 warps x 16"),
+                                      (6, 2, "threads: 6 CTAs x 8 warps x 11")):
+                    lib.hf_fps_set_variant(3, w, mode)
                     try:
                         o2 = farthest_point_sample_with_xyz(m, xb, index=ix)[0]
                         t2 = timeit(lambda: farthest_point_sample_with_xyz(m, xb, index=ix), reps=3)
                     finally:
                         lib.hf_fps_set_variant(0, 0, 0)
-                    print("        with index, %-24s %8.3f ms  same=%s" % (name, t2, bool(torch.equal(ref, o2))))
+                    print("        with index, compact %-32s %8.3f ms  same=%s" % (name, t2, bool(torch.equal(ref, o2))))
+            else:
+                lib = hf.load()
+                lib.hf_fps_set_variant(3, 0, 1)
+                try:
+                    o2 = farthest_point_sample_with_xyz(m, xb, index=ix)[0]
+                    t2 = timeit(lambda: farthest_point_sample_with_xyz(m, xb, index=ix), reps=3)
+                finally:
+                    lib.hf_fps_set_variant(0, 0, 0)
+                print("        with index, compact warps (8 x 8 x 32)       %8.3f ms  same=%s" % (t2, bool(torch.equal(ref, o2))))
             sys.stdout.flush()
 
 
