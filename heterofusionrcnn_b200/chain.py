@@ -54,9 +54,10 @@ class ChainConfig:
     # grouping: the coordinates and the features of a level's neighbourhoods in one launch (group_point_pair);
     # False = two group_point launches per level (pointnet_util.py:49,56)
     fused_grouping: bool = True
-    # level-1 FPS over the input's spatial index (warps skip the centres that cannot reach them): None = where it
-    # pays, i.e. clouds above 16384 points (65536: 8.8 -> 6.3 ms per launch; at 16384 points the wait for the index
-    # costs what the skipping saves, profiles/r2_fps_sorted_probe.txt)
+    # level-1 FPS over the input's spatial index (threads skip the centres that cannot reach their bucket of the cloud):
+    # None = whenever the index is built anyway.  16 x 16384 -> 4096: 1.25 -> 1.06 ms per launch (the SA/FP chain alone
+    # 1.72 -> 1.59 ms per step, the whole step unchanged within noise: it is bound by the crop + NMS beside the spine);
+    # 65536 -> 16384: 8.8 -> 5.6 ms (profiles/r2_fps_sorted_probe.txt, r2_fps_shape_in_step.txt)
     sorted_fps: object = None
 
     def scaled(self, points):
@@ -337,7 +338,7 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
     # The input's index needs whole SMs (1024-thread CTAs): it goes out before the crop floods the GPU.
     use_ix = [spatial.applies(n_lv[l + 1], n_lv[l]) and spatial.applies(n_lv[l], n_lv[l + 1]) for l in range(4)]
     index, index_ready = [None] * 5, [None] * 5
-    sorted_fps = use_ix[0] and (cfg.sorted_fps if cfg.sorted_fps is not None else cfg.points > 16384)
+    sorted_fps = use_ix[0] and (cfg.sorted_fps if cfg.sorted_fps is not None else True)
     if overlap and not sorted_fps:
         have_xyz[0] = sample_level(0)
     if use_ix[0]:
