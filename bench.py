@@ -903,7 +903,7 @@ def run_b200(args):
 
 NCU_KERNEL_OF = {  # probe name -> (kernel name fragment, grid) in the committed ncu --set full summary
     "pc_crop_and_sample/c=288": ("crop_kernel", "(8192, 1, 1)"),
-    "fps/level=1": ("fps_multi_kernel", None),
+    "fps/level=1": ("fps_multi", None),
 }
 
 
