@@ -90,6 +90,7 @@ SIGNATURES = {
     "hf_nms_set_spatial_sort": (None, [_c_int]),
     "hf_oriented_nms_last_pair_count": (ctypes.c_longlong, [_c_int, _c_int, _ptr, _ptr]),
     "hf_oriented_nms": (_c_int, [_ptr, _c_int, _c_int, _c_float, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_oriented_nms_topk": (_c_int, [_ptr, _c_int, _c_int, _c_float, _c_int, _ptr, _ptr, _ptr, _size_t, _ptr]),
 }
 
 _lib = None

@@ -35,11 +35,13 @@ def compute_bev_iou(proposals, gt_bboxes):
     return overlap, iou
 
 
-def oriented_nms_batch(boxes, thresh, return_num_kept=False):
+def oriented_nms_batch(boxes, thresh, return_num_kept=False, max_keep=None):
     """oriented_nms over S independent, score-sorted box sets in one call.
 
     boxes: (S, N, 5) -> keep_idx (S, N) int32 [, num_kept (S,) int32].
     The reference runs scenes one by one through tf.map_fn (hf/core/models/rpn_model.py:683).
+    max_keep: the caller only uses keep_idx[:, :max_keep] (sb_nms_fn slices to nms_size, model_util.py:126): the
+    result is that slice, (S, max_keep), num_kept = min(kept, max_keep), and the greedy sweep stops there.
     """
     require(float(thresh) >= 0, "Need nms_threshold >= 0, got %r" % (thresh,))
     boxes = dev_tensor(boxes, torch.float32, "boxes")
@@ -47,13 +49,15 @@ def oriented_nms_batch(boxes, thresh, return_num_kept=False):
     s, n = boxes.shape[0], boxes.shape[1]
     lib = _lib.load()
     dev = boxes.device
-    keep = torch.empty((s, n), dtype=torch.int32, device=dev)
+    require(max_keep is None or (isinstance(max_keep, int) and max_keep >= 1), "max_keep must be a positive int")
+    width = n if max_keep is None else min(max_keep, n)
+    keep = torch.empty((s, width), dtype=torch.int32, device=dev)
     num_kept = torch.empty((s,), dtype=torch.int32, device=dev)
     ws_bytes = lib.hf_oriented_nms_workspace_bytes(s, n)
     ws = torch.empty((max(ws_bytes, 8) // 8,), dtype=torch.int64, device=dev)
     with torch.cuda.device(dev):
-        rc = lib.hf_oriented_nms(boxes.data_ptr(), s, n, float(thresh), keep.data_ptr(), num_kept.data_ptr(),
-                                 ws.data_ptr(), ws.numel() * 8, stream_ptr(dev))
+        rc = lib.hf_oriented_nms_topk(boxes.data_ptr(), s, n, float(thresh), width, keep.data_ptr(), num_kept.data_ptr(),
+                                      ws.data_ptr(), ws.numel() * 8, stream_ptr(dev))
     _lib.check(rc, "oriented_nms")
     return (keep, num_kept) if return_num_kept else keep
 

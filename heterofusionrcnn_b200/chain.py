@@ -46,11 +46,12 @@ class ChainConfig:
     # sampling spine: level 1 = one launch that writes the indices AND the picked points; levels 2-4 = one launch
     # (fps pyramid).  False = the reference's op sequence, farthest_point_sample + gather_point per level (8 launches).
     fused_sampling: bool = True
-    # first level (0-based) whose sampling goes into the pyramid launch together with every deeper level.  1 = levels 2-4
-    # in one launch (default).  2 = levels 3-4: level 2 gets its own launch, its points exist 0.06 ms earlier and its ball
-    # query / three_nn (the longest branch behind the spine) start sooner: 1.696 vs 1.714 ms for the SA/FP chain alone,
-    # but 2.026 vs 1.997 ms for the whole step (tools/ablation_probe.py)
-    pyramid_from: int = 1
+    # first level (0-based) whose sampling goes into ONE pyramid launch together with every deeper level (hf_fps_pyramid);
+    # the levels before it get a launch each (indices + points).  4 = no pyramid launch (default): every level's points
+    # exist as early as possible, and their ball query / three_nn / grouping - the tail behind the spine - start sooner.
+    # Measured with the final kernels (tools/pyramid_split_probe.py): 1 (levels 2-4 fused) 1.98 ms per step, 2: 1.82,
+    # 3 and 4: 1.80.  (With the round-1 FPS the fused pyramid was the better one by 0.03 ms: the spine was the bound.)
+    pyramid_from: int = 4
     # grouping: the coordinates and the features of a level's neighbourhoods in one launch (group_point_pair);
     # False = two group_point launches per level (pointnet_util.py:49,56)
     fused_grouping: bool = True
@@ -59,6 +60,8 @@ class ChainConfig:
     # 1.72 -> 1.59 ms per step, the whole step unchanged within noise: it is bound by the crop + NMS beside the spine);
     # 65536 -> 16384: 8.8 -> 5.6 ms (profiles/r2_fps_sorted_probe.txt, r2_fps_shape_in_step.txt)
     sorted_fps: object = None
+    # the NMS sweep stops once post_nms boxes are kept (what sb_nms_fn's slice uses); False = the whole keep list
+    nms_early_stop: bool = True
 
     def scaled(self, points):
         """Same chain on a different cloud size (npoint = n/4 per level)."""
@@ -349,7 +352,9 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
         have_xyz[0] = sample_level(0)
     if cfg.with_nms:
         with on(s_nms), probe("oriented_nms", b=b, nb=cfg.nms_boxes):
-            keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True)
+            # sb_nms_fn keeps the first post_nms entries (model_util.py:126): the sweep stops there
+            keep, num = oriented_nms_batch(dev["nms_boxes"], cfg.nms_thresh, return_num_kept=True,
+                                           max_keep=cfg.post_nms if cfg.nms_early_stop else None)
         res["nms_keep"] = keep[:, : cfg.post_nms]
         res["nms_num"] = num
     if cfg.with_crop:

@@ -822,7 +822,9 @@ constexpr int kSweep2Threads = 1024;
 constexpr int kSweepInflight = 8;
 __global__ void __launch_bounds__(kSweep2Threads)
     nms_sweep_kernel2(int boxes_num, const unsigned long long *__restrict__ mask, int *__restrict__ keep,
-                      int *__restrict__ num_kept) {
+                      int *__restrict__ num_kept, int max_keep) {
+    // max_keep < boxes_num: keep is (scenes, max_keep) and the sweep stops at the block in which the max_keep-th box is
+    // kept - the caller (sb_nms_fn's slice) never looks further, and with half of the boxes kept that is 1/8 of the blocks
     extern __shared__ unsigned long long remv[];  // [cb]
     __shared__ unsigned long long sdiag[kTile];
     __shared__ unsigned long long skeep;
@@ -830,7 +832,7 @@ __global__ void __launch_bounds__(kSweep2Threads)
     const int scene = blockIdx.x, t = threadIdx.x, lane = t & 31;
     const int r = t & 63, g = t >> 6;  // row of the block, column lane (16 of them)
     const unsigned long long *sm = mask + (size_t)scene * boxes_num * cb;
-    int *kp = keep + (size_t)scene * boxes_num;
+    int *kp = keep + (size_t)scene * max_keep;
     for (int c = t; c < cb; c += kSweep2Threads) remv[c] = 0ull;
     int kept = 0;
     unsigned long long dnext = (t < kTile && t < boxes_num) ? sm[(size_t)t * cb] : 0ull;
@@ -869,8 +871,15 @@ __global__ void __launch_bounds__(kSweep2Threads)
         }
         __syncthreads();
         const unsigned long long kb = skeep;
-        if (t < kTile && ((kb >> t) & 1ull)) kp[kept + __popcll(kb & ((1ull << t) - 1ull))] = nb * kTile + t;
+        if (t < kTile && ((kb >> t) & 1ull)) {
+            const int pos = kept + __popcll(kb & ((1ull << t) - 1ull));
+            if (pos < max_keep) kp[pos] = nb * kTile + t;
+        }
         kept += __popcll(kb);
+        if (kept >= max_keep) {  // block uniform
+            kept = max_keep;
+            break;
+        }
         const bool rkept = (kb >> r) & 1ull;
         for (int c0 = nb + 1; c0 < cb; c0 += 16 * kSweepInflight) {
             if (c0 != nb + 1) {
@@ -893,8 +902,9 @@ __global__ void __launch_bounds__(kSweep2Threads)
         }
         __syncthreads();
     }
-    const int first = kp[0];  // written by this CTA before the last barrier; pad with keep[0] (:110-112)
-    for (int p = kept + t; p < boxes_num; p += kSweep2Threads) kp[p] = first;
+    __syncthreads();          // (the early exit leaves the loop before its closing barrier)
+    const int first = kp[0];  // written by this CTA before the barrier; pad with keep[0] (:110-112)
+    for (int p = kept + t; p < max_keep; p += kSweep2Threads) kp[p] = first;
     if (num_kept && t == 0) num_kept[scene] = kept;
 }
 
@@ -1022,9 +1032,31 @@ extern "C" long long hf_oriented_nms_last_pair_count(int scenes, int boxes_num, 
     return (long long)v;
 }
 
+namespace hf {
+namespace {
+int oriented_nms_any(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int max_keep, int *keep,
+                     int *num_kept, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+}
+}  // namespace hf
+
 extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int *keep,
                                int *num_kept, void *workspace, size_t workspace_bytes, hf_stream_t stream) {
+    return hf::oriented_nms_any(boxes, scenes, boxes_num, nms_overlap_thresh, boxes_num, keep, num_kept, workspace,
+                                workspace_bytes, stream);
+}
+
+extern "C" int hf_oriented_nms_topk(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int max_keep,
+                                    int *keep, int *num_kept, void *workspace, size_t workspace_bytes, hf_stream_t stream) {
     using namespace hf;
+    HF_REQUIRE(max_keep >= 1, "OrientedNMS: max_keep must be >= 1");
+    return oriented_nms_any(boxes, scenes, boxes_num, nms_overlap_thresh, max_keep < boxes_num ? max_keep : boxes_num, keep,
+                            num_kept, workspace, workspace_bytes, stream);
+}
+
+namespace hf {
+namespace {
+int oriented_nms_any(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int max_keep, int *keep,
+                     int *num_kept, void *workspace, size_t workspace_bytes, hf_stream_t stream) {
     HF_REQUIRE(nms_overlap_thresh >= 0, "Need nms_threshold >= 0");
     HF_REQUIRE(boxes_num > 0 && scenes >= 0, "OrientendNMS expects (N, 5) boxes shape");
     HF_REQUIRE(boxes && keep, "OrientedNMS: null pointer");
@@ -1076,7 +1108,9 @@ extern "C" int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, fl
     HF_LAUNCH_OK("nms_clip_kernel");
     if (smem > 40 * 1024)
         HF_CUDA_OK(cudaFuncSetAttribute(nms_sweep_kernel2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nms_sweep_kernel2<<<scenes, kSweep2Threads, smem, s>>>(boxes_num, mask, keep, num_kept);
+    nms_sweep_kernel2<<<scenes, kSweep2Threads, smem, s>>>(boxes_num, mask, keep, num_kept, max_keep);
     HF_LAUNCH_OK("nms_sweep_kernel2");
     return HF_OK;
 }
+}  // namespace
+}  // namespace hf

@@ -120,15 +120,15 @@ __global__ void map_keep_kernel(long long total, int per_scene, const int *__res
 // the caller's box order; entries from `limit` on are -1, limit = min(nms_size, N) when the duplicate padding of the
 // keep list is kept (fixed_num_proposal_nms) and min(nms_size, kept) when tf.unique removes it (the kept boxes are
 // distinct and the padding repeats keep[0], so unique leaves exactly the kept ones in order).
-__global__ void sb_nms_select_kernel(int scenes, int per_scene, int nms_size, int fixed, const int *__restrict__ order,
-                                     const int *__restrict__ keep_sorted, const int *__restrict__ num_kept,
-                                     int *__restrict__ out, int *__restrict__ out_num) {
+__global__ void sb_nms_select_kernel(int scenes, int per_scene, int keep_stride, int nms_size, int fixed,
+                                     const int *__restrict__ order, const int *__restrict__ keep_sorted,
+                                     const int *__restrict__ num_kept, int *__restrict__ out, int *__restrict__ out_num) {
     const long long total = (long long)scenes * nms_size;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int scene = (int)(i / nms_size), j = (int)(i - (long long)scene * nms_size);
         const int limit = min(nms_size, fixed ? per_scene : num_kept[scene]);
         const long long base = (long long)scene * per_scene;
-        out[i] = j < limit ? order[base + keep_sorted[base + j]] : -1;
+        out[i] = j < limit ? order[base + keep_sorted[(long long)scene * keep_stride + j]] : -1;
         if (j == 0) out_num[scene] = limit;
     }
 }
@@ -234,16 +234,18 @@ int nms_scored(const float *boxes3d, const float *scores, int scenes, int boxes_
     HF_LAUNCH_OK("score_order_kernel");
     boxes3d_to_bev_kernel<<<grid_for((long long)sn), 256, 0, s>>>((long long)sn, boxes3d, order, boxes_num, bev);
     HF_LAUNCH_OK("boxes3d_to_bev_kernel");
-    int rc = hf_oriented_nms(bev, scenes, boxes_num, thresh, keep_sorted, num_kept, nms_ws,
-                             hf_oriented_nms_workspace_bytes(scenes, boxes_num), stream);
+    // the selection only looks at the first nms_size entries of the keep list: the sweep stops there
+    const int kstride = (sel && !keep && nms_size < boxes_num) ? nms_size : boxes_num;
+    int rc = hf_oriented_nms_topk(bev, scenes, boxes_num, thresh, kstride, keep_sorted, num_kept, nms_ws,
+                                  hf_oriented_nms_workspace_bytes(scenes, boxes_num), stream);
     if (rc != HF_OK) return rc;
     if (keep) {
         map_keep_kernel<<<grid_for((long long)sn), 256, 0, s>>>((long long)sn, boxes_num, order, keep_sorted, keep);
         HF_LAUNCH_OK("map_keep_kernel");
     }
     if (sel) {
-        sb_nms_select_kernel<<<grid_for((long long)scenes * nms_size), 256, 0, s>>>(scenes, boxes_num, nms_size, fixed, order,
-                                                                                   keep_sorted, num_kept, sel, sel_num);
+        sb_nms_select_kernel<<<grid_for((long long)scenes * nms_size), 256, 0, s>>>(scenes, boxes_num, kstride, nms_size, fixed,
+                                                                                   order, keep_sorted, num_kept, sel, sel_num);
         HF_LAUNCH_OK("sb_nms_select_kernel");
     }
     return HF_OK;

@@ -265,6 +265,11 @@ size_t hf_oriented_nms_workspace_bytes(int scenes, int boxes_num);
 int hf_oriented_nms(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh,
                     int *keep, int *num_kept, void *workspace, size_t workspace_bytes,
                     hf_stream_t stream);
+/* The same for callers that only use the first max_keep entries of the keep list (sb_nms_fn's slice,
+ * hf/core/models/model_util.py:126): keep is (S,max_keep) and equals hf_oriented_nms's keep[:, :max_keep]; num_kept (S) =
+ * min(boxes kept, max_keep).  The greedy sweep stops in the block where the max_keep-th box is kept. */
+int hf_oriented_nms_topk(const float *boxes, int scenes, int boxes_num, float nms_overlap_thresh, int max_keep, int *keep,
+                         int *num_kept, void *workspace, size_t workspace_bytes, hf_stream_t stream);
 /* Tuning override: 0 = enumerate pairs in score order (no spatial sort, no tile culling to
  * speak of), 1 = Morton order (default).  Results are identical. */
 void hf_nms_set_spatial_sort(int on);

@@ -98,7 +98,7 @@ def test_bench_chain_graph_matches_reference_kernels(cuda, oracle):
     for s in range(batch):
         rmask = N(_refcuda.nms_mask(dev["nms_boxes"][s], cfg.nms_thresh)).view(np.uint64)
         want, kept = oracle.nms_sweep(rmask)
-        assert int(num[s]) == kept, "nms count scene %d" % s
+        assert int(num[s]) == min(kept, cfg.post_nms), "nms count scene %d" % s  # the sweep stops at post_nms kept boxes
         assert np.array_equal(keep[s], want[: cfg.post_nms]), "nms keep scene %d" % s
         margin.append(kept)
     assert min(margin) > 0

@@ -595,6 +595,19 @@ def test_oriented_nms_spatial_sort_changes_nothing(cuda, n, thresh):
     assert torch.equal(n0, n1) and torch.equal(k0, k1)
 
 
+@pytest.mark.parametrize("n,thresh,max_keep", [(2500, 0.85, 512), (9000, 0.8, 512), (700, 0.01, 64), (700, 0.01, 1),
+                                               (300, 0.5, 300), (300, 0.5, 1000), (65, 0.3, 7)])
+def test_oriented_nms_max_keep_is_the_slice_of_the_full_list(cuda, n, thresh, max_keep):
+    """max_keep (the sweep stops once that many boxes are kept - sb_nms_fn's slice, model_util.py:126): keep ==
+    full keep list[:, :max_keep] incl. its keep[0] padding when fewer are kept, num_kept == min(kept, max_keep)."""
+    boxes = T(np.stack([synthetic.make_nms_boxes(500 + s, n, 7) for s in range(3)]), cuda)
+    full, num = oriented_nms_batch(boxes, thresh, return_num_kept=True)
+    part, pnum = oriented_nms_batch(boxes, thresh, return_num_kept=True, max_keep=max_keep)
+    w = min(max_keep, n)
+    assert tuple(part.shape) == (3, w)
+    assert torch.equal(part, full[:, :w]) and torch.equal(pnum, torch.clamp(num, max=w))
+
+
 def test_oriented_nms_mask_matches_oracle_and_sweep(cuda, oracle):
     boxes = synthetic.make_nms_boxes(12, 900, 5)
     wmask = oracle.oriented_nms_mask(boxes, 0.6)
