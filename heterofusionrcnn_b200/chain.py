@@ -62,6 +62,9 @@ class ChainConfig:
     sorted_fps: object = None
     # the NMS sweep stops once post_nms boxes are kept (what sb_nms_fn's slice uses); False = the whole keep list
     nms_early_stop: bool = True
+    # warps per CTA of the level-1 FPS clusters (0 = the library's heuristic: 8 CTAs x 4 warps up to 15 scans, 4 x 8
+    # beyond; 4 forces 8 x 4 for any batch).  A tuning knob for tools/, not needed by callers.
+    fps_level1_warps: int = 0
 
     def scaled(self, points):
         """Same chain on a different cloud size (npoint = n/4 per level)."""
@@ -320,8 +323,16 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                 ix = index[0] if (l == 0 and sorted_fps) else None
                 if ix is not None:
                     after(crit, index_ready[0])
-                with probe("fps", level=l + 1, b=b, n=n, m=m, xyz=1):
-                    idx, new_xyz = farthest_point_sample_with_xyz(m, xyz[l], index=ix)
+                force = cfg.fps_level1_warps if l == 0 else 0
+                if force:
+                    from . import _lib
+                    _lib.load().hf_fps_set_variant(3, force, 0)
+                try:
+                    with probe("fps", level=l + 1, b=b, n=n, m=m, xyz=1):
+                        idx, new_xyz = farthest_point_sample_with_xyz(m, xyz[l], index=ix)
+                finally:
+                    if force:
+                        _lib.load().hf_fps_set_variant(0, 0, 0)
                 fps_idx.append(idx)
                 xyz.append(new_xyz)
             else:

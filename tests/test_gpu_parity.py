@@ -685,23 +685,24 @@ def test_chain_fused_entries_equal_the_reference_op_sequence(cuda, points, batch
     dev = chain.to_device(chain.make_host_inputs(cfg, batch=batch, seed=9), cuda)
     plain = chain.ChainConfig(**{**cfg.__dict__})
     plain.fused_sampling, plain.fused_grouping, plain.sorted_fps = False, False, False
-    fused = chain.ChainConfig(**{**cfg.__dict__})
-    fused.sorted_fps = True
     a = chain.run_chain(dev, plain, overlap=False)
-    for overlap in (False, True):
-        b = chain.run_chain(dev, fused, overlap=overlap)
-        torch.cuda.synchronize()
-        for l in range(4):
-            assert torch.equal(a["fps_idx"][l], b["fps_idx"][l]), l
-            assert torch.equal(a["xyz_levels"][l + 1], b["xyz_levels"][l + 1]), l
-            for x, y in zip(a["sa%d" % (l + 1)], b["sa%d" % (l + 1)]):
-                assert torch.equal(x, y), l
-            for x, y in zip(a["fp%d" % (l + 1)], b["fp%d" % (l + 1)]):
-                assert torch.equal(x, y), l
-        for x, y in zip(a["crop"], b["crop"]):
-            assert torch.equal(x, y)
-        assert torch.equal(a["nms_keep"], b["nms_keep"]) and torch.equal(a["nms_num"], b["nms_num"])
-    assert chain.chain_launches(plain) - chain.chain_launches(fused) == 6 + 4
+    for pyramid_from, saved in ((4, 4 + 4), (1, 6 + 4), (2, 5 + 4)):  # a launch per level / levels 2-4 (3-4) in one launch
+        fused = chain.ChainConfig(**{**cfg.__dict__})
+        fused.sorted_fps, fused.pyramid_from = True, pyramid_from
+        for overlap in (False, True):
+            b = chain.run_chain(dev, fused, overlap=overlap)
+            torch.cuda.synchronize()
+            for l in range(4):
+                assert torch.equal(a["fps_idx"][l], b["fps_idx"][l]), l
+                assert torch.equal(a["xyz_levels"][l + 1], b["xyz_levels"][l + 1]), l
+                for x, y in zip(a["sa%d" % (l + 1)], b["sa%d" % (l + 1)]):
+                    assert torch.equal(x, y), l
+                for x, y in zip(a["fp%d" % (l + 1)], b["fp%d" % (l + 1)]):
+                    assert torch.equal(x, y), l
+            for x, y in zip(a["crop"], b["crop"]):
+                assert torch.equal(x, y)
+            assert torch.equal(a["nms_keep"], b["nms_keep"]) and torch.equal(a["nms_num"], b["nms_num"])
+        assert chain.chain_launches(plain) - chain.chain_launches(fused) == saved
 
 
 # ---------------------------------------------------------------- three_nn fused with the FP weights

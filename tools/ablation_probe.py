@@ -20,9 +20,9 @@ def main():
     base = chain.ChainConfig()
     host = chain.make_host_inputs(base, batch=16, seed=2)
     resident = chain.to_device(host, dev)
-    for name, crop, nms, pyr in (("whole chain", True, True, 2), ("whole chain, pyramid of levels 2-4", True, True, 1),
-                                 ("without the NMS", True, False, 2), ("without the crop", False, True, 2),
-                                 ("SA/FP chain only", False, False, 2), ("SA/FP chain only, pyramid of levels 2-4", False, False, 1)):
+    for name, crop, nms, pyr in (("whole chain", True, True, 4), ("whole chain, pyramid of levels 2-4", True, True, 1),
+                                 ("without the NMS", True, False, 4), ("without the crop", False, True, 4),
+                                 ("SA/FP chain only", False, False, 4), ("SA/FP chain only, pyramid of levels 2-4", False, False, 1)):
         cfg = chain.ChainConfig(**{**base.__dict__})
         cfg.with_crop, cfg.with_nms, cfg.pyramid_from = crop, nms, pyr
         g = chain.ChainGraph(resident, cfg)

@@ -22,14 +22,10 @@ def main():
     for name, sorted_fps, warps in (("plain, 4 x 8 warps (default)", False, 0), ("plain, 8 x 4 warps", False, 4),
                                     ("index, 4 x 8 warps", True, 8), ("index, 8 x 4 warps", True, 4)):
         cfg = chain.ChainConfig(**{**base.__dict__})
-        cfg.sorted_fps = sorted_fps
+        cfg.sorted_fps, cfg.fps_level1_warps = sorted_fps, warps
         for with_rest in (True, False):
             cfg.with_crop = cfg.with_nms = with_rest
-            lib.hf_fps_set_variant(3 if warps else 0, warps, 0)
-            try:
-                g = chain.ChainGraph(res, cfg)
-            finally:
-                lib.hf_fps_set_variant(0, 0, 0)
+            g = chain.ChainGraph(res, cfg)
             for _ in range(3):
                 g.replay()
             torch.cuda.synchronize()
