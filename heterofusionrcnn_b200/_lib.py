@@ -68,6 +68,7 @@ SIGNATURES = {
     "hf_boxes3d_to_corners": (_c_int, [ctypes.c_longlong, _ptr, _c_float, _ptr, _ptr]),
     "hf_box3d_iou_workspace_bytes": (_size_t, [_c_int, _c_int]),
     "hf_box3d_iou": (_c_int, [_c_int, _ptr, _c_int, _ptr, _ptr, _ptr, _ptr, _size_t, _ptr]),
+    "hf_box3d_iou_static": (_c_int, [_c_int, _ptr, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_oriented_nms_scored_workspace_bytes": (_size_t, [_c_int, _c_int]),
     "hf_oriented_nms_scored": (_c_int, [_ptr, _ptr, _c_int, _c_int, _c_float, _ptr, _ptr, _ptr, _size_t, _ptr]),
     "hf_sb_nms_workspace_bytes": (_size_t, [_c_int, _c_int]),

@@ -10,6 +10,8 @@
 #include <float.h>
 #include <stdint.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace hf {
@@ -292,3 +294,74 @@ extern "C" int hf_sb_nms(const float *boxes3d, const float *scores, int scenes, 
                       nms_indices, num_selected, workspace, workspace_bytes, stream);
 }
 
+
+// ---- hf_box3d_iou_static: box3d_iou for hosts that may not allocate ---------------------------------------------------
+// Same four launches as hf_box3d_iou; the one difference is where the two BEV box lists are staged.  hf_box3d_iou
+// takes that memory from the caller.  A caller that cannot obtain device memory at call time (an executor that bans
+// cudaMalloc on its worker threads because it stalls the whole device, a control loop with a frozen memory budget)
+// gets it from the array below, which is part of this library's device image: it occupies 320 KiB on every GPU the
+// library is loaded on, from load until the process exits.
+namespace hf {
+namespace {
+
+constexpr size_t kStaticSideBytes = (size_t)HF_BOX3D_IOU_STATIC_MAX_BOXES * 5 * sizeof(float);  // one BEV list
+static_assert(kStaticSideBytes % 256 == 0, "the second list must start on the array's alignment");
+// [0, kStaticSideBytes): BEV boxes of boxes_a; [kStaticSideBytes, 2 * kStaticSideBytes): BEV boxes of boxes_b.
+static __device__ __align__(256) unsigned char g_box3d_iou_static_scratch[2 * kStaticSideBytes];
+
+// In host code `g_box3d_iou_static_scratch` is only a handle for the runtime, never an address a kernel may be given.
+// The device address differs per GPU; it is looked up once per device ordinal, with that device current, and kept.
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+unsigned char *g_static_device_ptr[kStaticMaxDevices];  // nullptr = not looked up on that device yet
+
+int static_scratch_of_current_device(unsigned char **out) {
+    int dev = -1;
+    HF_CUDA_OK(cudaGetDevice(&dev));
+    const bool cached_slot = dev >= 0 && dev < kStaticMaxDevices;
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (cached_slot && g_static_device_ptr[dev]) {
+        *out = g_static_device_ptr[dev];
+        return HF_OK;
+    }
+    unsigned char *ptr = nullptr;
+    HF_CUDA_OK(cudaGetSymbolAddress((void **)&ptr, g_box3d_iou_static_scratch));
+    if (!ptr) {
+        set_error("box3d_iou_static: the runtime returned a null address for the library's staging array on device %d", dev);
+        return HF_ERR_CUDA;
+    }
+    if (cached_slot) g_static_device_ptr[dev] = ptr;  // ordinals past the table are looked up on every call
+    *out = ptr;
+    return HF_OK;
+}
+
+}  // namespace
+}  // namespace hf
+
+extern "C" int hf_box3d_iou_static(int num_a, const float *boxes_a, int num_b, const float *boxes_b, float *iou_3d,
+                                   float *iou_2d, hf_stream_t stream) {
+    using namespace hf;
+    HF_REQUIRE(num_a >= 0 && num_b >= 0, "box3d_iou expects (N,7) and (M,7) boxes");
+    if (num_a > HF_BOX3D_IOU_STATIC_MAX_BOXES || num_b > HF_BOX3D_IOU_STATIC_MAX_BOXES) {
+        set_error("box3d_iou_static: %d x %d boxes, but the library's built-in staging array holds at most %d boxes per side; "
+                  "use hf_box3d_iou with a caller workspace for larger sets",
+                  num_a, num_b, HF_BOX3D_IOU_STATIC_MAX_BOXES);
+        return HF_ERR_UNSUPPORTED;
+    }
+    if (num_a == 0 || num_b == 0) return HF_OK;
+    HF_REQUIRE(boxes_a && boxes_b && iou_3d && iou_2d, "box3d_iou: null pointer");
+    unsigned char *scratch = nullptr;
+    int rc = static_scratch_of_current_device(&scratch);
+    if (rc != HF_OK) return rc;
+    // Whatever an earlier call left in the array is dead: the two conversions below write the num_a and num_b entries
+    // that the IoU kernel then reads, in stream order.  Calls that overlap on the GPU would race on these bytes.
+    float *bev_a = reinterpret_cast<float *>(scratch);
+    float *bev_b = reinterpret_cast<float *>(scratch + kStaticSideBytes);
+    rc = hf_boxes3d_to_bev(num_a, boxes_a, bev_a, stream);
+    if (rc == HF_OK) rc = hf_boxes3d_to_bev(num_b, boxes_b, bev_b, stream);
+    if (rc == HF_OK) rc = hf_compute_bev_iou(num_a, bev_a, num_b, bev_b, iou_3d, iou_2d, stream);  // iou_3d <- overlap
+    if (rc != HF_OK) return rc;
+    box3d_iou_kernel<<<grid_for((long long)num_a * num_b), 256, 0, (cudaStream_t)stream>>>(num_a, num_b, boxes_a, boxes_b, iou_3d);
+    HF_LAUNCH_OK("box3d_iou_kernel");
+    return HF_OK;
+}

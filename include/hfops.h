@@ -357,6 +357,27 @@ int hf_boxes3d_to_corners(long long num, const float *boxes3d, float expand_leng
 size_t hf_box3d_iou_workspace_bytes(int num_a, int num_b);
 int hf_box3d_iou(int num_a, const float *boxes_a, int num_b, const float *boxes_b, float *iou_3d,
                  float *iou_2d, void *workspace, size_t workspace_bytes, hf_stream_t stream);
+/* hf_box3d_iou for callers that have no device memory to lend and no way to get any.  This entry has NO counterpart
+ * in the reference; it exists because hf_box3d_iou needs a staging buffer for the two BEV box lists, and some hosts
+ * cannot supply one: a plugin running inside another framework's executor that forbids cudaMalloc on its worker
+ * threads (an allocation synchronises the whole device and stalls every other stream), a real-time loop whose memory
+ * is fixed at start-up, a process whose memory pool is already handed out in full.  Here the staging buffer is a fixed array inside the library's own device image (2 x 8192 x 20 bytes =
+ * 320 KiB; every GPU that loads libhfops.so keeps it until the process exits, whether or not this entry is ever
+ * called).  The call makes no cudaMalloc / cudaFree and calls nothing that allocates; inputs and outputs are still
+ * the caller's, and the results are those of hf_box3d_iou.
+ *   - Limit: num_a and num_b <= HF_BOX3D_IOU_STATIC_MAX_BOXES each; more returns HF_ERR_UNSUPPORTED (hf_last_error
+ *     names the limit) and launches nothing.  Larger problems: hf_box3d_iou with a workspace.
+ *   - First call on each device: the library looks up the device address of its array (cudaGetSymbolAddress, with
+ *     that device current) and remembers it per device; a failed look-up returns HF_ERR_CUDA.  Make that first call
+ *     during set-up, before any stream capture begins.
+ *   - One array per device, shared by every call and every thread: two calls whose kernels can be on the GPU at the
+ *     same time (different streams, or different host threads on different streams) overwrite each other's staging
+ *     data and give wrong answers.  Keep calls on one stream, or order them with events.  The array keeps the
+ *     previous call's boxes; nothing in it has to start at zero, because each call writes the num_a + num_b entries
+ *     it is about to read before it reads them. */
+#define HF_BOX3D_IOU_STATIC_MAX_BOXES 8192
+int hf_box3d_iou_static(int num_a, const float *boxes_a, int num_b, const float *boxes_b, float *iou_3d, float *iou_2d,
+                        hf_stream_t stream);
 /* oriented_nms_tf, compute_iou.py:67-80, batched over scenes (the reference maps scenes with
  * tf.map_fn, rpn_model.py:683): boxes3d (S,N,7), scores (S,N) in any order -> keep (S,N) indices
  * into the caller's box order (descending score, suppressed boxes removed, tail padded with
