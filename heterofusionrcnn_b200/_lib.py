@@ -35,6 +35,7 @@ SIGNATURES = {
     "hf_fps_set_cluster": (None, [_c_int]),
     "hf_fps_set_threads": (None, [_c_int]),
     "hf_fps_set_variant": (None, [_c_int, _c_int, _c_int]),
+    "hf_fps_get_variant": (None, [_ptr, _ptr, _ptr]),
     "hf_gather_point": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_gather_set_mode": (None, [_c_int]),
     "hf_group_point_pair": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),

@@ -324,15 +324,19 @@ def run_chain(dev, cfg, probe=None, overlap=True, slot=0, join=True):
                 if ix is not None:
                     after(crit, index_ready[0])
                 force = cfg.fps_level1_warps if l == 0 else 0
-                if force:
+                if force:  # scoped: the variant the caller (a probe under tools/) had selected comes back afterwards
+                    import ctypes
+
                     from . import _lib
+                    prev = [ctypes.c_int(0) for _ in range(3)]
+                    _lib.load().hf_fps_get_variant(*[ctypes.byref(v) for v in prev])
                     _lib.load().hf_fps_set_variant(3, force, 0)
                 try:
                     with probe("fps", level=l + 1, b=b, n=n, m=m, xyz=1):
                         idx, new_xyz = farthest_point_sample_with_xyz(m, xyz[l], index=ix)
                 finally:
                     if force:
-                        _lib.load().hf_fps_set_variant(0, 0, 0)
+                        _lib.load().hf_fps_set_variant(*[v.value for v in prev])
                 fps_idx.append(idx)
                 xyz.append(new_xyz)
             else:

@@ -342,6 +342,11 @@ extern "C" void hf_fps_set_variant(int algo, int warps, int buckets_per_warp) {
     hf::g_bucket_w = warps;
     hf::g_bucket_j = buckets_per_warp;
 }
+extern "C" void hf_fps_get_variant(int *algo, int *warps, int *buckets_per_warp) {
+    if (algo) *algo = hf::g_algo;
+    if (warps) *warps = hf::g_bucket_w;
+    if (buckets_per_warp) *buckets_per_warp = hf::g_bucket_j;
+}
 
 namespace hf {
 namespace {

@@ -88,10 +88,22 @@ int hf_fps_pyramid(int b, int levels, int n, const int *m, const float *inp, int
 void hf_fps_set_cluster(int cluster);
 /* Tuning override for the FPS CTA size (256 or 512 threads, 0 = heuristic). */
 void hf_fps_set_threads(int threads);
-/* Tuning override for the FPS algorithm: algo 0 = heuristic, 1 = plain on-chip kernel
- * (every point every iteration), 2 = bucket-pruned kernel with `warps` x `buckets_per_warp`
- * buckets of 32 points per CTA (0,0 = heuristic shape).  Results are identical. */
+/* Tuning override for the FPS algorithm.  Results are identical for every setting.
+ *   algo 0 = heuristic (the multi-pick cluster kernel of csrc/fps_multi.cu where it has a shape, else algo 1);
+ *   algo 1 = plain on-chip kernel (every point every iteration, csrc/sampling.cu);
+ *   algo 2 = bucket-pruned kernel (csrc/fps_bucket.cu) with `warps` x `buckets_per_warp` buckets of 32 points per
+ *            CTA (0,0 = heuristic shape);
+ *   algo 3 = the multi-pick cluster kernel with a forced CTA shape: `warps` = warps per CTA (4, 6 or 8; 0 = the
+ *            heuristic's), and for the indexed form (hf_farthest_point_sample_indexed) `buckets_per_warp` selects how
+ *            the curve-ordered cloud is dealt out: 1 = a compact region per warp, any other value = a compact region per
+ *            thread (the default).  A shape the kernel has no instantiation for returns HF_ERR_UNSUPPORTED.
+ * Like every hf_*_set_* override (hf_fps_set_cluster / _threads / _variant, hf_gather_set_mode, hf_spatial_set_mode,
+ * hf_spatial_set_pair_counter, hf_nms_set_spatial_sort) the setting belongs to the CALLING THREAD: it changes what
+ * that thread launches from then on and is invisible to every other thread, so set it on the thread that makes the
+ * calls.  hf_fps_get_variant reads the calling thread's setting back (any pointer may be NULL) so that a scoped
+ * override can restore what was there before. */
 void hf_fps_set_variant(int algo, int warps, int buckets_per_warp);
+void hf_fps_get_variant(int *algo, int *warps, int *buckets_per_warp);
 
 /* Replaces gatherpointLauncher(b,n,m,inp,idx,out), sampling/tf_sampling_g.cu:206.
  * inp (b,n,3), idx (b,m) -> out (b,m,3). */
@@ -114,7 +126,9 @@ int hf_prob_sample(int b, int n, int m, const float *inp_p, const float *inp_r, 
  *   extra (S,num_out) uint32 (may be NULL unless num_out > 2n): choice(a, k, replace=True) := a[extra[e] % len(a)];
  *   slot_of (S,num_out) int32, a permutation per scan: shuffle(choice) := new[slot_of[j]] = old[j].
  * choice (S,num_out) int32 (may be NULL) receives the source row of every output row; status (S): 1, or 0 where the
- * reference raises (empty scan; more far points than num_out) and the rows are zero.  n_cap <= 131072. */
+ * reference raises (empty scan; more far points than num_out) and the rows are zero.  A slot_of entry outside
+ * [0, num_out) also gives status 0 and zero rows for that scan; that slot_of holds no value twice is the caller's
+ * precondition and is not checked (a duplicate leaves one row unwritten).  n_cap <= 131072. */
 int hf_pc_sample_points(int scans, int n_cap, int num_out, const float *pts, const int *counts, const unsigned *keys,
                         const int *slot_of, const unsigned *extra, float depth_split, float intensity_shift, float *out,
                         int *choice, int *status, hf_stream_t stream);

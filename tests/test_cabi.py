@@ -134,3 +134,32 @@ def test_tuning_overrides_are_per_thread():
     t.join()
     assert seen["other"] == 1
     assert lib.hf_spatial_applies(1024, 1024) == 0  # this thread still sees the default
+
+
+def test_fps_variant_can_be_read_back_and_is_per_thread():
+    """hf_fps_get_variant returns the calling thread's hf_fps_set_variant setting (what chain.run_chain uses to put a
+    caller's variant back after its own scoped override); another thread sees the default."""
+    import threading
+
+    from heterofusionrcnn_b200 import _lib
+
+    lib = _lib.load()
+
+    def get():
+        v = [ctypes.c_int(-1) for _ in range(3)]
+        lib.hf_fps_get_variant(*[ctypes.byref(x) for x in v])
+        return [x.value for x in v]
+
+    assert get() == [0, 0, 0]
+    lib.hf_fps_set_variant(3, 6, 1)
+    try:
+        assert get() == [3, 6, 1]
+        lib.hf_fps_get_variant(None, None, None)  # every pointer is optional
+        seen = {}
+        t = threading.Thread(target=lambda: seen.update(other=get()))
+        t.start()
+        t.join()
+        assert seen["other"] == [0, 0, 0]
+    finally:
+        lib.hf_fps_set_variant(0, 0, 0)
+    assert get() == [0, 0, 0]
