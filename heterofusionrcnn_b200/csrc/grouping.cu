@@ -209,8 +209,10 @@ __global__ void __launch_bounds__(kGbThreads)
         const long long g = gw + k * nw;
         if (g >= groups) break;
         const int s = (int)(k % kGbStages);
-        // stage (k + 2) % 3 was written out as group k - 1: its store must have read the stage before it is refilled
-        if (lane == 0) tma_store_wait_read<1>();
+        // stage (k + 2) % 3 == (k - 1) % 3 was written out as bulk group k - 1, the NEWEST committed group: every
+        // committed store must have finished reading shared memory before that stage is refilled (wait_group.read 0; a
+        // wait of 1 would let exactly group k - 1 still be reading).  That store was issued a whole mbar_wait ago.
+        if (lane == 0) tma_store_wait_read<0>();
         __syncwarp();
         issue(k + 2);
         mbar_wait(&bars[warp][s], (uint32_t)(k / kGbStages) & 1u);

@@ -365,6 +365,29 @@ def test_group_point_tma_row_mover(cuda, oracle, c):
     assert np.array_equal(N(got), oracle.group_point(pts, idx))
 
 
+@pytest.mark.parametrize("c", [4, 8, 32])
+def test_group_point_tma_row_mover_stage_reuse_stress(cuda, c):
+    """Many short rows through the bulk row mover: every warp walks its ring of three shared-memory stages hundreds
+    of times, so a stage refilled while the previous store still reads it (write-after-read on the stage) would show
+    as rows of the wrong source.  Row r of the source holds the value r in every channel, so validity is checked on
+    the device against the index itself, over several repetitions."""
+    from heterofusionrcnn_b200 import _lib
+
+    b, n, m, ns = 4, 4096, 16384, 32
+    g = torch.Generator(device="cpu").manual_seed(c)
+    idx = torch.randint(0, n, (b, m, ns), generator=g, dtype=torch.int32).to(cuda)
+    pts = (torch.arange(n, dtype=torch.float32, device=cuda)[None, :, None] +
+           n * torch.arange(b, dtype=torch.float32, device=cuda)[:, None, None]).expand(b, n, c).contiguous()
+    want = (idx.to(torch.float32) + n * torch.arange(b, dtype=torch.float32, device=cuda)[:, None, None])[..., None].expand(b, m, ns, c)
+    _lib.load().hf_gather_set_mode(1)
+    try:
+        for _ in range(5):
+            got = group_point(pts, idx)
+            assert torch.equal(got, want)
+    finally:
+        _lib.load().hf_gather_set_mode(0)
+
+
 # ---------------------------------------------------------------- three_nn / interpolate
 @pytest.mark.parametrize("b,n,m", [(2, 16384, 4096), (2, 4096, 1024), (3, 1024, 256), (2, 256, 64), (2, 333, 1027),
                                    (1, 10, 2), (1, 5, 1)])
@@ -671,6 +694,36 @@ def test_chain_on_streams_equals_chain_in_program_order(cuda):
         assert len(a) == len(b)
         for (ka, ta), (kb, tb) in zip(a, b):
             assert ka == kb and torch.equal(ta, tb), ka
+
+
+def test_chain_level1_shape_knob_restores_the_callers_fps_variant(cuda):
+    """ChainConfig.fps_level1_warps is a scoped override: whatever hf_fps_set_variant the caller had chosen is back in
+    place when run_chain returns (it used to be reset to the heuristic), and the results do not depend on the knob."""
+    import ctypes
+
+    from heterofusionrcnn_b200 import _lib, chain
+
+    lib = _lib.load()
+
+    def variant():
+        v = [ctypes.c_int(-1) for _ in range(3)]
+        lib.hf_fps_get_variant(*[ctypes.byref(x) for x in v])
+        return [x.value for x in v]
+
+    cfg = chain.ChainConfig().scaled(8192)
+    cfg.crop_boxes, cfg.crop_resize, cfg.crop_channels, cfg.nms_boxes = 16, 64, 16, 500
+    dev = chain.to_device(chain.make_host_inputs(cfg, batch=2, seed=11), cuda)
+    want = chain.run_chain(dev, cfg)["fps_idx"]
+    knob = chain.ChainConfig(**{**cfg.__dict__})
+    knob.fps_level1_warps = 8
+    lib.hf_fps_set_variant(3, 4, 1)  # the caller's own choice (a probe under tools/)
+    try:
+        got = chain.run_chain(dev, knob)["fps_idx"]
+        assert variant() == [3, 4, 1]
+    finally:
+        lib.hf_fps_set_variant(0, 0, 0)
+    torch.cuda.synchronize()
+    assert len(got) == len(want) and all(torch.equal(a, b) for a, b in zip(got, want))
 
 
 @pytest.mark.parametrize("points,batch", [(8192, 3), (16384, 2), (20000, 2)])
