@@ -91,9 +91,13 @@ __global__ void __launch_bounds__(kPsThreads)
         }
         if (t == 0) status[scene] = 0;
     };
+    bool bad_slot = false;  // this thread met a slot_of entry outside [0, P)
     auto emit = [&](int j, int i) {  // pre-shuffle position j holds point i
         const int slot = slot_of[j];
-        if (slot < 0 || slot >= P) return;  // not a permutation: the row stays unwritten, status reports it below
+        if (slot < 0 || slot >= P) {  // not a permutation: nothing is written through it, the scan is failed below
+            bad_slot = true;
+            return;
+        }
         float4 p = pts[i];
         p.w = __fsub_rn(p.w, shift);
         out[slot] = p;
@@ -221,6 +225,13 @@ __global__ void __launch_bounds__(kPsThreads)
         for (int e = t; e < P - n; e += kPsThreads) emit(n + e, (int)(extra[e] % (unsigned)n));
     }
     (void)n_cand;
+    // An out-of-range slot_of entry would leave rows of `out` unwritten: report the scan like the reference's own
+    // failures (status 0, rows zero).  The barrier also orders every emit() before fail()'s rewrite of the rows.
+    // (Duplicate in-range slots are the caller's precondition and are not detected.)
+    if (__syncthreads_or(bad_slot ? 1 : 0)) {
+        fail();
+        return;
+    }
     if (t == 0) status[scene] = 1;
 }
 

@@ -105,3 +105,24 @@ def test_pc_sample_argument_errors(cuda):
         kitti_sampling.sample_point_cloud(pts, cnt, 4, keys[:, :5], slot)
     with pytest.raises(InvalidArgumentError):
         kitti_sampling.sample_point_cloud(pts, cnt, 5, keys, slot)
+
+
+@pytest.mark.parametrize("n,P", [(600, 256), (100, 256)])
+def test_pc_sample_reports_a_slot_outside_the_output(cuda, n, P):
+    """slot_of must be a permutation of range(P).  An entry outside [0, P) cannot be honoured: the scan is reported with
+    status 0 and zero rows (include/hfops.h), the other scans of the batch are unaffected."""
+    rng = np.random.default_rng(n)
+    pts = rng.uniform(0.1, 39, (2, n, 4)).astype(np.float32)
+    counts = np.array([n, n], np.int32)
+    keys, slot_of, extra = kitti_sampling.draw_randomness(rng, 2, n, P)
+    good, gstatus = kitti_sampling.sample_point_cloud(T(pts, cuda), T(counts, cuda), P, T(keys, cuda), T(slot_of, cuda),
+                                                      T(extra, cuda))
+    assert N(gstatus).tolist() == [1, 1]
+    bad = slot_of.copy()
+    bad[1, 7] = P  # one past the end
+    bad[1, 100] = -3
+    out, status, choice = kitti_sampling.sample_point_cloud(T(pts, cuda), T(counts, cuda), P, T(keys, cuda), T(bad, cuda),
+                                                            T(extra, cuda), return_choice=True)
+    assert N(status).tolist() == [1, 0]
+    assert torch.equal(out[0], good[0])
+    assert not N(out[1]).any() and (N(choice[1]) == -1).all()
