@@ -58,6 +58,18 @@ inline int num_sms() {
     return sms;
 }
 
+// Read-only view of a cloud index (hf_cloud_index_build) for the kernels outside spatial.cu that consume one.  The
+// layout has ONE owner, spatial.cu (carve_index / super_count / kMaxIndexed): consumers ask for the view instead of
+// re-deriving offsets.  Returns false (and leaves *view alone) when `index` is null or not 16-byte aligned, or when a
+// cloud of (b, n) cannot be indexed at all; sorted/boxes/super are float4 records as documented in spatial.cu.
+struct CloudIndexView {
+    const float4 *sorted;  // (b, npad) {x, y, z, original index as int bits}; padding = {NaN, NaN, NaN, -1}
+    const float4 *boxes;   // (b, npad / 32, 2) bucket boxes {lo.xyz, smallest original index}, {hi.xyz, -}
+    const float4 *super;   // (b, nsuper, 2) boxes of 32 consecutive buckets; nullptr when nsuper == 0
+    int npad, nsuper;
+};
+bool cloud_index_view(int b, int n, const void *index, CloudIndexView *view);
+
 #ifdef __CUDACC__
 // ---- device side ----------------------------------------------------------
 

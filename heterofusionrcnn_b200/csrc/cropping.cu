@@ -326,14 +326,11 @@ extern "C" int hf_pc_crop_and_sample_indexed(const float *pts, const float *fts,
     }
     const bool vec = (channel % 4 == 0) && ((reinterpret_cast<uintptr_t>(fts) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(crop_fts) & 15) == 0);
-    // cloud index layout (spatial.cu:carve_index): [sorted: batch x npad float4][boxes: batch x npad/32 x 2 float4]
-    // [super: batch x nsuper x 2 float4, clouds above 16384 points only]
-    const bool indexed = pts_index && (reinterpret_cast<uintptr_t>(pts_index) & 15) == 0 && hf_cloud_index_bytes(batch, npts) != 0;
-    const int npad = (npts + 31) & ~31;
-    const float4 *ix_sorted = static_cast<const float4 *>(pts_index);
-    const float4 *ix_boxes = indexed ? ix_sorted + (size_t)batch * npad : nullptr;
-    const int nsuper = npad > 16384 ? (npad / 32 + 31) / 32 : 0;
-    const float4 *ix_super = (indexed && nsuper) ? ix_boxes + (size_t)batch * (npad / 32) * 2 : nullptr;
+    // the layout of a cloud index belongs to spatial.cu: ask it for the view (false = no usable index, plain select)
+    CloudIndexView ix = {nullptr, nullptr, nullptr, (npts + 31) & ~31, 0};
+    const bool indexed = cloud_index_view(batch, npts, pts_index, &ix);
+    const int npad = ix.npad, nsuper = ix.nsuper;
+    const float4 *ix_sorted = ix.sorted, *ix_boxes = ix.boxes, *ix_super = ix.super;
     cudaStream_t s = (cudaStream_t)stream;
 #define HF_CROP_ARGS                                                                                                     \
     smem, s, pts, fts, intensities, mask, boxes, box_ind, num_boxes, npts, resize, channel, intensity_channel, crop_pts, \

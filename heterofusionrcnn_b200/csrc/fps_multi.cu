@@ -685,8 +685,10 @@ int fps_multi_dispatch(int b, int n, int m, const float *inp, int *out, float *o
 int fps_sorted_dispatch(int b, int n, int m, const float *inp, const void *index, int *out, float *oxyz, cudaStream_t s,
                         int warps_req, int mode_req) {
     const int mode = mode_req == 1 ? 1 : 2;  // 1 = compact warps, 2 = compact threads (default)
-    const int npad = (n + 31) & ~31;
-    const float4 *sorted = reinterpret_cast<const float4 *>(index);
+    CloudIndexView ix;  // layout owned by spatial.cu
+    if (!cloud_index_view(b, n, index, &ix)) return HF_ERR_UNSUPPORTED;
+    const int npad = ix.npad;
+    const float4 *sorted = ix.sorted;
     if (npad <= 4096) return HF_ERR_UNSUPPORTED;  // small clouds: the exchange, not the update, is the cost
     if (npad <= 16384) {
         if (warps_req == 4 || (warps_req == 0 && b <= 15)) return launch_fps_sorted<8, 4, 16>(mode, b, n, npad, m, inp, sorted, out, oxyz, s);

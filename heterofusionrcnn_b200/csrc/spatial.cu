@@ -851,6 +851,18 @@ extern "C" size_t hf_cloud_index_bytes(int b, int n) {
     return cloud_bytes(b, n);
 }
 
+// The one place outside carve_index that hands out pointers into an index: cropping.cu and fps_multi.cu go through it.
+bool hf::cloud_index_view(int b, int n, const void *index, CloudIndexView *view) {
+    if (!index || !aligned16(index) || b < 0 || hf_cloud_index_bytes(b, n) == 0) return false;
+    const CloudDesc d = carve_index(b, n, nullptr, const_cast<void *>(index));
+    view->sorted = d.sorted;
+    view->boxes = d.boxes;
+    view->super = d.super;
+    view->npad = d.npad;
+    view->nsuper = d.nsuper;
+    return true;
+}
+
 extern "C" size_t hf_spatial_workspace_bytes(int b, int n, int m) {
     const size_t a = hf_cloud_index_bytes(b, n), c = hf_cloud_index_bytes(b, m);
     return (a && c) ? a + c : 0;
