@@ -190,6 +190,40 @@ def knn_point(k, xyz1, xyz2):
     return val, idx
 
 
+def expanded_sqdist(xyz1, xyz2):
+    """The (b, m, n) matrix knn_point_old sorts: r_xyz2 - 2 * xyz2 . xyz1^T + r_xyz1^T (grouping/tf_grouping.py:
+    117-121), float32.  The batched product is a plain library GEMM, as in the reference (tf.matmul)."""
+    r1 = (xyz1 * xyz1).sum(dim=2, keepdim=True)  # (b, n, 1)
+    r2 = (xyz2 * xyz2).sum(dim=2, keepdim=True)  # (b, m, 1)
+    mul = torch.bmm(xyz2, xyz1.transpose(1, 2))  # (b, m, n)
+    return (r2 - 2 * mul + r1.transpose(1, 2)).contiguous()
+
+
+def knn_point_old(k, xyz1, xyz2):
+    """
+    Input:
+        k: int32, number of k in k-nn search
+        xyz1: (batch_size, ndataset, c) float32 array, input points
+        xyz2: (batch_size, npoint, c) float32 array, query points
+    Output:
+        val: (batch_size, npoint, k) float32 array, L2 distances
+        idx: (batch_size, npoint, k) int32 array, indices to input points
+
+    Reference: grouping/tf_grouping.py:98-131 - the expanded-form distance matrix, select_top_k (the SelectionSort
+    op) and a slice of its first k columns.  Kept for completeness of the module's public names (the reference uses
+    it only in its __main__ demo); knn_point is the fused form that never builds the matrix.  val carries the
+    cancellation error of the expanded form, exactly like the reference.  Any c.
+    """
+    require(isinstance(k, int) and k > 0, "SelectionSort expects positive k")
+    xyz1 = dev_tensor(xyz1, torch.float32, "xyz1")
+    xyz2 = dev_tensor(xyz2, torch.float32, "xyz2")
+    require(xyz1.dim() == 3 and xyz2.dim() == 3 and xyz1.shape[0] == xyz2.shape[0] and xyz1.shape[2] == xyz2.shape[2],
+            "knn_point_old expects (batch_size, ndataset, c) xyz1 and (batch_size, npoint, c) xyz2")
+    require(k <= xyz1.shape[1], "knn_point_old: input must have at least k columns")
+    outi, out = select_top_k(k, expanded_sqdist(xyz1, xyz2))
+    return out[:, :, :k].contiguous(), outi[:, :, :k].contiguous()
+
+
 def group_point_concat(xyz, points, idx, new_xyz):
     """The tail of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49-60) as one kernel:
 

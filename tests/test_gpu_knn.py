@@ -141,6 +141,27 @@ def test_select_top_k_of_the_distance_matrix_agrees_with_knn_point(cuda):
     assert (oi[:, :, :8] == ki).float().mean().item() > 0.999  # the torch matrix rounds differently from sqdist
 
 
+@pytest.mark.parametrize("b,n,m,k", [(2, 2048, 128, 8), (1, 1000, 77, 32), (2, 300, 300, 1)])
+def test_knn_point_old_is_the_reference_composition(cuda, oracle, b, n, m, k):
+    """knn_point_old (grouping/tf_grouping.py:98-131) = expanded-form matrix -> SelectionSort -> first k columns.
+    Exact against the oracle's selection sort run on the very matrix the op sorted; pinned on the reference's float32
+    formula (restated in numpy) within that formula's own rounding error; and the neighbours agree with the fused
+    knn_point except at near-ties."""
+    from heterofusionrcnn_b200.grouping.tf_grouping import expanded_sqdist, knn_point_old
+
+    xyz, _ = synthetic.make_scans(n + k, b, n)
+    x1 = T(xyz, cuda)
+    x2 = x1[:, ::max(1, n // m)][:, :m].contiguous() + 0.01
+    val, idx = knn_point_old(k, x1, x2)
+    assert val.shape == (b, m, k) and idx.shape == (b, m, k) and idx.dtype == torch.int32
+    wi, wv = oracle.select_top_k(k, N(expanded_sqdist(x1, x2)))
+    assert np.array_equal(N(idx), wi[:, :, :k]) and np.array_equal(N(val), wv[:, :, :k])
+    decided = oracle.check_knn_against_reference_form(k, N(x1), N(x2), N(val), N(idx))
+    assert decided > 0.5  # most ranks are decided by a margin above the formula's own rounding error
+    _, ki = knn_point(k, x1, x2)
+    assert (idx == ki).float().mean().item() > 0.98
+
+
 # ---------------------------------------------------------------- prob_sample (SURVEY 8f row 4)
 @pytest.mark.parametrize("b,n,m", [(2, 40, 1000), (3, 8192, 4096), (2, 20000, 5000), (1, 8195, 300), (2, 1, 10), (1, 3, 7),
                                    (1, 100000, 20000)])
