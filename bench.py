@@ -82,6 +82,8 @@ def parse_args():
     ap.add_argument("--msg-radii", action="store_true",
                     help="use the reference configs' outer MSG radii [0.5,1,2,4] instead of BASELINE's [0.1..0.8]")
     ap.add_argument("--cpu-scenes", type=int, default=0, help="CPU sample size in scans (0 = auto)")
+    ap.add_argument("--no-side-legs", action="store_true",
+                    help="skip the separately timed legs of rank 0 at N=1 (BEV IoU / NMS pair rates, BASELINE configs[0])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--table", action="store_true", help="also print a per-launch table to stderr")
@@ -431,6 +433,117 @@ def run_reference(args):
     }
     print(json.dumps(line))
     return 0
+
+
+# --------------------------------------------------------------------------------------
+# legs timed on their own (SURVEY.md 8d work units that the chained step does not expose)
+# --------------------------------------------------------------------------------------
+def side_legs(torch, hf, dev, cfg, batch):
+    """Rank 0, N=1, after the timed region.  Each leg: 3 warm-up calls, then `reps` calls between two CUDA events on
+    the current stream, GPU otherwise idle, inputs resident.
+      bev_iou   compute_bev_iou at SURVEY 8(a) a8's sizes 9000x64 and 2048x2048: pairs/s (N*M pairs, 8d) and the HBM
+                fraction of its algorithmic bytes (20 B per input box, 8 B per pair written);
+      nms       oriented_nms, `batch` scenes x cfg.nms_boxes, full keep list, at the thresholds of rpn_multiclass.config:
+                25-30,43 (0.85 / 0.8 / 0.01): pairs/s over N(N-1)/2 pairs per scene (8d) and how many of them reached the
+                exact polygon clip; plus the early-stopping form the chained step uses (first cfg.post_nms kept);
+      config0   BASELINE configs[0]: three_nn + three_interpolate of fixture scan 000000 (16384 <- 4096 FPS picks,
+                C = 128), GPU launches beside the reference's own CPU code for the pair: interpolate/interpolate.cpp
+                compiled as it lies (oracle/_ref/libref_interpolate_cpu.so, built in the authoring container and shipped;
+                the oracle port when it is absent - said in `cpu_kind`) after the oracle's three_nn (the reference's
+                threenn_cpu ignores the query point, SURVEY 8c, so its three_nn is not timed)."""
+    import numpy as np
+
+    from heterofusionrcnn_b200 import synthetic
+    from heterofusionrcnn_b200.bev_iou.bev_iou import compute_bev_iou, oriented_nms_batch
+    from heterofusionrcnn_b200.interpolate.tf_interpolate import three_interpolate, three_nn
+    from heterofusionrcnn_b200.sampling.tf_sampling import farthest_point_sample, gather_point
+
+    hbm_peak, _ = peaks()
+    lib = hf.load()
+
+    def timed(fn, reps):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    out = {"note": "each leg timed alone with CUDA events (3 warm-up calls, then the stated repetitions), inputs resident"}
+    # ---- BEV IoU matrix
+    iou = []
+    for na, nb in ((9000, 64), (2048, 2048)):
+        a = torch.from_numpy(synthetic.make_nms_boxes(5, na)).to(dev)
+        b = torch.from_numpy(synthetic.make_nms_boxes(6, nb)).to(dev)
+        ms = timed(lambda: compute_bev_iou(a, b), 50)
+        by = 20 * (na + nb) + 8 * na * nb
+        iou.append({"num_a": na, "num_b": nb, "reps": 50, "ms": ms, "pairs_per_s": na * nb / (ms / 1e3),
+                    "algorithmic_bytes": by, "hbm_frac": by / (ms / 1e3) / 1e9 / hbm_peak,
+                    "note": "through the Python op, which also allocates both outputs per call"})
+    out["bev_iou"] = iou
+    # ---- oriented NMS
+    nbx = cfg.nms_boxes
+    boxes = torch.from_numpy(np.stack([synthetic.make_nms_boxes(2 * 17 + i, nbx) for i in range(batch)])).to(dev)
+    ws_bytes = int(lib.hf_oriented_nms_workspace_bytes(batch, nbx))
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+    keep = torch.empty((batch, nbx), dtype=torch.int32, device=dev)
+    num = torch.empty((batch,), dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    all_pairs = batch * nbx * (nbx - 1) // 2
+    nms = []
+    for th in (0.85, 0.8, 0.01):
+        def full():
+            rc = lib.hf_oriented_nms(boxes.data_ptr(), batch, nbx, th, keep.data_ptr(), num.data_ptr(), ws.data_ptr(), ws_bytes, st)
+            assert rc == 0, lib.hf_last_error()
+        ms = timed(full, 10)
+        clipped = int(lib.hf_oriented_nms_last_pair_count(batch, nbx, ws.data_ptr(), st))
+        ms_top = timed(lambda: oriented_nms_batch(boxes, th, return_num_kept=True, max_keep=cfg.post_nms), 10)
+        nms.append({"thresh": th, "scenes": batch, "boxes": nbx, "reps": 10, "ms_full_keep_list": ms, "pairs": all_pairs,
+                    "pairs_per_s": all_pairs / (ms / 1e3), "pairs_clipped": clipped, "clipped_share": clipped / all_pairs,
+                    "kept_mean": float(num.float().mean().item()), "ms_first_%d_kept" % cfg.post_nms: ms_top})
+    out["oriented_nms"] = nms
+    # ---- BASELINE configs[0]
+    gpath = os.path.join(ROOT, "tests", "golden", "kitti_000000_16384.npz")
+    if os.path.exists(gpath):
+        from oracle import binding as O  # the CPU side of this leg (the cpu_baseline use of the checker)
+
+        O.build()
+        xyz = np.load(gpath)["xyz"][None].astype(np.float32)
+        x = torch.from_numpy(xyz).to(dev)
+        known = gather_point(x, farthest_point_sample(4096, x))
+        feats_h = np.random.default_rng(0).standard_normal((1, 4096, 128)).astype(np.float32)
+        feats = torch.from_numpy(feats_h).to(dev)
+        d, i = three_nn(x, known)
+        w_h = synthetic.fp_weights(d.cpu().numpy())
+        w = torch.from_numpy(w_h).to(dev)
+        ms_nn = timed(lambda: three_nn(x, known), 50)
+        ms_ip = timed(lambda: three_interpolate(feats, i, w), 50)
+        known_h, i_h = known.cpu().numpy(), i.cpu().numpy()
+        O.set_threads(1)
+        t0 = time.perf_counter()
+        O.three_nn(xyz, known_h)
+        cpu_nn = (time.perf_counter() - t0) * 1e3
+        use_ref = O.ref_available("libref_interpolate_cpu.so")
+        ip = O.ref_interpolate_cpu if use_ref else O.three_interpolate
+        ip(feats_h, i_h, w_h)
+        t0 = time.perf_counter()
+        for _ in range(5):
+            ip(feats_h, i_h, w_h)
+        cpu_ip = (time.perf_counter() - t0) * 1e3 / 5
+        O.set_threads(host_cores())
+        out["config0"] = {
+            "workload": "configs[0]: fixture KITTI scan 000000, three_nn + three_interpolate, 16384 <- 4096, C=128, one scan",
+            "gpu_ms": {"three_nn": ms_nn, "three_interpolate": ms_ip, "both": ms_nn + ms_ip},
+            "cpu_ms": {"three_nn": cpu_nn, "three_interpolate": cpu_ip, "both": cpu_nn + cpu_ip}, "cpu_cores": 1,
+            "cpu_kind": {"three_nn": "port (oracle/hf_oracle.cpp restating tf_interpolate_g.cu:22-65)",
+                         "three_interpolate": "reference (interpolate/interpolate.cpp:84-104 compiled unmodified)" if use_ref
+                         else "port (oracle/_ref/libref_interpolate_cpu.so not shipped)"},
+            "scans_per_s_gpu": 1e3 / (ms_nn + ms_ip), "scans_per_s_cpu": 1e3 / (cpu_nn + cpu_ip)}
+    return out
 
 
 # --------------------------------------------------------------------------------------
@@ -889,6 +1002,8 @@ def run_b200(args):
     if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only
         cb, _ = time_cpu(args, cfg, 1, 0, single_thread=True)
         line["cpu_baseline"] = cb
+    if not args.no_side_legs and world == 1:
+        line["side_legs"] = side_legs(torch, hf, dev, cfg, args.batch)
     if args.table:
         for o in ops:
             sys.stderr.write("%-34s %-5s %9.4f ms (alone %9.4f) x%d  %s %s  frac=%s  share=%.3f\n" % (

@@ -24,7 +24,7 @@ if has ref; then
   timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/${TAG}_bench_ref.json 2>$OUT/${TAG}_bench_ref.err; echo "ref rc=$?"
 fi
 if has ncu; then
-  PROF="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-config5 --serial --profile-range"
+  PROF="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-config5 --no-side-legs --serial --profile-range"
   timeout 300 $PROF > $OUT/${TAG}_plain.log 2>&1 &&
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 200 --csv --log-file $OUT/${TAG}_launches.csv $PROF > $OUT/${TAG}_ncu1.log 2>&1
   echo "launch list rc=$?"
