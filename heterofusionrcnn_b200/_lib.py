@@ -80,6 +80,7 @@ SIGNATURES = {
                                      _ptr]),
     "hf_prob_sample": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_group_point_concat": (_c_int, [_c_int] * 5 + [_ptr] * 6),
+    "hf_group_point_concat_msg": (_c_int, [_c_int] * 5 + [_ptr] * 6),
     "hf_group_point": (_c_int, [_c_int, _c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_nn": (_c_int, [_c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "hf_three_interpolate": (_c_int, [_c_int, _c_int, _c_int, _c_int, _ptr, _ptr, _ptr, _ptr, _ptr]),

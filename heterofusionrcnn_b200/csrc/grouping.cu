@@ -270,6 +270,9 @@ __global__ void __launch_bounds__(kGpThreads)
 // [xyz[idx[r]] - new_xyz[r / nsample], points[idx[r]]], width 3 + c (c = 0: the translated xyz only).
 // The reference runs two group_point ops, a tile + subtract and a concat: four passes over the big tensor.
 // One warp per output row, four rows in flight; rows are 3 + c floats, so accesses are 32-bit, coalesced.
+// XYZ_LAST: columns are [points[idx[r]], xyz[idx[r]] - new_xyz[r / nsample]] - the order pointnet_sa_module_msg
+// concatenates in (pointnet_util.py:262-264), the opposite of sample_and_group's.
+template <bool XYZ_LAST>
 __global__ void __launch_bounds__(kGpThreads)
     group_concat_kernel(int n, int c, int rows, int nsample, const float *__restrict__ xyz, const float *__restrict__ points,
                         const int *__restrict__ idx, const float *__restrict__ new_xyz, float *__restrict__ out) {
@@ -292,8 +295,10 @@ __global__ void __launch_bounds__(kGpThreads)
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 if (src[u] < 0) continue;
-                if (j < 3) v[u] = __fsub_rn(__ldg(&x[(size_t)src[u] * 3 + j]), __ldg(&ctr[(size_t)((r0 + u) / nsample) * 3 + j]));
-                else v[u] = __ldg(&pts[(size_t)src[u] * c + (j - 3)]);
+                const int jx = XYZ_LAST ? j - c : j;       // column of the translated coordinates, if 0 <= jx < 3
+                const int jp = XYZ_LAST ? j : j - 3;       // column of the features otherwise
+                if (jx >= 0 && jx < 3) v[u] = __fsub_rn(__ldg(&x[(size_t)src[u] * 3 + jx]), __ldg(&ctr[(size_t)((r0 + u) / nsample) * 3 + jx]));
+                else v[u] = __ldg(&pts[(size_t)src[u] * c + jp]);
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -448,9 +453,27 @@ extern "C" int hf_group_point_pair(int b, int n, int c, int m, int nsample, cons
     return group_point_any(b, n, c, m, nsample, points, idx, out_points, xyz, out_xyz, (cudaStream_t)stream);
 }
 
+namespace hf {
+namespace {
+int group_concat_any(bool xyz_last, int b, int n, int c, int m, int nsample, const float *xyz, const float *points,
+                     const int *idx, const float *new_xyz, float *out, hf_stream_t stream);
+}
+}  // namespace hf
+
 extern "C" int hf_group_point_concat(int b, int n, int c, int m, int nsample, const float *xyz, const float *points,
                                      const int *idx, const float *new_xyz, float *out, hf_stream_t stream) {
-    using namespace hf;
+    return hf::group_concat_any(false, b, n, c, m, nsample, xyz, points, idx, new_xyz, out, stream);
+}
+
+extern "C" int hf_group_point_concat_msg(int b, int n, int c, int m, int nsample, const float *xyz, const float *points,
+                                         const int *idx, const float *new_xyz, float *out, hf_stream_t stream) {
+    return hf::group_concat_any(true, b, n, c, m, nsample, xyz, points, idx, new_xyz, out, stream);
+}
+
+namespace hf {
+namespace {
+int group_concat_any(bool xyz_last, int b, int n, int c, int m, int nsample, const float *xyz, const float *points,
+                     const int *idx, const float *new_xyz, float *out, hf_stream_t stream) {
     HF_REQUIRE(b >= 0 && n >= 1 && c >= 0 && m >= 0 && nsample >= 1,
                "GroupPoint expects (batch_size, num_points, channel) points shape");
     HF_REQUIRE(b <= 65535, "GroupPoint: batch_size > 65535 not supported");
@@ -461,8 +484,14 @@ extern "C" int hf_group_point_concat(int b, int n, int c, int m, int nsample, co
     int blocks = (rows + 4 * (kGpThreads / 32) - 1) / (4 * (kGpThreads / 32));
     const int cap = (num_sms() * 8 + b - 1) / b;
     if (blocks > cap) blocks = cap;
-    group_concat_kernel<<<dim3(blocks, b), kGpThreads, 0, (cudaStream_t)stream>>>(n, c, rows, nsample, xyz, c ? points : nullptr,
-                                                                                   idx, new_xyz, out);
+    const dim3 grid(blocks, b);
+    if (xyz_last && c)
+        group_concat_kernel<true><<<grid, kGpThreads, 0, (cudaStream_t)stream>>>(n, c, rows, nsample, xyz, points, idx, new_xyz, out);
+    else
+        group_concat_kernel<false><<<grid, kGpThreads, 0, (cudaStream_t)stream>>>(n, c, rows, nsample, xyz, c ? points : nullptr,
+                                                                                  idx, new_xyz, out);
     HF_LAUNCH_OK("group_concat_kernel");
     return HF_OK;
 }
+}  // namespace
+}  // namespace hf

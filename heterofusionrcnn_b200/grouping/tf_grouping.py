@@ -224,13 +224,15 @@ def knn_point_old(k, xyz1, xyz2):
     return out[:, :, :k].contiguous(), outi[:, :, :k].contiguous()
 
 
-def group_point_concat(xyz, points, idx, new_xyz):
+def group_point_concat(xyz, points, idx, new_xyz, xyz_last=False):
     """The tail of sample_and_group (hf/core/feature_extractors/pointnet_util.py:49-60) as one kernel:
 
         grouped_xyz = group_point(xyz, idx) - new_xyz[:, :, None, :]
         new_points  = concat([grouped_xyz, group_point(points, idx)], -1)     (points None: grouped_xyz)
 
     xyz (b,n,3), points (b,n,c) or None, idx (b,m,nsample) int32, new_xyz (b,m,3) -> (b,m,nsample,3+c).
+    xyz_last=True gives the column order of pointnet_sa_module_msg (:262-264),
+    concat([group_point(points, idx), grouped_xyz], -1).
     """
     xyz = dev_tensor(xyz, torch.float32, "xyz")
     idx = dev_tensor(idx, torch.int32, "idx")
@@ -249,7 +251,8 @@ def group_point_concat(xyz, points, idx, new_xyz):
         c = points.shape[2]
     out = torch.empty((b, m, nsample, 3 + c), dtype=torch.float32, device=xyz.device)
     with torch.cuda.device(xyz.device):
-        rc = _lib.load().hf_group_point_concat(b, n, c, m, nsample, xyz.data_ptr(), points.data_ptr() if c else None,
-                                               idx.data_ptr(), new_xyz.data_ptr(), out.data_ptr(), stream_ptr(xyz.device))
+        fn = _lib.load().hf_group_point_concat_msg if xyz_last else _lib.load().hf_group_point_concat
+        rc = fn(b, n, c, m, nsample, xyz.data_ptr(), points.data_ptr() if c else None, idx.data_ptr(), new_xyz.data_ptr(),
+                out.data_ptr(), stream_ptr(xyz.device))
     _lib.check(rc, "group_point_concat")
     return out

@@ -43,6 +43,32 @@ def sample_and_group(npoint, radius, nsample, xyz, points, knn=False, use_xyz=Tr
     return new_xyz, new_points, idx, grouped_xyz
 
 
+def sample_and_group_msg(npoint, radius_list, nsample_list, xyz, points, use_xyz=True):
+    """The operator part of pointnet_sa_module_msg (hf/core/feature_extractors/pointnet_util.py:223-286, the module the
+    paper config uses: rpn_cars_pointnet_paper.config:62-111): ONE farthest-point sampling, then per scale i
+
+        idx, _         = query_ball_point(radius_list[i], nsample_list[i], xyz, new_xyz)
+        grouped_xyz    = group_point(xyz, idx) - new_xyz[:, :, None, :]
+        grouped_points = concat([group_point(points, idx), grouped_xyz], -1)    # features FIRST, unlike sample_and_group
+                         (points None: grouped_xyz; use_xyz False: group_point(points, idx))
+
+    Returns new_xyz (b,npoint,3) and the list of grouped_points, (b,npoint,nsample_i,channel+3) each - the tensors the
+    module's per-scale MLPs consume.  Both clouds are indexed once and the index is shared by every scale's search.
+    """
+    new_xyz = gather_point(xyz, farthest_point_sample(npoint, xyz))
+    ix = (None, None)
+    if spatial.applies(npoint, xyz.shape[1]):
+        ix = (spatial.build_cloud_index(xyz), spatial.build_cloud_index(new_xyz))
+    grouped = []
+    for radius, nsample in zip(radius_list, nsample_list):
+        idx, _ = query_ball_point(radius, nsample, xyz, new_xyz, index1=ix[0], index2=ix[1])
+        if points is not None and not use_xyz:
+            grouped.append(group_point(points, idx))
+        else:
+            grouped.append(group_point_concat(xyz, points, idx, new_xyz, xyz_last=True))
+    return new_xyz, grouped
+
+
 def interpolate_points(xyz1, xyz2, points2):
     """The operator part of pointnet_fp_module (hf/core/feature_extractors/pointnet_util.py:301-308):
     three_nn, inverse-distance weights (clamped at 1e-10), three_interpolate.

@@ -208,6 +208,14 @@ int hf_group_point_concat(int b, int n, int c, int m, int nsample, const float *
                           const float *points, const int *idx, const float *new_xyz, float *out,
                           hf_stream_t stream);
 
+/* The same pass in the column order of the multi-scale-grouping module, pointnet_sa_module_msg
+ * (hf/core/feature_extractors/pointnet_util.py:253-264: per scale, group_point on xyz, subtract the seed, group_point on
+ * the features, tf.concat([grouped_points, grouped_xyz])): out (b,m,nsample,c+3) = concat(points[idx], xyz[idx] -
+ * new_xyz).  c = 0 (points NULL) gives the translated grouped_xyz alone, as that module does without features. */
+int hf_group_point_concat_msg(int b, int n, int c, int m, int nsample, const float *xyz,
+                              const float *points, const int *idx, const float *new_xyz, float *out,
+                              hf_stream_t stream);
+
 /* ---- interpolate -------------------------------------------------------- */
 /* Replaces three_nn_gpu(b,n,m,unknown,known,dist2,idx), interpolate/tf_interpolate_g.cu:68.
  * unknown (b,n,3), known (b,m,3) -> dist2 (b,n,3) squared distances ascending,

@@ -149,3 +149,33 @@ def test_sample_and_group_and_fp_interpolation(cuda, oracle, knn, use_xyz, c):
         wd, wi = oracle.three_nn(xyz, w_new)
         want = oracle.three_interpolate(feats, wi, synthetic.fp_weights(wd))
         assert np.allclose(N(got), want, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n,m,radii,nsamples,c,use_xyz", [(16384, 4096, [0.1, 0.5], [16, 32], 1, True),
+                                                          (4096, 1024, [0.5, 1.0], [16, 32], 96, True),
+                                                          (1024, 256, [1.0, 2.0], [16, 32], 32, False),
+                                                          (512, 64, [2.0, 4.0], [16, 32], 0, True)])
+def test_sample_and_group_msg_matches_the_reference_composition(cuda, oracle, n, m, radii, nsamples, c, use_xyz):
+    """pointnet_util.sample_and_group_msg = the operator part of pointnet_sa_module_msg (reference pointnet_util.py:
+    223-286) at the radii / nsample of rpn_cars_pointnet_paper.config:65-111, against the same composition of oracle
+    ops: one FPS, then per scale ball query, two group_points, seed subtraction and the [points, xyz] concat.  Bit-exact."""
+    from heterofusionrcnn_b200 import pointnet_util
+
+    rng = np.random.default_rng(n + c)
+    b = 2
+    xyz, _ = synthetic.make_scans(31, b, n)
+    pts = rng.standard_normal((b, n, c)).astype(np.float32) if c else None
+    new_xyz, grouped = pointnet_util.sample_and_group_msg(m, radii, nsamples, T(xyz, cuda), T(pts, cuda) if c else None,
+                                                          use_xyz=use_xyz)
+    w_new = oracle.gather_point(xyz, oracle.farthest_point_sample(m, xyz))
+    assert np.array_equal(N(new_xyz), w_new) and len(grouped) == len(radii)
+    for r, ns, got in zip(radii, nsamples, grouped):
+        w_idx, _ = oracle.query_ball_point(r, ns, xyz, w_new)
+        w_gxyz = oracle.group_point(xyz, w_idx) - w_new[:, :, None, :]
+        if c == 0:
+            want = w_gxyz
+        elif use_xyz:
+            want = np.concatenate([oracle.group_point(pts, w_idx), w_gxyz], axis=-1)  # features first (:262-264)
+        else:
+            want = oracle.group_point(pts, w_idx)
+        assert N(got).shape == want.shape and np.array_equal(N(got), want), r
